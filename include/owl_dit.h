@@ -1,0 +1,234 @@
+/*
+ * owl_dit.h -- C ABI of libowl_dit.so: hand-written sm_100a (B200) CUDA kernels for the owl_wms
+ * DiT-block hot path (block-causal attention with QK-RMSNorm + RoPE + KV cache, adaLN
+ * modulate / gate / residual, MLP), forward and backward.
+ *
+ * The reference (shahbuland/owl-audio-exps) has NO native / FFI interface for this path: every op
+ * below is issued through PyTorch from `owl_wms/nn/*.py`.  Each entry point therefore cites the
+ * reference Python lines whose arithmetic it replaces.  Paths are relative to the reference root.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless stated otherwise.
+ *   - the caller owns every buffer (inputs, outputs, workspaces).  Nothing is allocated or freed
+ *     by the library; pointers are borrowed for the duration of the call.
+ *   - every call only ENQUEUES work on `stream` (a cudaStream_t passed as void*); no call
+ *     synchronises or reads device memory on the host => CUDA-graph-capture safe.
+ *   - return value: OWL_OK (0), a negative OWL_ERR_* for rejected arguments, or a positive
+ *     cudaError_t from the launch.  Never throws, never aborts.
+ *   - "bf16" = __nv_bfloat16 storage; all accumulation is fp32.
+ *   - stateless and re-entrant (only a read-only cache of the driver entry point / SM count).
+ */
+#ifndef OWL_DIT_H_
+#define OWL_DIT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OWL_OK 0
+#define OWL_ERR_BAD_ARG (-1)     /* null pointer / non-positive size / inconsistent sizes      */
+#define OWL_ERR_ALIGN (-2)       /* pointer or leading dimension violates 16-byte alignment    */
+#define OWL_ERR_UNSUPPORTED (-3) /* shape outside what the kernels implement (e.g. head dim)   */
+#define OWL_ERR_DRIVER (-4)      /* CUDA driver entry point / tensor-map encoding failed       */
+
+typedef void* owl_stream_t; /* cudaStream_t */
+
+/* ABI version (bumped on any signature change) and human-readable error text. */
+int owl_abi_version(void);
+const char* owl_error_string(int code);
+/* Number of kernels this library has launched from this process (monotonic; for bench.py's
+ * `gpu_launches`).  Host-side counter only. */
+uint64_t owl_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * GEMM  (tcgen05.mma, TMEM accumulators, TMA-fed, persistent, warp-specialised)
+ *
+ * Replaces every nn.Linear on the path and its autograd:
+ *   owl_wms/nn/attn.py:72-73,82,113 (qkv, out), owl_wms/nn/mlp.py:10-11,34-36 (fc1, fc2),
+ *   owl_wms/nn/modulation.py:10,19,31,40 (adaLN / gate projections of silu(cond)).
+ *
+ * C[m,n] = sum_k opA(m,k) * opB(n,k), bf16 operands, fp32 accumulation, followed by a fused
+ * epilogue.  `layout` picks the operand storage:
+ *   OWL_GEMM_NT : A is [M,K] (ld = lda), B is [N,K]      forward   y  = x W^T
+ *   OWL_GEMM_NN : A is [M,K],            B is [K,N]      dgrad     dx = dy W
+ *   OWL_GEMM_TN : A is [K,M],            B is [K,N]      wgrad     dW = dy^T x
+ * Leading dimensions are in elements and must be multiples of 8; base pointers 16-byte aligned.
+ * ---------------------------------------------------------------------------------------------- */
+enum { OWL_GEMM_NT = 0, OWL_GEMM_NN = 1, OWL_GEMM_TN = 2 };
+
+enum {
+  /* out0[m,n] (bf16) = acc + bias[n]                                                             */
+  OWL_EPI_STORE = 0,
+  /* z = bf16(acc + bias); out0 = z; out1 = bf16(silu(z))            (mlp.py:34-35)               */
+  OWL_EPI_BIAS_SILU = 1,
+  /* y = bf16(acc + bias); out1 = y (optional);                                                   */
+  /* out0 = bf16(aux0[m,n] + aux1[m / rows_per_frame, n] * y)        (modulation.py:41-43 +       */
+  /*                                                                  attn.py:135,141 residual)   */
+  OWL_EPI_GATE_RESIDUAL = 2,
+  /* g = acc * silu'(aux0[m,n]); out0 = bf16(g) if out0 else outf (+)= g                          */
+  /*                                   (backward of F.silu, mlp.py:35 / modulation.py:17,38)      */
+  OWL_EPI_DSILU = 3,
+  /* outf[m,n] (fp32) = acc (+ outf[m,n] if accumulate)              (weight gradients)           */
+  OWL_EPI_F32 = 4
+};
+
+typedef struct owl_gemm_epilogue {
+  int32_t mode;           /* OWL_EPI_*                                                            */
+  int32_t accumulate;     /* fp32 outputs: add to the existing contents                           */
+  int32_t rows_per_frame; /* OWL_EPI_GATE_RESIDUAL: tokens per frame T (gate row = m / T)         */
+  int32_t reserved;
+  const float* bias;      /* [N] fp32 or NULL                                                     */
+  void* out0;             /* bf16 [M, ld0]                                                        */
+  int64_t ld0;
+  void* out1;             /* bf16 [M, ld1] or NULL                                                */
+  int64_t ld1;
+  float* outf;            /* fp32 [M, ldf] or NULL                                                */
+  int64_t ldf;
+  const void* aux0;       /* bf16 [M, lda0]: residual (GATE_RESIDUAL) or pre-activation (DSILU)   */
+  int64_t lda0;
+  const void* aux1;       /* bf16 [M / rows_per_frame, lda1]: gate                                */
+  int64_t lda1;
+} owl_gemm_epilogue;
+
+int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* B,
+                  int64_t ldb, const owl_gemm_epilogue* epi, owl_stream_t stream);
+
+/* Plain CUDA-core GEMM with the same contract (OWL_EPI_STORE / OWL_EPI_F32 only, no bias).
+ * Verification aid for tests: an independent on-device answer at sizes where the CPU oracle is
+ * too slow.  Never called by the product path. */
+int owl_gemm_bf16_check(int layout, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* B,
+                        int64_t ldb, float* C, int64_t ldc, owl_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Memory-bound kernels: coalesced, 128-bit vectorised, warp-shuffle reductions.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* dst[i] = bf16(src[i])  -- fp32 master weights -> bf16 operands (what autocast does per forward,
+ * rft_trainer.py:146).  n elements, n % 8 == 0 not required. */
+int owl_cast_f32_bf16(const float* src, void* dst, int64_t n, owl_stream_t stream);
+
+/* y = silu(x), bf16, n elements                                    (modulation.py:17,38)         */
+int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream);
+
+/* adaLN modulate forward                                           (modulation.py:20-25,
+ *                                                                   normalization.py:10-11)
+ *   h[m,:] = rms_norm(x[m,:]) * (1 + a[m / T,:]) + b[m / T,:]
+ * x,h: bf16 [M,d]; a,b: bf16 rows of length d with row stride ld_ab (they are column slices of
+ * the fused cond projection); rstd: fp32 [M] out (saved for backward; may be NULL).
+ * eps: value added to mean(x^2) (see DESIGN.md on F.rms_norm's default).  d % 8 == 0.           */
+int owl_adaln_modulate_fwd(const void* x, const void* a, const void* b, int64_t ld_ab, void* h, float* rstd,
+                           int64_t M, int64_t d, int64_t T, float eps, owl_stream_t stream);
+
+/* adaLN modulate backward.  Given dh [M,d]:
+ *   dx[m,:]  = rms_norm_bwd(dh * (1 + a)) (+ dres[m,:] if dres != NULL)   (residual path grad)
+ *   da[f,:]  = sum_{m in frame f} dh[m,:] * xhat[m,:]
+ *   db[f,:]  = sum_{m in frame f} dh[m,:]
+ * da, db: bf16 rows with row stride ld_dab (column slices of the cond-projection gradient).      */
+int owl_adaln_modulate_bwd(const void* dh, const void* x, const void* a, int64_t ld_ab, const float* rstd,
+                           const void* dres, void* dx, void* da, void* db, int64_t ld_dab, int64_t M, int64_t d,
+                           int64_t T, owl_stream_t stream);
+
+/* gate forward, unfused (standalone Gate module / cond_gate; the block path fuses this into the
+ * GEMM epilogue OWL_EPI_GATE_RESIDUAL)                               (modulation.py:41-43,57-63)
+ *   out[m,:] = c[m / T,:] * x[m,:] (+ res[m,:] if res != NULL)                                   */
+int owl_gate_fwd(const void* x, const void* c, int64_t ld_c, const void* res, void* out, int64_t M, int64_t d,
+                 int64_t T, owl_stream_t stream);
+
+/* gate + residual backward                                          (modulation.py:41-43)
+ *   x_out = x_in + c[m / T] * y    =>   dy[m,:] = dx[m,:] * c[m / T,:]
+ *                                       dc[f,:] = sum_{m in frame f} dx[m,:] * y[m,:]
+ *   dbias[n] (+)= sum_m dy[m,n]   (fp32, optional: bias gradient of the Linear that produced y)  */
+int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, void* dy, void* dc, int64_t ld_dc,
+                 float* dbias, int dbias_accumulate, int64_t M, int64_t d, int64_t T, owl_stream_t stream);
+
+/* out[n] (+)= sum_m x[m,n]; x bf16 [M, ld], out fp32 [N]           (bias gradients)              */
+int owl_colsum_bf16(const void* x, int64_t ld, float* out, int accumulate, int64_t M, int64_t N,
+                    owl_stream_t stream);
+
+/* QK-RMSNorm + RoPE + head split                                    (attn.py:83-89, rope.py:43-51)
+ *   qkv: bf16 [B, L, 3, H, dh] (the qkv Linear output)
+ *   q   -> bf16, element (b,h,l,:) at q + b*q_sb + h*q_sh + l*dh   (same for k, v with their strides;
+ *          k/v strides let the kernel write straight into a preallocated KV cache at its tail)
+ *   q,k = rope(rms_norm(.)) with cos/sin fp32 [*, dh/2] rows (pos_offset + l); v copied.
+ *   RoPE output layout is [even-rotated | odd-rotated] halves, as rope.py:48-51.
+ *   rstd_q, rstd_k: fp32 [B,H,L] out (NULL allowed).  dh in {64, 128}.                           */
+int owl_qk_norm_rope_fwd(const void* qkv, const float* cos_tab, const float* sin_tab, int64_t pos_offset, void* q,
+                         int64_t q_sb, int64_t q_sh, void* k, int64_t k_sb, int64_t k_sh, void* v, int64_t v_sb,
+                         int64_t v_sh, float* rstd_q, float* rstd_k, int64_t B, int64_t L, int64_t H, int64_t dh,
+                         float eps, owl_stream_t stream);
+
+/* Backward of the above: (dq, dk, dv) in [B,H,L,dh] (given strides) + saved rotated q,k and rstd
+ * -> dqkv bf16 [B, L, 3, H, dh].                                                                  */
+int owl_qk_norm_rope_bwd(const void* dq, const void* dk, const void* dv, int64_t g_sb, int64_t g_sh, const void* q,
+                         int64_t q_sb, int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh,
+                         const float* rstd_q, const float* rstd_k, const float* cos_tab, const float* sin_tab,
+                         int64_t pos_offset, void* dqkv, int64_t B, int64_t L, int64_t H, int64_t dh,
+                         owl_stream_t stream);
+
+/* KV-cache append                                                   (attn.py:92-99, kv_cache.py:50-58)
+ * Copies new rows src [B,H,Ln,dh] (strides src_sb, src_sh) into cache [B,H,cap,dh] at row `pos`.
+ * The reference re-concatenates the whole cache (O(cache) bytes per call); this moves only the
+ * new rows.                                                                                       */
+int owl_kv_append(const void* src, int64_t src_sb, int64_t src_sh, void* cache, int64_t cache_sb, int64_t cache_sh,
+                  int64_t pos, int64_t B, int64_t H, int64_t Ln, int64_t dh, owl_stream_t stream);
+
+/* Weight-less LayerNorm over the last dim (normalization.py:6-7), bf16 [M,d].                     */
+int owl_layer_norm_fwd(const void* x, void* y, int64_t M, int64_t d, float eps, owl_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Attention                                                          (attn.py:24-62,102-111)
+ *
+ * softmax(q k^T / sqrt(dh) + mask) v with the reference's frame-block mask evaluated in-kernel:
+ *   frame(i) = i / tokens_per_frame
+ *   allowed(i,j) = (!causal || frame(j) <= frame(i + q_offset))
+ *                  && |frame(i + q_offset) - frame(j)| < window_frames
+ *                  && (doc_id == NULL || doc_id[b, frame(i + q_offset)] == doc_id[b, frame(j)])
+ * window_frames <= 0 means "no window".  KV tiles that are fully masked are skipped.
+ *   q: bf16 (b,h,i,:) at q + b*q_sb + h*q_sh + i*dh;  k, v likewise with Lk rows
+ *   o: bf16 (b,i,h,:) at o + b*o_sb + i*o_sl + h*dh   (i.e. [B,L,H*dh] ready for the out Linear,
+ *      replacing attn.py:111's permute+contiguous copy)
+ *   lse: fp32 [B,H,Lq] natural-log-sum-exp of the scaled scores (saved for backward; NULL ok)
+ *   doc_id: int32 [B, doc_ld] frame-indexed, or NULL.
+ * dh in {64, 128}.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct owl_attn_mask {
+  int32_t tokens_per_frame;
+  int32_t window_frames; /* <= 0: unlimited */
+  int32_t q_offset;      /* tokens already in the KV prefix (kv_cache.length_at(0))               */
+  int32_t causal;        /* 0/1; decode mode (attn.py:106-107, block_mask None) = causal 0, window 0 */
+  const int32_t* doc_id; /* [B, doc_ld] or NULL                                                   */
+  int64_t doc_ld;
+} owl_attn_mask;
+
+int owl_attn_fwd(const void* q, int64_t q_sb, int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh,
+                 const void* v, int64_t v_sb, int64_t v_sh, void* o, int64_t o_sb, int64_t o_sl, float* lse,
+                 int64_t B, int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask,
+                 owl_stream_t stream);
+
+/* Backward.  dout/o: bf16 in the o layout above.  dq/dk/dv: bf16 [B,H,L*,dh] with strides g?_sb, g?_sh.
+ * delta: fp32 [B,H,Lq] workspace (rowsum(dout * o)).  dq_acc: fp32 [B,H,Lq,dh] workspace.        */
+int owl_attn_bwd(const void* dout, const void* o, int64_t o_sb, int64_t o_sl, const void* q, int64_t q_sb,
+                 int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb,
+                 int64_t v_sh, const float* lse, float* delta, float* dq_acc, void* dq, int64_t dq_sb, int64_t dq_sh,
+                 void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh, int64_t B,
+                 int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask, owl_stream_t stream);
+
+/* CUDA-core versions of the two calls above with identical contracts (one warp per query row /
+ * per key row).  Verification aid for tests, as owl_gemm_bf16_check.                              */
+int owl_attn_fwd_check(const void* q, int64_t q_sb, int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh,
+                       const void* v, int64_t v_sb, int64_t v_sh, void* o, int64_t o_sb, int64_t o_sl, float* lse,
+                       int64_t B, int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask,
+                       owl_stream_t stream);
+int owl_attn_bwd_check(const void* dout, const void* o, int64_t o_sb, int64_t o_sl, const void* q, int64_t q_sb,
+                       int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb,
+                       int64_t v_sh, const float* lse, float* delta, float* dq_acc, void* dq, int64_t dq_sb,
+                       int64_t dq_sh, void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh,
+                       int64_t B, int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask,
+                       owl_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OWL_DIT_H_ */

@@ -1,0 +1,545 @@
+// Memory-bound kernels of the DiT block: every one is a single pass over its tensors with 128-bit
+// loads/stores, fp32 math in registers and warp-shuffle row reductions.  Roofline = HBM.
+//
+// Row kernels use one warp per row; lane `l` owns the 8-element (16-byte) column groups
+// c = (i*32 + l)*8, i = 0..NV-1, so every warp-wide access is a contiguous 512-byte run.
+#include <cuda_bf16.h>
+
+#include "host_common.h"
+#include "sm100.cuh"
+
+namespace owl {
+
+static constexpr int kRowThreads = 256;  // 8 warps = 8 rows per CTA pass
+
+__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void stg16(void* p, const uint4& v) { *reinterpret_cast<uint4*>(p) = v; }
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 v;
+  v.x = pack_bf16(f[0], f[1]); v.y = pack_bf16(f[2], f[3]); v.z = pack_bf16(f[4], f[5]); v.w = pack_bf16(f[6], f[7]);
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// cast / silu
+// ------------------------------------------------------------------------------------------------
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int64_t n) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t n8 = n >> 3;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * i);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(src) + 2 * i + 1);
+    uint4 o;
+    o.x = pack_bf16(a.x, a.y); o.y = pack_bf16(a.z, a.w); o.z = pack_bf16(b.x, b.y); o.w = pack_bf16(b.z, b.w);
+    stg16(dst + 8 * i, o);
+  }
+  // tail (n % 8 elements)
+  for (int64_t i = (n8 << 3) + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+__global__ void silu_bf16_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int64_t n) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t n8 = n >> 3;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float f[8];
+    unpack8(ldg16(x + 8 * i), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = f[j] * sigmoidf_fast(f[j]);
+    stg16(y + 8 * i, pack8(f));
+  }
+  for (int64_t i = (n8 << 3) + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v = __bfloat162float(x[i]);
+    y[i] = __float2bfloat16_rn(v * sigmoidf_fast(v));
+  }
+}
+
+static inline int grid_for(int64_t work_items, int threads) {
+  int64_t blocks = (work_items + threads - 1) / threads;
+  const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+// ------------------------------------------------------------------------------------------------
+// adaLN modulate forward: h = rms_norm(x) * (1 + a[frame]) + b[frame]      (a, b may be NULL)
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(kRowThreads)
+adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const bf16* __restrict__ b, int64_t ld_ab,
+                 bf16* __restrict__ h, float* __restrict__ rstd_out, int64_t M, int d, int T, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
+    const bf16* xr = x + row * d;
+    uint4 xv[NV];
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        xv[i] = ldg16(xr + c);
+        float f[8];
+        unpack8(xv[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += f[j] * f[j];
+      }
+    }
+    ss = warp_sum(ss);
+    const float rstd = rsqrtf(ss / static_cast<float>(d) + eps);
+    if (rstd_out != nullptr && lane == 0) rstd_out[row] = rstd;
+    const int64_t frow = row / T;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        float f[8];
+        unpack8(xv[i], f);
+        if (a != nullptr) {
+          float fa[8], fb[8];
+          unpack8(ldg16(a + frow * ld_ab + c), fa);
+          unpack8(ldg16(b + frow * ld_ab + c), fb);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = f[j] * rstd * (1.f + fa[j]) + fb[j];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = f[j] * rstd;
+        }
+        stg16(h + row * d + c, pack8(f));
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// adaLN modulate backward, row part:
+//   g = dh * (1 + a);  xh = x * rstd;  dx = rstd * (g - xh * mean(g * xh)) (+ dres)
+//   if T == 1 also da = dh * xh, db = dh (a frame is a row; no reduction needed)
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(kRowThreads)
+adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, const bf16* __restrict__ a,
+                     int64_t ld_ab, const float* __restrict__ rstd_in, const bf16* __restrict__ dres,
+                     bf16* __restrict__ dx, bf16* __restrict__ da, bf16* __restrict__ db, int64_t ld_dab, int64_t M,
+                     int d, int T) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  const bool write_ab = (T == 1) && (da != nullptr);
+  for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
+    const float rstd = rstd_in[row];
+    const int64_t frow = row / T;
+    uint4 xv[NV], gv[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        xv[i] = ldg16(x + row * d + c);
+        gv[i] = ldg16(dh + row * d + c);
+        float fx[8], fg[8];
+        unpack8(xv[i], fx);
+        unpack8(gv[i], fg);
+        if (write_ab) {
+          float t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t[j] = fg[j] * fx[j] * rstd;
+          stg16(da + frow * ld_dab + c, pack8(t));
+          stg16(db + frow * ld_dab + c, gv[i]);
+        }
+        if (a != nullptr) {
+          float fa[8];
+          unpack8(ldg16(a + frow * ld_ab + c), fa);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) fg[j] *= (1.f + fa[j]);
+          gv[i] = pack8(fg);  // keep g (bf16-rounded) for the second pass: saves the re-read of a
+          unpack8(gv[i], fg);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += fg[j] * fx[j] * rstd;
+      }
+    }
+    s = warp_sum(s) / static_cast<float>(d);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        float fx[8], fg[8], o[8];
+        unpack8(xv[i], fx);
+        unpack8(gv[i], fg);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (fg[j] - fx[j] * rstd * s);
+        if (dres != nullptr) {
+          float fr[8];
+          unpack8(ldg16(dres + row * d + c), fr);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += fr[j];
+        }
+        stg16(dx + row * d + c, pack8(o));
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-frame column reductions (T > 1):
+//   out_pq[f, c] = sum_{r in frame f} p[r, c] * q[r, c] * (scale ? scale[r] : 1)
+//   out_p [f, c] = sum_{r in frame f} p[r, c]                       (optional)
+// grid = (frames, ceil(d / 512)); 64 threads x 8 columns.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64)
+frame_reduce_kernel(const bf16* __restrict__ p, const bf16* __restrict__ q, const float* __restrict__ scale,
+                    bf16* __restrict__ out_pq, bf16* __restrict__ out_p, int64_t ld_out, int d, int T) {
+  const int c = (blockIdx.y * 64 + threadIdx.x) * 8;
+  if (c >= d) return;
+  const int64_t f = blockIdx.x;
+  float apq[8], ap[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) apq[j] = ap[j] = 0.f;
+  const int64_t r0 = f * T;
+#pragma unroll 4
+  for (int r = 0; r < T; ++r) {
+    float fp[8], fq[8];
+    unpack8(ldg16(p + (r0 + r) * d + c), fp);
+    unpack8(ldg16(q + (r0 + r) * d + c), fq);
+    const float s = scale != nullptr ? __ldg(scale + r0 + r) : 1.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      apq[j] += fp[j] * fq[j] * s;
+      ap[j] += fp[j];
+    }
+  }
+  stg16(out_pq + f * ld_out + c, pack8(apq));
+  if (out_p != nullptr) stg16(out_p + f * ld_out + c, pack8(ap));
+}
+
+// ------------------------------------------------------------------------------------------------
+// gate forward (standalone Gate module / cond_gate): out = c[frame] * x (+ res)
+// gate backward, elementwise part: dy = dx * c[frame]; if T == 1 also dc = dx * y
+// Flat grid-stride over 16-byte groups.
+// ------------------------------------------------------------------------------------------------
+__global__ void gate_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ c, int64_t ld_c,
+                                const bf16* __restrict__ res, bf16* __restrict__ out, int64_t M, int d, int T) {
+  const int dv = d >> 3;
+  const int64_t total = M * dv;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t row = i / dv;
+    const int col = static_cast<int>(i - row * dv) * 8;
+    float fx[8], fc[8];
+    unpack8(ldg16(x + row * d + col), fx);
+    unpack8(ldg16(c + (row / T) * ld_c + col), fc);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) fx[j] *= fc[j];
+    if (res != nullptr) {
+      float fr[8];
+      unpack8(ldg16(res + row * d + col), fr);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) fx[j] += fr[j];
+    }
+    stg16(out + row * d + col, pack8(fx));
+  }
+}
+
+__global__ void gate_bwd_kernel(const bf16* __restrict__ dx, const bf16* __restrict__ y, const bf16* __restrict__ c,
+                                int64_t ld_c, bf16* __restrict__ dy, bf16* __restrict__ dc, int64_t ld_dc, int64_t M,
+                                int d, int T) {
+  const int dv = d >> 3;
+  const int64_t total = M * dv;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const bool write_dc = (T == 1) && (dc != nullptr);
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t row = i / dv;
+    const int col = static_cast<int>(i - row * dv) * 8;
+    float fd[8], fc[8], o[8];
+    unpack8(ldg16(dx + row * d + col), fd);
+    unpack8(ldg16(c + (row / T) * ld_c + col), fc);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fd[j] * fc[j];
+    stg16(dy + row * d + col, pack8(o));
+    if (write_dc) {
+      float fy[8];
+      unpack8(ldg16(y + row * d + col), fy);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fd[j] * fy[j];
+      stg16(dc + row * ld_dc + col, pack8(o));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// column sum: out[n] (+)= sum_m x[m, n].  Block = 32 column groups (256 columns) x 8 row lanes;
+// grid = (ceil(N/256), row_splits).  Partial sums meet in shared memory, then one fp32 atomic per
+// column per CTA (the output is zeroed by the launcher unless accumulating).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+colsum_kernel(const bf16* __restrict__ x, int64_t ld, float* __restrict__ out, int64_t M, int N) {
+  __shared__ float part[8][256 + 8];
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = (blockIdx.x * 32 + cg) * 8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c < N) {
+    for (int64_t r = static_cast<int64_t>(blockIdx.y) * 8 + rl; r < M; r += static_cast<int64_t>(gridDim.y) * 8) {
+      float f[8];
+      unpack8(ldg16(x + r * ld + c), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[rl][cg * 8 + j] = acc[j];
+  __syncthreads();
+  const int col = threadIdx.x;  // 256 threads -> 256 columns
+  if (blockIdx.x * 256 + col < N) {
+    float s = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) s += part[r][col];
+    atomicAdd(out + blockIdx.x * 256 + col, s);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// KV-cache append: copy [B,H,Ln,dh] rows into cache[B,H,cap,dh] at row `pos` (16-byte groups).
+// ------------------------------------------------------------------------------------------------
+__global__ void kv_append_kernel(const bf16* __restrict__ src, int64_t src_sb, int64_t src_sh,
+                                 bf16* __restrict__ cache, int64_t c_sb, int64_t c_sh, int64_t pos, int64_t B, int H,
+                                 int64_t Ln, int dh) {
+  const int64_t per_head = Ln * dh / 8;
+  const int64_t total = B * H * per_head;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t bh = i / per_head, e = (i - bh * per_head) * 8;
+    const int64_t b = bh / H, h = bh - b * H;
+    stg16(cache + b * c_sb + h * c_sh + pos * dh + e, ldg16(src + b * src_sb + h * src_sh + e));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// weight-less LayerNorm forward (normalization.py:6-7)
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(kRowThreads)
+layer_norm_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int64_t M, int d, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
+    uint4 xv[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        xv[i] = ldg16(x + row * d + c);
+        float f[8];
+        unpack8(xv[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += f[j];
+      }
+    }
+    const float mean = warp_sum(s) / static_cast<float>(d);
+    float v = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        float f[8];
+        unpack8(xv[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v += (f[j] - mean) * (f[j] - mean);
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(v) / static_cast<float>(d) + eps);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        float f[8];
+        unpack8(xv[i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = (f[j] - mean) * rstd;
+        stg16(y + row * d + c, pack8(f));
+      }
+    }
+  }
+}
+
+// NV dispatch: NV*256 >= d.  d up to 4096.
+#define OWL_DISPATCH_NV(d, ...)                         \
+  do {                                                  \
+    const int nv_ = ((d) + 255) / 256;                  \
+    if (nv_ <= 1) { constexpr int NV = 1; __VA_ARGS__; }        \
+    else if (nv_ <= 2) { constexpr int NV = 2; __VA_ARGS__; }   \
+    else if (nv_ <= 4) { constexpr int NV = 4; __VA_ARGS__; }   \
+    else if (nv_ <= 6) { constexpr int NV = 6; __VA_ARGS__; }   \
+    else if (nv_ <= 8) { constexpr int NV = 8; __VA_ARGS__; }   \
+    else if (nv_ <= 10) { constexpr int NV = 10; __VA_ARGS__; } \
+    else { constexpr int NV = 16; __VA_ARGS__; }                \
+  } while (0)
+
+static inline int row_grid(int64_t M) {
+  int64_t blocks = (M + (kRowThreads / 32) - 1) / (kRowThreads / 32);
+  const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+  if (blocks > cap) blocks = cap;
+  return static_cast<int>(blocks < 1 ? 1 : blocks);
+}
+
+}  // namespace owl
+
+using namespace owl;
+
+#define OWL_REQUIRE(cond, code) \
+  do {                          \
+    if (!(cond)) return (code); \
+  } while (0)
+
+extern "C" {
+
+int owl_cast_f32_bf16(const float* src, void* dst, int64_t n, owl_stream_t stream) {
+  OWL_REQUIRE(src && dst && n > 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(aligned16(src) && aligned16(dst), OWL_ERR_ALIGN);
+  cast_f32_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, static_cast<bf16*>(dst), n);
+  return launch_status();
+}
+
+int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream) {
+  OWL_REQUIRE(x && y && n > 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
+  silu_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(x), static_cast<bf16*>(y), n);
+  return launch_status();
+}
+
+int owl_adaln_modulate_fwd(const void* x, const void* a, const void* b, int64_t ld_ab, void* h, float* rstd,
+                           int64_t M, int64_t d, int64_t T, float eps, owl_stream_t stream) {
+  OWL_REQUIRE(x && h && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE((a == nullptr) == (b == nullptr), OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(x) && aligned16(h) && aligned16(a) && aligned16(b) && (a == nullptr || ld_ab % 8 == 0),
+              OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  OWL_DISPATCH_NV(d, (adaln_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
+                         static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
+                         static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps)));
+  return launch_status();
+}
+
+int owl_adaln_modulate_bwd(const void* dh, const void* x, const void* a, int64_t ld_ab, const float* rstd,
+                           const void* dres, void* dx, void* da, void* db, int64_t ld_dab, int64_t M, int64_t d,
+                           int64_t T, owl_stream_t stream) {
+  OWL_REQUIRE(dh && x && rstd && dx && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE((da == nullptr) == (db == nullptr), OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(dh) && aligned16(x) && aligned16(a) && aligned16(dres) && aligned16(dx) && aligned16(da) &&
+                  aligned16(db) && (a == nullptr || ld_ab % 8 == 0) && (da == nullptr || ld_dab % 8 == 0),
+              OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  OWL_DISPATCH_NV(d, (adaln_bwd_row_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
+                         static_cast<const bf16*>(dh), static_cast<const bf16*>(x), static_cast<const bf16*>(a), ld_ab,
+                         rstd, static_cast<const bf16*>(dres), static_cast<bf16*>(dx), static_cast<bf16*>(da),
+                         static_cast<bf16*>(db), ld_dab, M, static_cast<int>(d), static_cast<int>(T))));
+  int rc = launch_status();
+  if (rc != OWL_OK) return rc;
+  if (T > 1 && da != nullptr) {
+    dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
+    frame_reduce_kernel<<<grid, 64, 0, s>>>(static_cast<const bf16*>(dh), static_cast<const bf16*>(x), rstd,
+                                            static_cast<bf16*>(da), static_cast<bf16*>(db), ld_dab,
+                                            static_cast<int>(d), static_cast<int>(T));
+    rc = launch_status();
+  }
+  return rc;
+}
+
+int owl_gate_fwd(const void* x, const void* c, int64_t ld_c, const void* res, void* out, int64_t M, int64_t d,
+                 int64_t T, owl_stream_t stream) {
+  OWL_REQUIRE(x && c && out && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(x) && aligned16(c) && aligned16(res) && aligned16(out) && ld_c % 8 == 0, OWL_ERR_ALIGN);
+  gate_fwd_kernel<<<grid_for(M * (d / 8), 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(x), static_cast<const bf16*>(c), ld_c, static_cast<const bf16*>(res),
+      static_cast<bf16*>(out), M, static_cast<int>(d), static_cast<int>(T));
+  return launch_status();
+}
+
+int owl_colsum_bf16(const void* x, int64_t ld, float* out, int accumulate, int64_t M, int64_t N,
+                    owl_stream_t stream) {
+  OWL_REQUIRE(x && out && M > 0 && N > 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(N % 8 == 0, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(x) && ld % 8 == 0, OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (!accumulate) {
+    cudaError_t e = cudaMemsetAsync(out, 0, static_cast<size_t>(N) * sizeof(float), s);
+    if (e != cudaSuccess) return static_cast<int>(e);
+  }
+  const unsigned gx = static_cast<unsigned>((N + 255) / 256);
+  int64_t splits = (M + 63) / 64;  // >= 8 rows per row-lane
+  const int64_t cap = (static_cast<int64_t>(sm_count()) * 4 + gx - 1) / gx;
+  if (splits > cap) splits = cap;
+  if (splits < 1) splits = 1;
+  colsum_kernel<<<dim3(gx, static_cast<unsigned>(splits)), 256, 0, s>>>(static_cast<const bf16*>(x), ld, out, M,
+                                                                         static_cast<int>(N));
+  return launch_status();
+}
+
+int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, void* dy, void* dc, int64_t ld_dc,
+                 float* dbias, int dbias_accumulate, int64_t M, int64_t d, int64_t T, owl_stream_t stream) {
+  OWL_REQUIRE(dx && c && dy && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(dc == nullptr || y != nullptr, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(dx) && aligned16(y) && aligned16(c) && aligned16(dy) && aligned16(dc) && ld_c % 8 == 0 &&
+                  (dc == nullptr || ld_dc % 8 == 0),
+              OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  gate_bwd_kernel<<<grid_for(M * (d / 8), 256), 256, 0, s>>>(
+      static_cast<const bf16*>(dx), static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c,
+      static_cast<bf16*>(dy), static_cast<bf16*>(dc), ld_dc, M, static_cast<int>(d), static_cast<int>(T));
+  int rc = launch_status();
+  if (rc != OWL_OK) return rc;
+  if (T > 1 && dc != nullptr) {
+    dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
+    frame_reduce_kernel<<<grid, 64, 0, s>>>(static_cast<const bf16*>(dx), static_cast<const bf16*>(y), nullptr,
+                                            static_cast<bf16*>(dc), nullptr, ld_dc, static_cast<int>(d),
+                                            static_cast<int>(T));
+    rc = launch_status();
+    if (rc != OWL_OK) return rc;
+  }
+  if (dbias != nullptr) rc = owl_colsum_bf16(dy, d, dbias, dbias_accumulate, M, d, stream);
+  return rc;
+}
+
+int owl_kv_append(const void* src, int64_t src_sb, int64_t src_sh, void* cache, int64_t cache_sb, int64_t cache_sh,
+                  int64_t pos, int64_t B, int64_t H, int64_t Ln, int64_t dh, owl_stream_t stream) {
+  OWL_REQUIRE(src && cache && B > 0 && H > 0 && Ln > 0 && dh > 0 && pos >= 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(dh % 8 == 0, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(src) && aligned16(cache) && src_sb % 8 == 0 && src_sh % 8 == 0 && cache_sb % 8 == 0 &&
+                  cache_sh % 8 == 0,
+              OWL_ERR_ALIGN);
+  kv_append_kernel<<<grid_for(B * H * Ln * dh / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(src), src_sb, src_sh, static_cast<bf16*>(cache), cache_sb, cache_sh, pos, B,
+      static_cast<int>(H), Ln, static_cast<int>(dh));
+  return launch_status();
+}
+
+int owl_layer_norm_fwd(const void* x, void* y, int64_t M, int64_t d, float eps, owl_stream_t stream) {
+  OWL_REQUIRE(x && y && M > 0 && d > 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  OWL_DISPATCH_NV(d, (layer_norm_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
+                         static_cast<const bf16*>(x), static_cast<bf16*>(y), M, static_cast<int>(d), eps)));
+  return launch_status();
+}
+
+}  // extern "C"

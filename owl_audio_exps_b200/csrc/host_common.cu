@@ -1,0 +1,93 @@
+// Host-side helpers shared by the C-ABI launchers (see host_common.h).
+#include "host_common.h"
+
+#include <atomic>
+#include <mutex>
+
+namespace owl {
+
+std::atomic<uint64_t> g_launches{0};
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encode() {
+  static encode_tiled_fn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<encode_tiled_fn>(p);
+    (void)cudaGetLastError();
+  });
+  return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                      uint32_t box_cols, uint32_t box_rows) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) return OWL_ERR_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld_elems * 2) % 16) return OWL_ERR_ALIGN;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
+}
+
+int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t s1_elems,
+                      uint64_t s2_elems, uint32_t b0, uint32_t b1) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) return OWL_ERR_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (s1_elems * 2) % 16 || (s2_elems * 2) % 16) return OWL_ERR_ALIGN;
+  cuuint64_t dims[3] = {n0, n1, n2};
+  cuuint64_t strides[2] = {s1_elems * 2, s2_elems * 2};
+  cuuint32_t box[3] = {b0, b1, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
+}
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      n = v;
+    else
+      n = 148;
+    (void)cudaGetLastError();
+  }
+  return n;
+}
+
+}  // namespace owl
+
+extern "C" {
+
+int owl_abi_version(void) { return 1; }
+
+const char* owl_error_string(int code) {
+  switch (code) {
+    case OWL_OK: return "ok";
+    case OWL_ERR_BAD_ARG: return "bad argument (null pointer, non-positive or inconsistent size)";
+    case OWL_ERR_ALIGN: return "pointer or leading dimension not 16-byte aligned";
+    case OWL_ERR_UNSUPPORTED: return "shape not supported by the sm_100a kernels";
+    case OWL_ERR_DRIVER: return "CUDA driver entry point / tensor-map encoding failed";
+    default: break;
+  }
+  if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));
+  return "unknown error";
+}
+
+uint64_t owl_launch_count(void) { return owl::g_launches.load(); }
+
+}  // extern "C"

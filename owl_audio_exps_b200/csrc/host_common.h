@@ -1,0 +1,38 @@
+// Host-side helpers shared by the C-ABI launchers: error codes, TMA tensor-map encoding
+// (through the driver entry point, so the library has no link-time dependency on libcuda),
+// device properties cache.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+
+#include "../../include/owl_dit.h"
+
+namespace owl {
+
+// 2-D bf16 row-major tensor [rows, cols] with leading dimension ld (elements); box = {box_cols, box_rows},
+// 128-byte swizzle (box_cols * 2 bytes must be <= 128).
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                      uint32_t box_cols, uint32_t box_rows);
+
+// 3-D bf16 tensor [n2, n1, n0] (n0 contiguous) with element strides s1, s2; box {b0, b1, 1}; 128B swizzle.
+int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t s1_elems,
+                      uint64_t s2_elems, uint32_t b0, uint32_t b1);
+
+int sm_count();
+
+extern std::atomic<uint64_t> g_launches;
+
+// Call right after a <<<>>> launch: counts it (owl_launch_count) and maps the launch error to the ABI code.
+inline int launch_status(int n = 1) {
+  g_launches.fetch_add(static_cast<uint64_t>(n), std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? OWL_OK : static_cast<int>(e);
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace owl
