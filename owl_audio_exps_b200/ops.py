@@ -1,0 +1,268 @@
+"""Tensor-level wrappers over the C ABI (include/owl_dit.h).
+
+PyTorch is plumbing here: it owns device memory and the stream; every function below only passes
+raw device pointers, sizes and the current CUDA stream to libowl_dit.so.  All outputs/workspaces
+are allocated by the caller side (here) -- the library never allocates.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import (OWL_EPI_BIAS_SILU, OWL_EPI_DSILU, OWL_EPI_F32, OWL_EPI_GATE_RESIDUAL, OWL_EPI_STORE,
+                   OWL_GEMM_NN, OWL_GEMM_NT, OWL_GEMM_TN, AttnMask, GemmEpilogue)
+
+bf16 = torch.bfloat16
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _req(t: torch.Tensor, dtype=bf16):
+    if not t.is_cuda:
+        raise RuntimeError("owl ops need CUDA tensors: there is no CPU fallback")
+    if t.dtype != dtype:
+        raise RuntimeError(f"expected {dtype}, got {t.dtype}")
+
+
+def _rows(t: torch.Tensor):
+    """2-D view info of a tensor whose last dim is contiguous and leading dims are collapsible."""
+    if t.stride(-1) != 1:
+        raise RuntimeError("last dim must be contiguous")
+    if t.dim() == 1:
+        return 1, t.shape[0], t.shape[0]
+    if t.dim() > 2:
+        t = t.reshape(-1, t.shape[-1]) if t.is_contiguous() else t.flatten(0, -2)
+    return t.shape[0], t.shape[1], t.stride(0)
+
+
+def launch_count() -> int:
+    return int(_lib.load().owl_launch_count())
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM
+# ------------------------------------------------------------------------------------------------
+def gemm(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, mode: int = OWL_EPI_STORE,
+         bias: Optional[torch.Tensor] = None, out0: Optional[torch.Tensor] = None,
+         out1: Optional[torch.Tensor] = None, outf: Optional[torch.Tensor] = None,
+         aux0: Optional[torch.Tensor] = None, aux1: Optional[torch.Tensor] = None, rows_per_frame: int = 1,
+         accumulate: bool = False) -> None:
+    """C[M,N] = opA . opB with a fused epilogue; a/b are 2-D bf16 (row stride = leading dimension)."""
+    lib = _lib.load()
+    _req(a), _req(b)
+    e = GemmEpilogue()
+    e.mode, e.accumulate, e.rows_per_frame = mode, int(accumulate), rows_per_frame
+    if bias is not None:
+        _req(bias, torch.float32)
+        e.bias = bias.data_ptr()
+    for name, ldname, t, dt in (("out0", "ld0", out0, bf16), ("out1", "ld1", out1, bf16),
+                                ("outf", "ldf", outf, torch.float32), ("aux0", "lda0", aux0, bf16),
+                                ("aux1", "lda1", aux1, bf16)):
+        if t is not None:
+            _req(t, dt)
+            setattr(e, name, t.data_ptr())
+            setattr(e, ldname, _rows(t)[2])
+    rc = lib.owl_gemm_bf16(layout, M, N, K, a.data_ptr(), _rows(a)[2], b.data_ptr(), _rows(b)[2], C.byref(e), _stream())
+    _lib.check(rc, "owl_gemm_bf16")
+
+
+def gemm_check(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int) -> torch.Tensor:
+    lib = _lib.load()
+    c = torch.empty(M, N, device=a.device, dtype=torch.float32)
+    rc = lib.owl_gemm_bf16_check(layout, M, N, K, a.data_ptr(), _rows(a)[2], b.data_ptr(), _rows(b)[2], c.data_ptr(), N,
+                                 _stream())
+    _lib.check(rc, "owl_gemm_bf16_check")
+    return c
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = x w^T + bias, x [..., K] bf16, w [N, K] bf16, bias fp32."""
+    M, K, _ = _rows(x)
+    N = w.shape[0]
+    y = torch.empty(*x.shape[:-1], N, device=x.device, dtype=bf16)
+    gemm(OWL_GEMM_NT, x, w, M, N, K, mode=OWL_EPI_STORE, bias=bias, out0=y)
+    return y
+
+
+# ------------------------------------------------------------------------------------------------
+# memory-bound ops
+# ------------------------------------------------------------------------------------------------
+def cast_f32_bf16(src: torch.Tensor, dst: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _req(src, torch.float32)
+    if dst is None:
+        dst = torch.empty(src.shape, device=src.device, dtype=bf16)
+    _lib.check(_lib.load().owl_cast_f32_bf16(src.data_ptr(), dst.data_ptr(), src.numel(), _stream()), "owl_cast_f32_bf16")
+    return dst
+
+
+def silu(x: torch.Tensor) -> torch.Tensor:
+    _req(x)
+    y = torch.empty_like(x)
+    _lib.check(_lib.load().owl_silu_bf16(x.data_ptr(), y.data_ptr(), x.numel(), _stream()), "owl_silu_bf16")
+    return y
+
+
+def adaln_modulate_fwd(x, a, b, T: int, eps: float, want_rstd: bool = True):
+    """h = rms_norm(x) * (1 + a[frame]) + b[frame]; x [M,d]; a,b [M/T,d] column slices (or None)."""
+    _req(x)
+    M, d, _ = _rows(x)
+    h = torch.empty_like(x)
+    rstd = torch.empty(M, device=x.device, dtype=torch.float32) if want_rstd else None
+    ld_ab = _rows(a)[2] if a is not None else 0
+    rc = _lib.load().owl_adaln_modulate_fwd(x.data_ptr(), _p(a), _p(b), ld_ab, h.data_ptr(), _p(rstd), M, d, T, eps,
+                                            _stream())
+    _lib.check(rc, "owl_adaln_modulate_fwd")
+    return h, rstd
+
+
+def adaln_modulate_bwd(dh, x, a, rstd, dres, da, db, T: int):
+    """Returns dx; writes da, db (views with a row stride) in place."""
+    M, d, _ = _rows(x)
+    dx = torch.empty_like(x)
+    ld_ab = _rows(a)[2] if a is not None else 0
+    ld_dab = _rows(da)[2] if da is not None else 0
+    rc = _lib.load().owl_adaln_modulate_bwd(dh.data_ptr(), x.data_ptr(), _p(a), ld_ab, rstd.data_ptr(), _p(dres),
+                                            dx.data_ptr(), _p(da), _p(db), ld_dab, M, d, T, _stream())
+    _lib.check(rc, "owl_adaln_modulate_bwd")
+    return dx
+
+
+def gate_fwd(x, c, res, T: int):
+    M, d, _ = _rows(x)
+    out = torch.empty_like(x)
+    rc = _lib.load().owl_gate_fwd(x.data_ptr(), c.data_ptr(), _rows(c)[2], _p(res), out.data_ptr(), M, d, T, _stream())
+    _lib.check(rc, "owl_gate_fwd")
+    return out
+
+
+def gate_bwd(dx, y, c, dc, dbias, T: int, dbias_accumulate: bool = False):
+    """dy = dx * c[frame]; dc[frame] = sum dx*y (written in place); dbias (+)= colsum(dy)."""
+    M, d, _ = _rows(dx)
+    dy = torch.empty_like(dx)
+    rc = _lib.load().owl_gate_bwd(dx.data_ptr(), _p(y), c.data_ptr(), _rows(c)[2], dy.data_ptr(), _p(dc),
+                                  _rows(dc)[2] if dc is not None else 0, _p(dbias), int(dbias_accumulate), M, d, T,
+                                  _stream())
+    _lib.check(rc, "owl_gate_bwd")
+    return dy
+
+
+def colsum(x, out, accumulate: bool = False):
+    M, N, ld = _rows(x)
+    _lib.check(_lib.load().owl_colsum_bf16(x.data_ptr(), ld, out.data_ptr(), int(accumulate), M, N, _stream()),
+               "owl_colsum_bf16")
+    return out
+
+
+def layer_norm(x, eps: float = 1e-5):
+    M, d, _ = _rows(x)
+    y = torch.empty_like(x)
+    _lib.check(_lib.load().owl_layer_norm_fwd(x.data_ptr(), y.data_ptr(), M, d, eps, _stream()), "owl_layer_norm_fwd")
+    return y
+
+
+def qk_norm_rope_fwd(qkv, cos, sin, pos_offset: int, H: int, eps: float, q, k, v, want_rstd: bool = True):
+    """qkv [B,L,3*H*dh] -> q,k,v written into caller views [B,H,L,dh] (dh contiguous, L stride dh)."""
+    B, L, three_d = qkv.shape
+    dh = three_d // (3 * H)
+    for t in (q, k, v):
+        assert t.stride(3) == 1 and t.stride(2) == dh, "head-major views need contiguous [L, dh] rows"
+    rq = torch.empty(B, H, L, device=qkv.device, dtype=torch.float32) if want_rstd else None
+    rk = torch.empty(B, H, L, device=qkv.device, dtype=torch.float32) if want_rstd else None
+    rc = _lib.load().owl_qk_norm_rope_fwd(qkv.data_ptr(), cos.data_ptr(), sin.data_ptr(), pos_offset, q.data_ptr(),
+                                          q.stride(0), q.stride(1), k.data_ptr(), k.stride(0), k.stride(1),
+                                          v.data_ptr(), v.stride(0), v.stride(1), _p(rq), _p(rk), B, L, H, dh, eps,
+                                          _stream())
+    _lib.check(rc, "owl_qk_norm_rope_fwd")
+    return rq, rk
+
+
+def qk_norm_rope_bwd(dq, dk, dv, q, k, rq, rk, cos, sin, pos_offset: int):
+    """dq/dk/dv share strides ([B,H,L,dh]); returns dqkv [B,L,3*H*dh]."""
+    B, H, L, dh = dq.shape
+    assert dq.stride() == dk.stride() == dv.stride()
+    dqkv = torch.empty(B, L, 3 * H * dh, device=dq.device, dtype=bf16)
+    rc = _lib.load().owl_qk_norm_rope_bwd(dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), dq.stride(0), dq.stride(1),
+                                          q.data_ptr(), q.stride(0), q.stride(1), k.data_ptr(), k.stride(0),
+                                          k.stride(1), rq.data_ptr(), rk.data_ptr(), cos.data_ptr(), sin.data_ptr(),
+                                          pos_offset, dqkv.data_ptr(), B, L, H, dh, _stream())
+    _lib.check(rc, "owl_qk_norm_rope_bwd")
+    return dqkv
+
+
+def kv_append(src, cache, pos: int):
+    B, H, Ln, dh = src.shape
+    rc = _lib.load().owl_kv_append(src.data_ptr(), src.stride(0), src.stride(1), cache.data_ptr(), cache.stride(0),
+                                   cache.stride(1), pos, B, H, Ln, dh, _stream())
+    _lib.check(rc, "owl_kv_append")
+
+
+# ------------------------------------------------------------------------------------------------
+# attention
+# ------------------------------------------------------------------------------------------------
+def _mask(tokens_per_frame: int, window_frames: int, q_offset: int, causal: bool, doc_id) -> AttnMask:
+    m = AttnMask()
+    m.tokens_per_frame, m.window_frames, m.q_offset, m.causal = tokens_per_frame, window_frames, q_offset, int(causal)
+    if doc_id is not None:
+        _req(doc_id, torch.int32)
+        m.doc_id, m.doc_ld = doc_id.data_ptr(), doc_id.stride(0)
+    return m
+
+
+def _hm(t: torch.Tensor):
+    """[B,H,L,dh] head-major view: dh contiguous, row stride dh; returns (ptr, batch stride, head stride)."""
+    _req(t)
+    if t.stride(3) != 1 or (t.shape[2] > 1 and t.stride(2) != t.shape[3]):
+        raise RuntimeError("head-major tensors need contiguous [L, dh] rows")
+    return t.data_ptr(), t.stride(0), t.stride(1)
+
+
+def attn_fwd(q, k, v, *, tokens_per_frame: int, window_frames: int = 0, q_offset: int = 0, causal: bool = True,
+             doc_id=None, want_lse: bool = True, check: bool = False):
+    """q [B,H,Lq,dh], k/v [B,H,Lk,dh] -> o [B,Lq,H*dh] (token-major, ready for the out Linear), lse [B,H,Lq]."""
+    lib = _lib.load()
+    B, H, Lq, dh = q.shape
+    Lk = k.shape[2]
+    o = torch.empty(B, Lq, H * dh, device=q.device, dtype=bf16)
+    lse = torch.empty(B, H, Lq, device=q.device, dtype=torch.float32) if want_lse else None
+    m = _mask(tokens_per_frame, window_frames, q_offset, causal, doc_id)
+    fn = lib.owl_attn_fwd_check if check else lib.owl_attn_fwd
+    rc = fn(*_hm(q), *_hm(k), *_hm(v), o.data_ptr(), o.stride(0), o.stride(1), _p(lse), B, H, Lq, Lk, dh, C.byref(m),
+            _stream())
+    _lib.check(rc, "owl_attn_fwd")
+    return o, lse
+
+
+def attn_bwd(dout, o, q, k, v, lse, *, tokens_per_frame: int, window_frames: int = 0, q_offset: int = 0,
+             causal: bool = True, doc_id=None, check: bool = False, dq=None, dk=None, dv=None):
+    """Returns (dq, dk, dv) in [B,H,L,dh]."""
+    lib = _lib.load()
+    B, H, Lq, dh = q.shape
+    Lk = k.shape[2]
+    _req(dout), _req(o)
+    if dout.stride() != o.stride():
+        dout = dout.contiguous()
+    dq = torch.empty(B, H, Lq, dh, device=q.device, dtype=bf16) if dq is None else dq
+    dk = torch.empty(B, H, Lk, dh, device=q.device, dtype=bf16) if dk is None else dk
+    dv = torch.empty(B, H, Lk, dh, device=q.device, dtype=bf16) if dv is None else dv
+    delta = torch.empty(B, H, Lq, device=q.device, dtype=torch.float32)
+    dq_acc = None if check else torch.empty(attn_bwd_workspace_elems(B, H, Lq, dh), device=q.device, dtype=torch.float32)
+    m = _mask(tokens_per_frame, window_frames, q_offset, causal, doc_id)
+    fn = lib.owl_attn_bwd_check if check else lib.owl_attn_bwd
+    rc = fn(dout.data_ptr(), o.data_ptr(), o.stride(0), o.stride(1), *_hm(q), *_hm(k), *_hm(v), lse.data_ptr(),
+            delta.data_ptr(), _p(dq_acc), *_hm(dq), *_hm(dk), *_hm(dv), B, H, Lq, Lk, dh, C.byref(m), _stream())
+    _lib.check(rc, "owl_attn_bwd")
+    return dq, dk, dv
+
+
+def attn_bwd_workspace_elems(B: int, H: int, Lq: int, dh: int) -> int:
+    """fp32 elements of the dq accumulator workspace owl_attn_bwd needs (query rows padded to 128)."""
+    return B * H * ((Lq + 127) // 128 * 128) * dh

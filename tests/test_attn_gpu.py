@@ -1,0 +1,100 @@
+"""Attention kernels against torch SDPA with the dense mask of attn.py:43-59 (fp32 math on the same
+bf16 inputs).  Covers T=1/64/65, windows, q_offset (KV prefix), non-causal, doc ids, dh 64/128.
+Bar: max|out-ref|/max|ref| <= 1e-2 forward, 2e-2 gradients (north_star tolerance)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+bf16 = torch.bfloat16
+
+
+def _ops():
+    from owl_audio_exps_b200 import ops
+    return ops
+
+
+def relerr(a, b):
+    return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-20)).item()
+
+
+def dense_mask(Lq, Lk, T, W, q_offset, causal, doc, dev):
+    qi = torch.arange(Lq, device=dev)[:, None] + q_offset
+    kj = torch.arange(Lk, device=dev)[None, :]
+    fq, fk = qi // T, kj // T
+    m = torch.ones(Lq, Lk, dtype=torch.bool, device=dev)
+    if causal:
+        m &= fk <= fq
+    if W > 0:
+        m &= (fq - fk).abs() < W
+    m = m[None].clone()
+    if doc is not None:
+        m = m & (doc[:, fq.squeeze(1)][:, :, None] == doc[:, fk.squeeze(0)][:, None, :])
+    return m[:, None]  # [B or 1, 1, Lq, Lk]
+
+
+CASES = [
+    # B, H, Lq, Lk, dh, T, W, causal, doc
+    (2, 4, 120, 120, 64, 1, 16, True, False),
+    (2, 4, 120, 120, 64, 1, 0, True, False),
+    (1, 3, 1040, 1040, 64, 65, 0, True, False),
+    (1, 3, 1040, 1040, 64, 65, 4, True, False),
+    (1, 2, 2048, 2048, 64, 64, 8, True, True),
+    (1, 2, 1024, 1024, 128, 64, 0, True, False),
+    (1, 2, 65, 65 * 7, 64, 65, 0, False, False),       # decode mode: block_mask None, all keys visible
+    (1, 2, 130, 65 * 5, 64, 65, 3, True, False),       # cached, masked path with q_offset
+    (2, 2, 520, 520, 64, 65, 3, False, False),         # bidirectional window
+    (1, 2, 300, 300, 128, 1, 16, True, False),
+]
+
+
+def _inputs(case, dev):
+    B, H, Lq, Lk, dh, T, W, causal, use_doc = case
+    g = torch.Generator(device="cpu").manual_seed(Lq + Lk + dh)
+    q = torch.randn(B, H, Lq, dh, generator=g).to(bf16).to(dev)
+    k = torch.randn(B, H, Lk, dh, generator=g).to(bf16).to(dev)
+    v = torch.randn(B, H, Lk, dh, generator=g).to(bf16).to(dev)
+    doc = None
+    if use_doc:
+        nF = (Lk + T - 1) // T
+        doc = (torch.arange(nF)[None] // 11).repeat(B, 1).to(torch.int32).to(dev)
+    return q, k, v, doc
+
+
+def _reference(q, k, v, mask, dout):
+    qf, kf, vf = (t.float().requires_grad_(True) for t in (q, k, v))
+    s = (qf @ kf.transpose(-1, -2)) / math.sqrt(q.shape[-1])
+    s = s.masked_fill(~mask, float("-inf"))
+    p = torch.softmax(s, -1)
+    o = p @ vf
+    lse = torch.logsumexp(s, -1)
+    o_tm = o.permute(0, 2, 1, 3).reshape(q.shape[0], q.shape[2], -1)
+    o_tm.backward(dout.float())
+    return o_tm, lse, qf.grad, kf.grad, vf.grad
+
+
+@pytest.mark.parametrize("impl", ["check", "tcgen05"])
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "-".join(str(x) for x in c))
+def test_attn_fwd_bwd(case, impl):
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    B, H, Lq, Lk, dh, T, W, causal, use_doc = case
+    q_offset = Lk - Lq if causal else 0
+    if not causal and Lk != Lq:
+        q_offset = Lk - Lq
+    q, k, v, doc = _inputs(case, dev)
+    mask = dense_mask(Lq, Lk, T, W, q_offset, causal, doc, dev)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    dout = torch.randn(B, Lq, H * dh, generator=g).to(bf16).to(dev)
+    o_ref, lse_ref, dq_ref, dk_ref, dv_ref = _reference(q, k, v, mask, dout)
+    kw = dict(tokens_per_frame=T, window_frames=W, q_offset=q_offset, causal=causal, doc_id=doc, check=impl == "check")
+    o, lse = ops.attn_fwd(q, k, v, **kw)
+    torch.cuda.synchronize()
+    assert relerr(o, o_ref) <= 1e-2
+    assert (lse - lse_ref).abs().max().item() <= 2e-2
+    dq, dk, dv = ops.attn_bwd(dout, o, q, k, v, lse, **kw)
+    torch.cuda.synchronize()
+    assert relerr(dq, dq_ref) <= 2e-2
+    assert relerr(dk, dk_ref) <= 2e-2
+    assert relerr(dv, dv_ref) <= 2e-2

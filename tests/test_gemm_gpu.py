@@ -1,0 +1,129 @@
+"""tcgen05 GEMM (owl_gemm_bf16) against a torch fp32 reference and the CUDA-core check kernel.
+
+Tolerance: operands are bf16 (exact in fp32), accumulation fp32, so the only error of a bf16
+output is its final rounding: |err| <= 2^-8 * |ref| + accumulation-order noise.  Stated bar:
+max|out - ref| / max|ref| <= 1e-2 for bf16 outputs, 1e-4 for fp32 outputs.
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+bf16 = torch.bfloat16
+
+
+def _ops():
+    from owl_audio_exps_b200 import ops
+    return ops
+
+
+def relerr(a, b):
+    return ((a.float() - b.float()).abs().max() / b.float().abs().max().clamp_min(1e-20)).item()
+
+
+def _operands(layout, M, N, K, dev):
+    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K + layout)
+    A = torch.randn(M, K, generator=g).to(bf16)
+    Bm = torch.randn(N, K, generator=g).to(bf16)
+    ref = A.float() @ Bm.float().t()
+    a = A if layout != 2 else A.t().contiguous()          # TN: A stored [K, M]
+    b = Bm if layout == 0 else Bm.t().contiguous()        # NN/TN: B stored [K, N]
+    return a.to(dev), b.to(dev), ref.to(dev)
+
+
+SHAPES = [
+    (128, 128, 64), (128, 256, 128), (256, 512, 1024), (120, 1024, 1024), (3840, 3072, 1024),
+    (3840, 1024, 4096), (200, 72, 136), (1, 64, 64), (65, 1536, 1536), (1000, 2048, 520),
+]
+
+
+@pytest.mark.parametrize("layout", [0, 1, 2])
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_store(layout, M, N, K):
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    if layout == 2 and M % 8:
+        pytest.skip("TN needs lda = M multiple of 8")
+    a, b, ref = _operands(layout, M, N, K, dev)
+    out = torch.empty(M, N, device=dev, dtype=bf16)
+    ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_STORE, out0=out)
+    torch.cuda.synchronize()
+    assert relerr(out, ref) <= 1e-2
+    chk = ops.gemm_check(layout, a, b, M, N, K)
+    assert relerr(chk, ref) <= 1e-4
+
+
+@pytest.mark.parametrize("layout", [0, 2])
+@pytest.mark.parametrize("M,N,K", [(1024, 1024, 3840), (3072, 1024, 3840), (256, 128, 98304), (1024, 4096, 120)])
+def test_gemm_f32_splitk_and_accumulate(layout, M, N, K):
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    a, b, ref = _operands(layout, M, N, K, dev)
+    out = torch.full((M, N), 7.0, device=dev, dtype=torch.float32)
+    ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_F32, outf=out)
+    assert relerr(out, ref) <= 1e-4
+    ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_F32, outf=out, accumulate=True)
+    assert relerr(out, 2 * ref) <= 1e-4
+
+
+def test_gemm_bias_silu():
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    M, N, K = 3840, 4096, 1024
+    a, b, ref = _operands(0, M, N, K, dev)
+    ref = ref / 32
+    a = (a.float() / 32).to(bf16)  # exact power-of-two scaling
+    bias = torch.randn(N, device=dev)
+    z = torch.empty(M, N, device=dev, dtype=bf16)
+    s = torch.empty(M, N, device=dev, dtype=bf16)
+    ops.gemm(0, a, b, M, N, K, mode=ops.OWL_EPI_BIAS_SILU, bias=bias, out0=z, out1=s)
+    zr = (ref + bias).to(bf16)
+    assert relerr(z, zr) <= 1e-2
+    assert relerr(s, torch.nn.functional.silu(zr.float())) <= 1e-2
+
+
+@pytest.mark.parametrize("T", [1, 64, 65])
+def test_gemm_gate_residual(T):
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    F_, N, K = 24, 1536, 1536
+    M = F_ * T
+    a, b, ref = _operands(0, M, N, K, dev)
+    ref = ref / 32
+    a = (a.float() / 32).to(bf16)
+    bias = torch.randn(N, device=dev)
+    res = torch.randn(M, N, device=dev).to(bf16)
+    gate = torch.randn(F_, N, device=dev).to(bf16)
+    out = torch.empty(M, N, device=dev, dtype=bf16)
+    y = torch.empty(M, N, device=dev, dtype=bf16)
+    ops.gemm(0, a, b, M, N, K, mode=ops.OWL_EPI_GATE_RESIDUAL, bias=bias, out0=out, out1=y, aux0=res, aux1=gate,
+             rows_per_frame=T)
+    yr = (ref + bias).to(bf16)
+    expect = res.float() + gate.float().repeat_interleave(T, 0) * yr.float()
+    assert relerr(y, yr) <= 1e-2
+    assert relerr(out, expect) <= 1e-2
+
+
+def test_gemm_dsilu():
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    M, N, K = 1024, 4096, 1024
+    a, b, ref = _operands(1, M, N, K, dev)
+    z = torch.randn(M, N, device=dev).to(bf16)
+    out = torch.empty(M, N, device=dev, dtype=bf16)
+    ops.gemm(1, a, b, M, N, K, mode=ops.OWL_EPI_DSILU, out0=out, aux0=z)
+    zf = z.float()
+    sg = torch.sigmoid(zf)
+    expect = ref * (sg * (1 + zf * (1 - sg)))
+    assert relerr(out, expect) <= 1e-2
+
+
+def test_gemm_rejects_bad_args():
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    a = torch.zeros(128, 64, device=dev, dtype=bf16)
+    b = torch.zeros(128, 64, device=dev, dtype=bf16)
+    with pytest.raises(RuntimeError):
+        ops.gemm(0, a, b, 128, 128, 64, mode=ops.OWL_EPI_STORE)  # no output
+    with pytest.raises(RuntimeError):
+        ops.gemm(0, a[:, 1:], b, 128, 128, 56, mode=ops.OWL_EPI_STORE, out0=torch.empty(128, 128, device=dev, dtype=bf16))
