@@ -55,6 +55,25 @@ int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t 
   return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
 }
 
+int make_tmap_4d_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_t rows, uint64_t H, uint64_t B,
+                      uint64_t row_stride, uint64_t sh_elems, uint64_t sb_elems, uint32_t box_cols, uint32_t box_rows) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) return OWL_ERR_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (row_stride * 2) % 16 || (sh_elems * 2) % 16 || (sb_elems * 2) % 16)
+    return OWL_ERR_ALIGN;
+  // a size-1 dimension may carry any stride; the driver still wants it to be a non-zero multiple of 16 bytes
+  if (sh_elems == 0) sh_elems = rows * row_stride;
+  if (sb_elems == 0) sb_elems = H * sh_elems;
+  cuuint64_t dims[4] = {cols, rows, H, B};
+  cuuint64_t strides[3] = {row_stride * 2, sh_elems * 2, sb_elems * 2};
+  cuuint32_t box[4] = {box_cols, box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
+}
+
 int sm_count() {
   static int n = 0;
   if (n == 0) {

@@ -22,6 +22,11 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t s1_elems,
                       uint64_t s2_elems, uint32_t b0, uint32_t b1);
 
+// 4-D bf16 head-major tensor (b, h, row, col): dims {cols, rows, H, B}, row stride = cols (contiguous rows),
+// head / batch strides in elements; box {box_cols, box_rows, 1, 1}; 128B swizzle; out-of-bounds rows read as 0.
+int make_tmap_4d_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_t rows, uint64_t H, uint64_t B,
+                      uint64_t row_stride, uint64_t sh_elems, uint64_t sb_elems, uint32_t box_cols, uint32_t box_rows);
+
 int sm_count();
 
 extern std::atomic<uint64_t> g_launches;
