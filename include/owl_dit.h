@@ -112,6 +112,10 @@ int owl_cast_f32_bf16(const float* src, void* dst, int64_t n, owl_stream_t strea
 /* y = silu(x), bf16, n elements                                    (modulation.py:17,38)         */
 int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream);
 
+/* dz = dy * silu'(z), bf16, n elements: autograd of F.silu where it is not fused into a GEMM
+ * epilogue (attn.py:274 FinalLayer.act; standalone MLP)                                           */
+int owl_dsilu_mul_bf16(const void* dy, const void* z, void* dz, int64_t n, owl_stream_t stream);
+
 /* adaLN modulate forward                                           (modulation.py:20-25,
  *                                                                   normalization.py:10-11)
  *   h[m,:] = rms_norm(x[m,:]) * (1 + a[m / T,:]) + b[m / T,:]
@@ -166,6 +170,12 @@ int owl_qk_norm_rope_bwd(const void* dq, const void* dk, const void* dv, int64_t
                          const float* rstd_q, const float* rstd_k, const float* cos_tab, const float* sin_tab,
                          int64_t pos_offset, void* dqkv, int64_t B, int64_t L, int64_t H, int64_t dh,
                          owl_stream_t stream);
+
+/* Bare RoPE on contiguous rows x [R, L, dh] (R = B*H): RoPE.forward on its own     (rope.py:43-51)
+ *   inverse == 0: pairs (2i, 2i+1) -> [y_even | y_odd] halves;  inverse != 0: the transposed
+ *   rotation from halves back to pairs (the autograd of the former).  dh % 8 == 0.                */
+int owl_rope_apply(const void* x, const float* cos_tab, const float* sin_tab, int64_t pos_offset, void* y, int64_t R,
+                   int64_t L, int64_t dh, int inverse, owl_stream_t stream);
 
 /* KV-cache append                                                   (attn.py:92-99, kv_cache.py:50-58)
  * Copies new rows src [B,H,Ln,dh] (strides src_sb, src_sh) into cache [B,H,cap,dh] at row `pos`.

@@ -1,6 +1,23 @@
 """owl_audio_exps_b200: B200-native (sm_100a) implementation of the owl_wms DiT-block hot path.
 
 Layout: csrc/ (CUDA kernels + C ABI, built into libowl_dit.so), _lib.py (ctypes binding), ops.py
-(tensor-level wrappers), nn/ (drop-in mirror of owl_wms/nn), engine.py (data-parallel step).
+(tensor-level wrappers), functional.py (autograd schedule of the block), nn/ (drop-in mirror of
+owl_wms/nn), engine.py (data-parallel step: flat gradient buckets, overlapped NCCL all-reduce, CUDA graphs).
 """
+import sys
+
 __version__ = "0.1.0"
+
+_NN_MODULES = ("attn", "kv_cache", "mlp", "modulation", "normalization", "rope")
+
+
+def install(package: str = "owl_wms"):
+    """Make `<package>.nn.{attn,kv_cache,mlp,modulation,normalization,rope}` resolve to this
+    implementation, so the reference's models / samplers / trainers / inference pipeline (which do
+    `from ..nn.attn import DiT, FinalLayer`, `from ..nn.kv_cache import KVCache`, ...) pick up the
+    sm_100a path without any edit.  Call before importing `<package>.models`.  See INTEGRATION.md."""
+    from . import nn as _nn
+    sys.modules[f"{package}.nn"] = sys.modules.get(f"{package}.nn", _nn)
+    for name in _NN_MODULES:
+        sys.modules[f"{package}.nn.{name}"] = getattr(_nn, name)
+    return _nn

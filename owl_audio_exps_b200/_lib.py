@@ -49,6 +49,7 @@ SIGNATURES = {
     "owl_gemm_bf16_check": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, vp, i64, vp], C.c_int),
     "owl_cast_f32_bf16": ([vp, vp, i64, vp], C.c_int),
     "owl_silu_bf16": ([vp, vp, i64, vp], C.c_int),
+    "owl_dsilu_mul_bf16": ([vp, vp, vp, i64, vp], C.c_int),
     "owl_adaln_modulate_fwd": ([vp, vp, vp, i64, vp, vp, i64, i64, i64, f32, vp], C.c_int),
     "owl_adaln_modulate_bwd": ([vp, vp, vp, i64, vp, vp, vp, vp, vp, i64, i64, i64, i64, vp], C.c_int),
     "owl_gate_fwd": ([vp, vp, i64, vp, vp, i64, i64, i64, vp], C.c_int),
@@ -58,6 +59,7 @@ SIGNATURES = {
                               i64, i64, i64, i64, f32, vp], C.c_int),
     "owl_qk_norm_rope_bwd": ([vp, vp, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, vp, vp, vp, i64, vp,
                               i64, i64, i64, i64, vp], C.c_int),
+    "owl_rope_apply": ([vp, vp, vp, i64, vp, i64, i64, i64, C.c_int, vp], C.c_int),
     "owl_kv_append": ([vp, i64, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp], C.c_int),
     "owl_layer_norm_fwd": ([vp, vp, i64, i64, f32, vp], C.c_int),
     "owl_attn_fwd": (_ATTN_FWD, C.c_int),

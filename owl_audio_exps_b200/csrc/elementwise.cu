@@ -64,6 +64,29 @@ __global__ void silu_bf16_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
   }
 }
 
+// dz = dy * silu'(z)   (backward of F.silu when it is not fused into a GEMM epilogue)
+__global__ void dsilu_mul_bf16_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, bf16* __restrict__ dz,
+                                      int64_t n) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  const int64_t n8 = n >> 3;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float g[8], f[8];
+    unpack8(ldg16(dy + 8 * i), g);
+    unpack8(ldg16(z + 8 * i), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float s = sigmoidf_fast(f[j]);
+      g[j] *= s * (1.f + f[j] * (1.f - s));
+    }
+    stg16(dz + 8 * i, pack8(g));
+  }
+  for (int64_t i = (n8 << 3) + static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v = __bfloat162float(z[i]);
+    const float s = sigmoidf_fast(v);
+    dz[i] = __float2bfloat16_rn(__bfloat162float(dy[i]) * s * (1.f + v * (1.f - s)));
+  }
+}
+
 static inline int grid_for(int64_t work_items, int threads) {
   int64_t blocks = (work_items + threads - 1) / threads;
   const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
@@ -419,6 +442,14 @@ int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream) {
   OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
   silu_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const bf16*>(x), static_cast<bf16*>(y), n);
+  return launch_status();
+}
+
+int owl_dsilu_mul_bf16(const void* dy, const void* z, void* dz, int64_t n, owl_stream_t stream) {
+  OWL_REQUIRE(dy && z && dz && n > 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(aligned16(dy) && aligned16(z) && aligned16(dz), OWL_ERR_ALIGN);
+  dsilu_mul_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(dy), static_cast<const bf16*>(z), static_cast<bf16*>(dz), n);
   return launch_status();
 }
 

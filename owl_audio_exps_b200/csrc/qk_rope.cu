@@ -144,6 +144,59 @@ qk_norm_rope_bwd_kernel(const bf16* __restrict__ dq, const bf16* __restrict__ dk
   *reinterpret_cast<uint4*>(dqkv + tt * 8) = out;
 }
 
+// Bare RoPE on contiguous [R, L, dh] rows (RoPE.forward called on its own, rope.py:43-51).
+// forward: pairs (2i, 2i+1) -> halves [y0 | y1];  inverse (its autograd): halves -> pairs with the
+// transposed rotation.  One thread = 4 pairs.
+__global__ void __launch_bounds__(256)
+rope_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ cos_tab, const float* __restrict__ sin_tab,
+                  int64_t pos_offset, bf16* __restrict__ y, int64_t R, int64_t L, int dh, int inverse) {
+  const int half = dh >> 1, Q = half >> 2;
+  const int64_t total = R * L * Q;
+  const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int chunk = static_cast<int>(t % Q);
+  const int64_t row = t / Q;  // r * L + l
+  const int64_t l = row % L;
+  const int64_t pos = pos_offset + l;
+  const float4 c4 = __ldg(reinterpret_cast<const float4*>(cos_tab + pos * half + chunk * 4));
+  const float4 s4 = __ldg(reinterpret_cast<const float4*>(sin_tab + pos * half + chunk * 4));
+  const float cs[4] = {c4.x, c4.y, c4.z, c4.w};
+  const float sn[4] = {s4.x, s4.y, s4.z, s4.w};
+  const bf16* xr = x + row * dh;
+  bf16* yr = y + row * dh;
+  if (!inverse) {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(xr + chunk * 8));
+    const float f[8] = {bf16_lo(raw.x), bf16_hi(raw.x), bf16_lo(raw.y), bf16_hi(raw.y),
+                        bf16_lo(raw.z), bf16_hi(raw.z), bf16_lo(raw.w), bf16_hi(raw.w)};
+    float y0[4], y1[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      y0[p] = f[2 * p] * cs[p] - f[2 * p + 1] * sn[p];
+      y1[p] = f[2 * p + 1] * cs[p] + f[2 * p] * sn[p];
+    }
+    uint2 o0, o1;
+    o0.x = pack_bf16(y0[0], y0[1]); o0.y = pack_bf16(y0[2], y0[3]);
+    o1.x = pack_bf16(y1[0], y1[1]); o1.y = pack_bf16(y1[2], y1[3]);
+    *reinterpret_cast<uint2*>(yr + chunk * 4) = o0;
+    *reinterpret_cast<uint2*>(yr + half + chunk * 4) = o1;
+  } else {
+    const uint2 g0 = __ldg(reinterpret_cast<const uint2*>(xr + chunk * 4));
+    const uint2 g1 = __ldg(reinterpret_cast<const uint2*>(xr + half + chunk * 4));
+    const float d0[4] = {bf16_lo(g0.x), bf16_hi(g0.x), bf16_lo(g0.y), bf16_hi(g0.y)};
+    const float d1[4] = {bf16_lo(g1.x), bf16_hi(g1.x), bf16_lo(g1.y), bf16_hi(g1.y)};
+    float o[8];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      o[2 * p] = d0[p] * cs[p] + d1[p] * sn[p];
+      o[2 * p + 1] = d1[p] * cs[p] - d0[p] * sn[p];
+    }
+    uint4 out;
+    out.x = pack_bf16(o[0], o[1]); out.y = pack_bf16(o[2], o[3]);
+    out.z = pack_bf16(o[4], o[5]); out.w = pack_bf16(o[6], o[7]);
+    *reinterpret_cast<uint4*>(yr + chunk * 8) = out;
+  }
+}
+
 }  // namespace owl
 
 using namespace owl;
@@ -187,6 +240,18 @@ int owl_qk_norm_rope_bwd(const void* dq, const void* dk, const void* dv, int64_t
       static_cast<const bf16*>(dq), static_cast<const bf16*>(dk), static_cast<const bf16*>(dv), g_sb, g_sh,
       static_cast<const bf16*>(q), q_sb, q_sh, static_cast<const bf16*>(k), k_sb, k_sh, rstd_q, rstd_k, cos_tab,
       sin_tab, pos_offset, static_cast<bf16*>(dqkv), B, L, static_cast<int>(H), static_cast<int>(dh));
+  return launch_status();
+}
+
+int owl_rope_apply(const void* x, const float* cos_tab, const float* sin_tab, int64_t pos_offset, void* y, int64_t R,
+                   int64_t L, int64_t dh, int inverse, owl_stream_t stream) {
+  if (!x || !y || !cos_tab || !sin_tab || R <= 0 || L <= 0 || dh <= 0 || pos_offset < 0) return OWL_ERR_BAD_ARG;
+  if (dh % 8 != 0) return OWL_ERR_UNSUPPORTED;
+  if (!aligned16(x) || !aligned16(y) || !aligned16(cos_tab) || !aligned16(sin_tab)) return OWL_ERR_ALIGN;
+  const int64_t total = R * L * (dh / 8);
+  rope_apply_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(x), cos_tab, sin_tab, pos_offset, static_cast<bf16*>(y), R, L, static_cast<int>(dh),
+      inverse);
   return launch_status();
 }
 

@@ -1,0 +1,632 @@
+"""Autograd layer over the C-ABI kernels: the DiT block (fused schedule) and its standalone pieces.
+
+This is the host side of the hot path.  Every function here only sequences launches of
+libowl_dit.so (through `ops`) and keeps the tensors the backward needs; there is no torch math on
+the path except allocation, views and (outside the block) gradient accumulation by autograd.
+
+Reference arithmetic being replaced (paths relative to the reference root):
+  DiTBlock.forward   owl_wms/nn/attn.py:130-143
+  Attn.forward       owl_wms/nn/attn.py:79-113
+  AdaLN / Gate       owl_wms/nn/modulation.py:12-26, 33-43
+  MLP.forward        owl_wms/nn/mlp.py:33-37
+  rms_norm           owl_wms/nn/normalization.py:10-11
+  RoPE.forward       owl_wms/nn/rope.py:43-51
+
+Numerics: bf16 storage, fp32 accumulation, one bf16 rounding per fused op (the eager reference rounds
+after every op).  Parameters may be fp32 (autocast regime, rft_trainer.py:146) or bf16 (inference
+regime, causvid_pipeline.py:36); activations on the path are always bf16.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import ops
+from ._lib import (OWL_EPI_BIAS_SILU, OWL_EPI_DSILU, OWL_EPI_F32, OWL_EPI_GATE_RESIDUAL, OWL_EPI_STORE,
+                   OWL_GEMM_NN, OWL_GEMM_NT, OWL_GEMM_TN)
+
+bf16 = torch.bfloat16
+f32 = torch.float32
+
+# F.rms_norm(x, (D,)) with eps=None: torch 2.11 adds fp32 machine epsilon to mean(x^2) for bf16 inputs
+# (tests/test_block_gpu.py::test_rms_eps_matches_torch re-probes this on the GPU box).
+RMS_EPS = 1.1920928955078125e-07
+LN_EPS = 1e-5
+
+
+@dataclass(frozen=True)
+class FrameMask:
+    """The reference's frame-block mask (attn.py:24-62) as the closed-form descriptor the attention
+    kernels evaluate in place of a materialised BlockMask.  `window_frames` <= 0: unlimited."""
+
+    tokens_per_frame: int
+    window_frames: int = 0
+    q_offset: int = 0
+    causal: bool = True
+    doc_id: Optional[torch.Tensor] = None  # int32 [B, n_frames_total] on the device, or None
+
+    def kw(self):
+        return dict(tokens_per_frame=self.tokens_per_frame, window_frames=self.window_frames,
+                    q_offset=self.q_offset, causal=self.causal, doc_id=self.doc_id)
+
+    def mask_mod(self, b, h, q, kv):
+        """Same predicate as the closure in attn.py:43-59 (for tests / dense rendering)."""
+        T = self.tokens_per_frame
+        fq, fk = (q + self.q_offset) // T, kv // T
+        m = torch.ones_like(fq + fk, dtype=torch.bool)
+        if self.causal:
+            m = m & (fk <= fq)
+        if self.window_frames > 0:
+            m = m & ((fq - fk).abs() < self.window_frames)
+        if self.doc_id is not None:
+            m = m & (self.doc_id[b, fq] == self.doc_id[b, fk])
+        return m
+
+
+DECODE_MASK_T = 1  # decode mode (block_mask None, attn.py:106-107): every key visible
+
+
+def _decode_mask() -> FrameMask:
+    return FrameMask(tokens_per_frame=DECODE_MASK_T, window_frames=0, q_offset=0, causal=False, doc_id=None)
+
+
+# ------------------------------------------------------------------------------------------------
+# parameter staging: fp32 master weights -> bf16 operands (what autocast does per forward)
+# ------------------------------------------------------------------------------------------------
+def _capturing() -> bool:
+    return torch.cuda.is_current_stream_capturing()
+
+
+class WeightStage:
+    """bf16 operand copies of a module's parameters, re-staged when a parameter's version changes.
+
+    Inside CUDA-graph capture nothing is cached: the casts are recorded into the graph so each replay
+    sees the current master weights."""
+
+    def __init__(self):
+        self._slots = {}
+
+    def get(self, key: str, params, rows=None) -> torch.Tensor:
+        """bf16 [sum(rows), K] concatenation of 2-D `params` (or fp32 concatenation of 1-D biases)."""
+        vers = tuple((p.data_ptr(), p._version, p.dtype) for p in params)
+        hit = self._slots.get(key)
+        if hit is not None and hit[0] == vers and not _capturing():
+            return hit[1]
+        p0 = params[0]
+        if p0.dim() == 1:
+            out = params[0].detach().float() if len(params) == 1 else torch.cat([p.detach().float() for p in params])
+            out = out.contiguous()
+        elif len(params) == 1 and p0.dtype == bf16 and p0.is_contiguous():
+            out = p0.detach()
+        else:
+            n = sum(p.shape[0] for p in params)
+            out = torch.empty(n, p0.shape[1], device=p0.device, dtype=bf16)
+            r = 0
+            for p in params:
+                dst = out[r:r + p.shape[0]]
+                if p.dtype == f32:
+                    ops.cast_f32_bf16(p.detach().contiguous(), dst)
+                else:
+                    dst.copy_(p.detach())
+                r += p.shape[0]
+        if not _capturing():
+            self._slots[key] = (vers, out)
+        return out
+
+    def clear(self):
+        self._slots.clear()
+
+    # EMA deep-copies the model and checkpoints pickle it: the staged operands never travel
+    def __deepcopy__(self, memo):
+        return WeightStage()
+
+    def __reduce__(self):
+        return (WeightStage, ())
+
+
+def _as_bf16(t: torch.Tensor) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError("owl_audio_exps_b200: CUDA tensors required (sm_100a kernels only; there is no CPU path)")
+    if t.dtype == bf16:
+        return t if t.is_contiguous() else t.contiguous()
+    if t.dtype == f32 and not t.requires_grad:
+        return ops.cast_f32_bf16(t.contiguous())
+    return t.to(bf16).contiguous()
+
+
+def _grad_like(g32: Optional[torch.Tensor], p: torch.Tensor):
+    if g32 is None:
+        return None
+    return g32 if p.dtype == f32 else g32.to(p.dtype)
+
+
+def _sink(p: torch.Tensor) -> Optional[torch.Tensor]:
+    """fp32 gradient sink installed by engine.GradBuckets: wgrad GEMMs accumulate straight into the
+    flat all-reduce bucket instead of materialising a gradient tensor for autograd to copy."""
+    return getattr(p, "_owl_grad_sink", None)
+
+
+def _wgrad(dy: torch.Tensor, x: torch.Tensor, p: torch.Tensor, M: int) -> Optional[torch.Tensor]:
+    """dW[N,K] = dy[M,N]^T x[M,K] in fp32.  Returns the gradient for autograd, or None when it was
+    accumulated into the parameter's bucket sink."""
+    N, K = p.shape
+    sink = _sink(p)
+    if sink is not None:
+        ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=sink, accumulate=True)
+        return None
+    g = torch.empty(N, K, device=dy.device, dtype=f32)
+    ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=g)
+    return _grad_like(g, p)
+
+
+def _bgrad(dy: torch.Tensor, p: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    if p is None:
+        return None
+    sink = _sink(p)
+    if sink is not None:
+        ops.colsum(dy, sink, accumulate=True)
+        return None
+    g = torch.empty(p.shape[0], device=dy.device, dtype=f32)
+    ops.colsum(dy, g)
+    return _grad_like(g, p)
+
+
+# ------------------------------------------------------------------------------------------------
+# standalone pieces (used by the AdaLN / Gate / MLP / Attn / FinalLayer modules when they are called
+# on their own; DiTBlock uses the fused schedule further down)
+# ------------------------------------------------------------------------------------------------
+class _Linear(torch.autograd.Function):
+    """y = act(x W^T + b).  silu_in: apply SiLU to x first (modulation.py:17-19: fc(silu(cond)));
+    silu_out: y = silu(.) (mlp.py:34-35).  dgrad / wgrad / dbias are the NN / TN GEMMs and a column sum."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, w16, b32, silu_in: bool, silu_out: bool):
+        shp = x.shape
+        x16 = _as_bf16(x).view(-1, shp[-1])
+        M, K = x16.shape
+        N = w16.shape[0]
+        a = ops.silu(x16) if silu_in else x16
+        y = torch.empty(M, N, device=x16.device, dtype=bf16)
+        z = None
+        if silu_out:
+            z = torch.empty_like(y)
+            ops.gemm(OWL_GEMM_NT, a, w16, M, N, K, mode=OWL_EPI_BIAS_SILU, bias=b32, out0=z, out1=y)
+        else:
+            ops.gemm(OWL_GEMM_NT, a, w16, M, N, K, mode=OWL_EPI_STORE, bias=b32, out0=y)
+        ctx.save_for_backward(x16 if silu_in else None, a, z, w16, weight, bias)
+        ctx.flags = (silu_in, silu_out, shp, x.dtype)
+        return y.view(*shp[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x16, a, z, w16, weight, bias = ctx.saved_tensors
+        silu_in, silu_out, shp, xdtype = ctx.flags
+        N, K = w16.shape
+        dy = _as_bf16(dy).view(-1, N)
+        M = dy.shape[0]
+        if silu_out:  # dz = dy * silu'(z): identity-free path = tiny GEMM-less elementwise via torch is avoided:
+            dz = torch.empty_like(dy)
+            ops.dsilu_mul(dy, z, dz)
+            dy = dz
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, device=dy.device, dtype=bf16)
+            if silu_in:
+                ops.gemm(OWL_GEMM_NN, dy, w16, M, K, N, mode=OWL_EPI_DSILU, aux0=x16, out0=dx)
+            else:
+                ops.gemm(OWL_GEMM_NN, dy, w16, M, K, N, mode=OWL_EPI_STORE, out0=dx)
+            dx = dx.view(shp).to(xdtype)
+        dw = _wgrad(dy, a, weight, M) if ctx.needs_input_grad[1] else None
+        db = _bgrad(dy, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
+        return dx, dw, db, None, None, None, None
+
+
+def linear(x, weight, bias, stage: WeightStage, key: str, silu_in=False, silu_out=False):
+    w16 = stage.get(key + ".w", [weight])
+    b32 = stage.get(key + ".b", [bias]) if bias is not None else None
+    return _Linear.apply(x, weight, bias, w16, b32, silu_in, silu_out)
+
+
+class _Silu(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x16 = _as_bf16(x)
+        ctx.save_for_backward(x16)
+        ctx.xdtype = x.dtype
+        return ops.silu(x16)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x16,) = ctx.saved_tensors
+        dx = torch.empty_like(x16)
+        ops.dsilu_mul(_as_bf16(dy), x16, dx)
+        return dx.to(ctx.xdtype)
+
+
+def silu(x):
+    return _Silu.apply(x)
+
+
+class _AdaLNModulate(torch.autograd.Function):
+    """h = rms_norm(x) * (1 + a[frame]) + b[frame]; ab = [B, F, 2d] (a | b) or None for plain rms_norm."""
+
+    @staticmethod
+    def forward(ctx, x, ab):
+        shp = x.shape
+        d = shp[-1]
+        x16 = _as_bf16(x).view(-1, d)
+        M = x16.shape[0]
+        if ab is not None:
+            ab16 = _as_bf16(ab).view(-1, 2 * d)
+            T = M // ab16.shape[0]
+            a, b = ab16[:, :d], ab16[:, d:]
+        else:
+            ab16, T, a, b = None, 1, None, None
+        h, rstd = ops.adaln_modulate_fwd(x16, a, b, T, RMS_EPS)
+        ctx.save_for_backward(x16, ab16, rstd)
+        ctx.meta = (shp, T, x.dtype, None if ab is None else (ab.shape, ab.dtype))
+        return h.view(shp)
+
+    @staticmethod
+    def backward(ctx, dh):
+        x16, ab16, rstd = ctx.saved_tensors
+        shp, T, xdtype, abmeta = ctx.meta
+        d = shp[-1]
+        dh = _as_bf16(dh).view(-1, d)
+        if ab16 is not None:
+            dab = torch.empty_like(ab16)
+            dx = ops.adaln_modulate_bwd(dh, x16, ab16[:, :d], rstd, None, dab[:, :d], dab[:, d:], T)
+            return dx.view(shp).to(xdtype), dab.view(abmeta[0]).to(abmeta[1])
+        dx = ops.adaln_modulate_bwd(dh, x16, None, rstd, None, None, None, 1)
+        return dx.view(shp).to(xdtype), None
+
+
+def adaln_modulate(x, ab):
+    return _AdaLNModulate.apply(x, ab)
+
+
+def rms_norm(x):
+    """Weight-less RMSNorm over the last dim (normalization.py:10-11)."""
+    if x.shape[-1] % 8 != 0:
+        raise RuntimeError("rms_norm: last dim must be a multiple of 8 for the 128-bit vectorised kernel")
+    return _AdaLNModulate.apply(x, None)
+
+
+class _Gate(torch.autograd.Function):
+    """out = c[frame] * x (+ res)   (modulation.py:41-43, cond_gate 57-63)."""
+
+    @staticmethod
+    def forward(ctx, x, c, res):
+        shp = x.shape
+        d = shp[-1]
+        x16 = _as_bf16(x).view(-1, d)
+        c16 = _as_bf16(c).view(-1, d)
+        T = x16.shape[0] // c16.shape[0]
+        r16 = _as_bf16(res).view(-1, d) if res is not None else None
+        out = ops.gate_fwd(x16, c16, r16, T)
+        ctx.save_for_backward(x16, c16)
+        ctx.meta = (shp, T, x.dtype, c.shape, c.dtype, res is not None)
+        return out.view(shp)
+
+    @staticmethod
+    def backward(ctx, dout):
+        x16, c16 = ctx.saved_tensors
+        shp, T, xdtype, cshape, cdtype, has_res = ctx.meta
+        d = shp[-1]
+        dout = _as_bf16(dout).view(-1, d)
+        dc = torch.empty_like(c16)
+        dx = ops.gate_bwd(dout, x16, c16, dc, None, T)
+        return dx.view(shp).to(xdtype), dc.view(cshape).to(cdtype), (dout.view(shp) if has_res else None)
+
+
+def gate(x, c, res=None):
+    return _Gate.apply(x, c, res)
+
+
+# ------------------------------------------------------------------------------------------------
+# attention core: qkv -> (QK-RMSNorm, RoPE, head split, KV-cache append) -> masked attention
+# ------------------------------------------------------------------------------------------------
+@dataclass
+class AttnPlan:
+    """Everything Attn.forward (attn.py:79-113) decides on the host before launching kernels."""
+
+    n_heads: int
+    cos: torch.Tensor            # fp32 [L_max, dh/2]
+    sin: torch.Tensor
+    mask: Optional[FrameMask]    # None = decode mode (block_mask None)
+    local: bool = False
+    local_offset: int = 0        # local_window * tokens_per_frame (attn.py:77)
+    kv_cache: object = None
+    layer_idx: int = 0
+
+
+def _attn_core_fwd(qkv: torch.Tensor, plan: AttnPlan, need_grad: bool):
+    """qkv bf16 [B, L, 3*d] -> o bf16 [B, L, d] plus the tensors the backward needs."""
+    B, L, three_d = qkv.shape
+    H = plan.n_heads
+    dh = three_d // (3 * H)
+    if dh not in (64, 128):
+        raise RuntimeError(f"head dim {dh} unsupported by the tcgen05 attention kernels (64 or 128)")
+    dev = qkv.device
+    cache = plan.kv_cache
+    offset = cache.get_offset(plan.layer_idx) if cache is not None else 0
+    if offset + L > plan.cos.shape[0]:
+        raise RuntimeError(f"RoPE table has {plan.cos.shape[0]} positions; need {offset + L}")
+    q = torch.empty(B, H, L, dh, device=dev, dtype=bf16)
+    n_old = 0
+    if cache is not None and (offset > 0 or cache.should_update):
+        n_old = cache.length_at(plan.layer_idx) if offset > 0 else 0
+        # in-place: new K/V rows are written by the kernel straight behind the cached rows.  When the
+        # backward will need them later (self-forcing, sf_vid_only.py:180-190) the attention operands
+        # must not alias the cache (it is overwritten by later frames), so a private copy is used.
+        private = need_grad and not cache.should_update
+        k_all, v_all = cache._operands(plan.layer_idx, L, use_old=offset > 0, private=private)
+        k_new, v_new = k_all[:, :, n_old:], v_all[:, :, n_old:]
+    else:
+        k_all = torch.empty(B, H, L, dh, device=dev, dtype=bf16)
+        v_all = torch.empty(B, H, L, dh, device=dev, dtype=bf16)
+        k_new, v_new = k_all, v_all
+    rq, rk = ops.qk_norm_rope_fwd(qkv, plan.cos, plan.sin, offset, H, RMS_EPS, q, k_new, v_new, want_rstd=need_grad)
+    if cache is not None and cache.should_update:
+        cache._commit(plan.layer_idx, L, k_all, v_all)
+        if need_grad:
+            # the committed rows may be overwritten / compacted later: detach the autograd copy
+            k_all, v_all = k_all.clone(), v_all.clone()
+    mask = plan.mask
+    if mask is None:
+        mask = _decode_mask()
+        if plan.local and plan.local_offset < k_all.shape[2]:
+            k_all, v_all = k_all[:, :, -plan.local_offset:], v_all[:, :, -plan.local_offset:]
+    o, lse = ops.attn_fwd(q, k_all, v_all, want_lse=need_grad, **mask.kw())
+    return o, (q, k_all, v_all, lse, rq, rk, offset, mask)
+
+
+def _attn_core_bwd(do: torch.Tensor, o: torch.Tensor, saved, plan_cos, plan_sin, L: int):
+    """-> dqkv bf16 [B, L, 3*d].  Cached key/value rows carry no gradient (they were produced under
+    no_grad, av_caching_v2.py:68-76); only the last L rows of dk/dv flow back."""
+    q, k_all, v_all, lse, rq, rk, offset, mask = saved
+    dq, dk, dv = ops.attn_bwd(do, o, q, k_all, v_all, lse, **mask.kw())
+    Lk = k_all.shape[2]
+    if Lk != L:
+        dk, dv = dk[:, :, Lk - L:], dv[:, :, Lk - L:]
+        k_new = k_all[:, :, Lk - L:]
+        if dq.stride() != dk.stride():
+            dk, dv = dk.contiguous(), dv.contiguous()
+    else:
+        k_new = k_all
+    if not (k_new.stride(3) == 1 and k_new.stride(2) == k_new.shape[3]):
+        k_new = k_new.contiguous()
+    return ops.qk_norm_rope_bwd(dq, dk, dv, q, k_new, rq, rk, plan_cos, plan_sin, offset)
+
+
+class _AttnCore(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, plan: AttnPlan):
+        need_grad = ctx.needs_input_grad[0]
+        qkv16 = _as_bf16(qkv)
+        o, saved = _attn_core_fwd(qkv16, plan, need_grad)
+        if need_grad:
+            q, k_all, v_all, lse, rq, rk, offset, mask = saved
+            ctx.save_for_backward(o, q, k_all, v_all, lse, rq, rk, plan.cos, plan.sin)
+            ctx.meta = (offset, mask, qkv.shape[1], qkv.dtype)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        o, q, k_all, v_all, lse, rq, rk, cos, sin = ctx.saved_tensors
+        offset, mask, L, dtype = ctx.meta
+        dqkv = _attn_core_bwd(_as_bf16(do), o, (q, k_all, v_all, lse, rq, rk, offset, mask), cos, sin, L)
+        return dqkv.to(dtype), None
+
+
+def attention(qkv, plan: AttnPlan):
+    return _AttnCore.apply(qkv, plan)
+
+
+class _Rope(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cos, sin, offset: int):
+        ctx.save_for_backward(cos, sin)
+        ctx.meta = (offset, x.dtype)
+        L = x.shape[-2]
+        if offset + L > cos.shape[0]:
+            raise RuntimeError(f"RoPE table has {cos.shape[0]} positions; need {offset + L}")
+        return ops.rope_apply(_as_bf16(x), cos, sin, offset).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        cos, sin = ctx.saved_tensors
+        offset, dtype = ctx.meta
+        return ops.rope_apply(_as_bf16(dy), cos, sin, offset, inverse=True).to(dtype), None, None, None
+
+
+def rope_only(x, cos, sin, offset: int = 0):
+    return _Rope.apply(x, cos, sin, offset)
+
+
+# ------------------------------------------------------------------------------------------------
+# the fused DiT block (attn.py:130-143): 13 launches forward, 22 backward
+# ------------------------------------------------------------------------------------------------
+_BLOCK_PARAMS = ("attn.qkv.weight", "attn.qkv.bias", "attn.out.weight", "attn.out.bias",
+                 "mlp.fc1.weight", "mlp.fc1.bias", "mlp.fc2.weight", "mlp.fc2.bias",
+                 "adaln1.fc.weight", "adaln1.fc.bias", "gate1.fc_c.weight", "gate1.fc_c.bias",
+                 "adaln2.fc.weight", "adaln2.fc.bias", "gate2.fc_c.weight", "gate2.fc_c.bias")
+
+
+def stage_block_weights(stage: WeightStage, P):
+    """bf16 operands + fp32 biases of one block.  The four conditioning projections (adaln1.fc,
+    gate1.fc_c, adaln2.fc, gate2.fc_c; modulation.py:10,31) share their input silu(cond), so they are
+    staged as ONE [6d, d] operand: columns [a1 | b1 | c1 | a2 | b2 | c2] of a single GEMM."""
+    (wqkv, bqkv, wout, bout, w1, b1, w2, b2, wa1, ba1, wg1, bg1, wa2, ba2, wg2, bg2) = P
+    return dict(
+        wqkv=stage.get("wqkv", [wqkv]), bqkv=stage.get("bqkv", [bqkv]),
+        wout=stage.get("wout", [wout]), bout=stage.get("bout", [bout]),
+        w1=stage.get("w1", [w1]), b1=stage.get("b1", [b1]),
+        w2=stage.get("w2", [w2]), b2=stage.get("b2", [b2]),
+        wc=stage.get("wc", [wa1, wg1, wa2, wg2]), bc=stage.get("bc", [ba1, bg1, ba2, bg2]),
+    )
+
+
+class DiTBlockFn(torch.autograd.Function):
+    """x_out = DiTBlock(x, cond).  Inputs: x [B,L,d], cond [B,F,d] (L = F*T), the 16 block parameters.
+
+    Forward schedule (M = B*L rows, R = B*F conditioning rows):
+      1  scond = silu(cond)                                   [R,d]      (skipped when the DiT stack passes it in)
+      2  mod   = scond Wc^T + bc                              [R,6d]     GEMM
+      3  h1    = rms_norm(x)*(1+a1)+b1 ; rstd1                [M,d]      adaLN kernel
+      4  qkv   = h1 Wqkv^T + bqkv                             [M,3d]     GEMM
+      5  q,k,v = rope(rms_norm(.)) + head split (+KV append)  [B,H,L,dh] QK-norm+RoPE kernel
+      6  o,lse = attention(q,k,v,mask)                        [M,d]      tcgen05 attention (token-major out)
+      7  y1 = o Wout^T + bout ; x1 = x + c1*y1                [M,d]      GEMM, gate+residual epilogue
+      8  h2    = rms_norm(x1)*(1+a2)+b2 ; rstd2               [M,d]      adaLN kernel
+      9  z = h2 W1^T + b1 ; s = silu(z)                       [M,4d]     GEMM, bias+SiLU epilogue
+      10 y2 = s W2^T + b2 ; x2 = x1 + c2*y2                   [M,d]      GEMM, gate+residual epilogue
+    The backward mirrors it with dgrad (NN) and wgrad (TN, fp32) GEMMs; silu', the residual-gradient
+    add, the per-frame da/db/dc reductions and the bias column sums are fused into kernel epilogues or
+    the single-pass memory-bound kernels.
+    """
+
+    @staticmethod
+    def forward(ctx, x, cond, scond, plan: AttnPlan, stage: WeightStage, *P):
+        B, L, d = x.shape
+        R = cond.shape[0] * cond.shape[1]
+        M = B * L
+        if M % R != 0:
+            raise RuntimeError(f"tokens ({L}) must be a multiple of conditioning frames ({cond.shape[1]})")
+        T = M // R
+        need_grad = any(ctx.needs_input_grad)
+        W = stage_block_weights(stage, P)
+        x16 = _as_bf16(x).view(M, d)
+        cond16 = _as_bf16(cond).view(R, d)
+        scond16 = ops.silu(cond16) if scond is None else scond.view(R, d)
+
+        mod = torch.empty(R, 6 * d, device=x16.device, dtype=bf16)
+        ops.gemm(OWL_GEMM_NT, scond16, W["wc"], R, 6 * d, d, mode=OWL_EPI_STORE, bias=W["bc"], out0=mod)
+        a1, b1, c1 = mod[:, 0:d], mod[:, d:2 * d], mod[:, 2 * d:3 * d]
+        a2, b2, c2 = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], mod[:, 5 * d:6 * d]
+
+        h1, rstd1 = ops.adaln_modulate_fwd(x16, a1, b1, T, RMS_EPS, want_rstd=need_grad)
+        qkv = torch.empty(B, L, 3 * d, device=x16.device, dtype=bf16)
+        ops.gemm(OWL_GEMM_NT, h1, W["wqkv"], M, 3 * d, d, mode=OWL_EPI_STORE, bias=W["bqkv"], out0=qkv)
+        o, asaved = _attn_core_fwd(qkv, plan, need_grad)
+        del qkv
+        o2 = o.view(M, d)
+
+        x1 = torch.empty(M, d, device=x16.device, dtype=bf16)
+        y1 = torch.empty(M, d, device=x16.device, dtype=bf16) if need_grad else None
+        ops.gemm(OWL_GEMM_NT, o2, W["wout"], M, d, d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["bout"], out0=x1, out1=y1,
+                 aux0=x16, aux1=c1, rows_per_frame=T)
+
+        h2, rstd2 = ops.adaln_modulate_fwd(x1, a2, b2, T, RMS_EPS, want_rstd=need_grad)
+        z = torch.empty(M, 4 * d, device=x16.device, dtype=bf16)
+        s = torch.empty(M, 4 * d, device=x16.device, dtype=bf16)
+        ops.gemm(OWL_GEMM_NT, h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=z, out1=s)
+        x2 = torch.empty(M, d, device=x16.device, dtype=bf16)
+        y2 = torch.empty(M, d, device=x16.device, dtype=bf16) if need_grad else None
+        ops.gemm(OWL_GEMM_NT, s, W["w2"], M, d, 4 * d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["b2"], out0=x2, out1=y2,
+                 aux0=x1, aux1=c2, rows_per_frame=T)
+
+        if need_grad:
+            q, k_all, v_all, lse, rq, rk, offset, mask = asaved
+            ctx.save_for_backward(x16, cond16, scond16, mod, rstd1, h1, q, k_all, v_all, lse, rq, rk, o2, y1, x1, rstd2,
+                                  h2, z, s, y2, W["wqkv"], W["wout"], W["w1"], W["w2"], W["wc"], plan.cos, plan.sin, *P)
+            ctx.meta = (B, L, d, R, T, offset, mask, x.dtype, cond.dtype, cond.shape,
+                        None if scond is None else scond.shape)
+        return x2.view(B, L, d) if x.dtype == bf16 else x2.view(B, L, d).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dx2):
+        sv = ctx.saved_tensors
+        (x16, cond16, scond16, mod, rstd1, h1, q, k_all, v_all, lse, rq, rk, o2, y1, x1, rstd2, h2, z, s, y2,
+         wqkv16, wout16, w116, w216, wc16, cos, sin) = sv[:27]
+        P = sv[27:]
+        (wqkv, bqkv, wout, bout, w1, b1, w2, b2, wa1, ba1, wg1, bg1, wa2, ba2, wg2, bg2) = P
+        B, L, d, R, T, offset, mask, xdtype, cdtype, cond_shape, scond_shape = ctx.meta
+        M = B * L
+        dev = x16.device
+        need = ctx.needs_input_grad
+        np0 = 5  # index of the first parameter among forward's inputs
+        dx2 = _as_bf16(dx2).view(M, d)
+        c1, a2, c2, a1 = mod[:, 2 * d:3 * d], mod[:, 3 * d:4 * d], mod[:, 5 * d:6 * d], mod[:, 0:d]
+        dmod = torch.empty(R, 6 * d, device=dev, dtype=bf16)
+
+        # ---- MLP branch: x2 = x1 + c2 * (s W2^T + b2)
+        g_b2 = _fresh_or_sink(b2, need[np0 + 7])
+        dy2 = ops.gate_bwd(dx2, y2, c2, dmod[:, 5 * d:6 * d], g_b2[0], T, dbias_accumulate=g_b2[1])
+        g_b2 = None if (g_b2[0] is None or g_b2[1]) else _grad_like(g_b2[0], b2)
+        dz = torch.empty(M, 4 * d, device=dev, dtype=bf16)
+        ops.gemm(OWL_GEMM_NN, dy2, w216, M, 4 * d, d, mode=OWL_EPI_DSILU, aux0=z, out0=dz)
+        g_w2 = _wgrad(dy2, s, w2, M) if need[np0 + 6] else None
+        del dy2
+        g_b1 = _bgrad(dz, b1) if need[np0 + 5] else None
+        dh2 = torch.empty(M, d, device=dev, dtype=bf16)
+        ops.gemm(OWL_GEMM_NN, dz, w116, M, d, 4 * d, mode=OWL_EPI_STORE, out0=dh2)
+        g_w1 = _wgrad(dz, h2, w1, M) if need[np0 + 4] else None
+        del dz
+        dx1 = ops.adaln_modulate_bwd(dh2, x1, a2, rstd2, dx2, dmod[:, 3 * d:4 * d], dmod[:, 4 * d:5 * d], T)
+        del dh2
+
+        # ---- attention branch: x1 = x + c1 * (o Wout^T + bout)
+        g_bout = _fresh_or_sink(bout, need[np0 + 3])
+        dy1 = ops.gate_bwd(dx1, y1, c1, dmod[:, 2 * d:3 * d], g_bout[0], T, dbias_accumulate=g_bout[1])
+        g_bout = None if (g_bout[0] is None or g_bout[1]) else _grad_like(g_bout[0], bout)
+        do = torch.empty(B, L, d, device=dev, dtype=bf16)
+        ops.gemm(OWL_GEMM_NN, dy1, wout16, M, d, d, mode=OWL_EPI_STORE, out0=do)
+        g_wout = _wgrad(dy1, o2, wout, M) if need[np0 + 2] else None
+        del dy1
+        dqkv = _attn_core_bwd(do, o2.view(B, L, d), (q, k_all, v_all, lse, rq, rk, offset, mask), cos, sin, L)
+        dqkv2 = dqkv.view(M, 3 * d)
+        g_bqkv = _bgrad(dqkv2, bqkv) if need[np0 + 1] else None
+        dh1 = torch.empty(M, d, device=dev, dtype=bf16)
+        ops.gemm(OWL_GEMM_NN, dqkv2, wqkv16, M, d, 3 * d, mode=OWL_EPI_STORE, out0=dh1)
+        g_wqkv = _wgrad(dqkv2, h1, wqkv, M) if need[np0 + 0] else None
+        del dqkv, dqkv2
+        dx = ops.adaln_modulate_bwd(dh1, x16, a1, rstd1, dx1, dmod[:, 0:d], dmod[:, d:2 * d], T)
+
+        # ---- conditioning projections: mod = silu(cond) Wc^T + bc
+        g_wa1 = g_wg1 = g_wa2 = g_wg2 = g_ba1 = g_bg1 = g_ba2 = g_bg2 = None
+        if any(need[np0 + 8:np0 + 16]):
+            sinks = [_sink(p) for p in (wa1, wg1, wa2, wg2)]
+            if all(s_ is not None for s_ in sinks):
+                for p, lo, hi in ((wa1, 0, 2 * d), (wg1, 2 * d, 3 * d), (wa2, 3 * d, 5 * d), (wg2, 5 * d, 6 * d)):
+                    _wgrad(dmod[:, lo:hi], scond16, p, R)
+                for p, lo, hi in ((ba1, 0, 2 * d), (bg1, 2 * d, 3 * d), (ba2, 3 * d, 5 * d), (bg2, 5 * d, 6 * d)):
+                    _bgrad(dmod[:, lo:hi], p)
+            else:
+                gwc = torch.empty(6 * d, d, device=dev, dtype=f32)
+                ops.gemm(OWL_GEMM_TN, dmod, scond16, 6 * d, d, R, mode=OWL_EPI_F32, outf=gwc)
+                gbc = torch.empty(6 * d, device=dev, dtype=f32)
+                ops.colsum(dmod, gbc)
+                g_wa1, g_wg1 = _grad_like(gwc[0:2 * d], wa1), _grad_like(gwc[2 * d:3 * d], wg1)
+                g_wa2, g_wg2 = _grad_like(gwc[3 * d:5 * d], wa2), _grad_like(gwc[5 * d:6 * d], wg2)
+                g_ba1, g_bg1 = _grad_like(gbc[0:2 * d], ba1), _grad_like(gbc[2 * d:3 * d], bg1)
+                g_ba2, g_bg2 = _grad_like(gbc[3 * d:5 * d], ba2), _grad_like(gbc[5 * d:6 * d], bg2)
+        dcond = dscond = None
+        if scond_shape is not None:
+            if need[2]:
+                dscond = torch.empty(R, d, device=dev, dtype=bf16)
+                ops.gemm(OWL_GEMM_NN, dmod, wc16, R, d, 6 * d, mode=OWL_EPI_STORE, out0=dscond)
+                dscond = dscond.view(scond_shape)
+        elif need[1]:
+            dcond = torch.empty(R, d, device=dev, dtype=bf16)
+            ops.gemm(OWL_GEMM_NN, dmod, wc16, R, d, 6 * d, mode=OWL_EPI_DSILU, aux0=cond16, out0=dcond)
+            dcond = dcond.view(cond_shape).to(cdtype)
+
+        dx = dx.view(B, L, d)
+        if xdtype != bf16:
+            dx = dx.to(xdtype)
+        return (dx if need[0] else None, dcond, dscond, None, None,
+                g_wqkv, g_bqkv, g_wout, g_bout, g_w1, g_b1, g_w2, g_b2,
+                g_wa1, g_ba1, g_wg1, g_bg1, g_wa2, g_ba2, g_wg2, g_bg2)
+
+
+def _fresh_or_sink(p: torch.Tensor, needed: bool):
+    """(fp32 destination for a fused bias column-sum, accumulate flag)."""
+    if not needed:
+        return None, False
+    sink = _sink(p)
+    if sink is not None:
+        return sink, True
+    return torch.empty(p.shape[0], device=p.device, dtype=f32), False

@@ -111,6 +111,13 @@ def silu(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def dsilu_mul(dy: torch.Tensor, z: torch.Tensor, dz: torch.Tensor) -> torch.Tensor:
+    _req(dy), _req(z), _req(dz)
+    _lib.check(_lib.load().owl_dsilu_mul_bf16(dy.data_ptr(), z.data_ptr(), dz.data_ptr(), z.numel(), _stream()),
+               "owl_dsilu_mul_bf16")
+    return dz
+
+
 def adaln_modulate_fwd(x, a, b, T: int, eps: float, want_rstd: bool = True):
     """h = rms_norm(x) * (1 + a[frame]) + b[frame]; x [M,d]; a,b [M/T,d] column slices (or None)."""
     _req(x)
@@ -196,6 +203,17 @@ def qk_norm_rope_bwd(dq, dk, dv, q, k, rq, rk, cos, sin, pos_offset: int):
                                           pos_offset, dqkv.data_ptr(), B, L, H, dh, _stream())
     _lib.check(rc, "owl_qk_norm_rope_bwd")
     return dqkv
+
+
+def rope_apply(x, cos, sin, pos_offset: int, inverse: bool = False):
+    """x contiguous bf16 [..., L, dh] -> rotated copy (see owl_rope_apply)."""
+    _req(x)
+    L, dh = x.shape[-2], x.shape[-1]
+    y = torch.empty_like(x)
+    rc = _lib.load().owl_rope_apply(x.data_ptr(), cos.data_ptr(), sin.data_ptr(), pos_offset, y.data_ptr(),
+                                    x.numel() // (L * dh), L, dh, int(inverse), _stream())
+    _lib.check(rc, "owl_rope_apply")
+    return y
 
 
 def kv_append(src, cache, pos: int):

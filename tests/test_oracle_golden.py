@@ -1,0 +1,87 @@
+"""Pin the oracle (oracle/dit_oracle.py) to the reference: fixtures in tests/golden/ were produced by the
+reference's own owl_wms/nn modules (tests/golden/make_golden.py).  CPU only."""
+import pytest
+import torch
+
+from helpers import GOLDEN_CASES, cfg_of, load_golden, relerr
+from oracle import dit_oracle as O
+
+TOL = 2e-5  # fp32 vs fp32, different op order
+
+
+def _weights(fx):
+    return {k: v.float() for k, v in fx["state"].items()}
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_dit_forward_backward_matches_reference(name):
+    fx = load_golden(name)
+    cfg = cfg_of(fx)
+    assert fx["flex_vs_dense_fwd_maxabs"] < 5e-6  # the SDPA substitution used for the reference's CPU backward
+    W = {k: v.requires_grad_(True) for k, v in _weights(fx).items()}
+    x = fx["x"].float().requires_grad_(True)
+    cond = fx["cond"].float().requires_grad_(True)
+    y = O.dit_forward(x, cond, W, cfg, fx["rope"], doc_id=fx["doc_id"])
+    assert relerr(y, fx["y"]) < TOL
+    (y * fx["dy"].float()).sum().backward()
+    assert relerr(x.grad, fx["dx"]) < TOL
+    assert relerr(cond.grad, fx["dcond"]) < TOL
+    for k, g in fx["grads"].items():
+        assert relerr(W[k].grad, g) < 5 * TOL, k
+
+
+def test_kv_rollout_matches_reference():
+    fx = load_golden("kv_rollout")
+    cfg = cfg_of(fx)
+    W = _weights(fx)
+    xs, conds, ref = fx["xs"].float(), fx["conds"].float(), fx["out"]
+    T = cfg.tokens_per_frame
+    with torch.no_grad():
+        cache = O.OracleKVCache(cfg.n_layers, T)
+        cache.should_update = True
+        y = O.dit_forward(xs[:, :3 * T], conds[:, :3], W, cfg, fx["rope"], kv_cache=cache)
+        assert relerr(y, ref["prefill"]) < TOL
+        cache.should_update = False
+        y = O.dit_forward(xs[:, 3 * T:4 * T], conds[:, 3:4], W, cfg, fx["rope"], kv_cache=cache)
+        assert relerr(y, ref["masked_cached"]) < TOL
+        y = O.dit_forward(xs[:, 3 * T:4 * T], conds[:, 3:4], W, cfg, fx["rope"], kv_cache=cache, decoding=True)
+        assert relerr(y, ref["decode3"]) < TOL
+        assert relerr(y, ref["full4"]) < TOL  # cache equivalence (sanity/sampling.py:86-133)
+        cache.should_update = True
+        y = O.dit_forward(xs[:, 3 * T:4 * T], conds[:, 3:4], W, cfg, fx["rope"], kv_cache=cache, decoding=True)
+        assert relerr(y, ref["decode3_cache"]) < TOL
+        cache.should_update = False
+        assert [cache.length_at(i) for i in range(cfg.n_layers)] == ref["len_after"]
+        assert cache.offsets == ref["offsets_after"]
+        cache.truncate(1, front=False)
+        y = O.dit_forward(xs[:, 4 * T:5 * T], conds[:, 4:5], W, cfg, fx["rope"], kv_cache=cache, decoding=True)
+        assert relerr(y, ref["decode4"]) < TOL
+        assert relerr(cache.cache[1][0], ref["k_layer1"]) < TOL
+        assert relerr(cache.cache[1][1], ref["v_layer1"]) < TOL
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_rope_tables_match_reference_construction(name):
+    """The package's own table builders (nn/rope.py) against the tables the reference code built."""
+    from owl_audio_exps_b200.nn.rope import get_rope_cls
+    fx = load_golden(name)
+    cfg = cfg_of(fx)
+    r = get_rope_cls(cfg.rope_impl)(cfg)
+    cos, sin = fx["rope"][0]
+    assert r.cos.shape == cos.shape and r.cos.dtype == torch.float32
+    assert (r.cos - cos).abs().max().item() < 1e-6
+    assert (r.sin - sin).abs().max().item() < 1e-6
+
+
+def test_frame_mask_matches_package_descriptor():
+    """oracle.frame_mask == FrameMask.mask_mod (the predicate the kernels evaluate) on ragged cases."""
+    from owl_audio_exps_b200.nn.attn import get_block_mask
+    for T, nq, off, win, causal in [(1, 24, 0, 4, True), (5, 30, 0, None, True), (5, 10, 15, 3, True),
+                                    (4, 32, 0, 2, False), (65, 130, 65, 16, True)]:
+        doc = torch.tensor([[0, 0, 1, 1, 1, 2, 2, 2, 2, 2][: (nq + off) // T + 1]]) if T in (4, 5) else None
+        if doc is not None and doc.shape[1] < (nq + off) // T:
+            doc = None
+        fm = get_block_mask(nq + off, T, win, doc, off, causal)
+        dense = fm.mask_mod(torch.tensor(0), torch.tensor(0), torch.arange(nq)[:, None], torch.arange(nq + off)[None, :])
+        ref = O.frame_mask(nq, nq + off, T, win, doc, off, causal)[0, 0]
+        assert torch.equal(dense, ref), (T, nq, off, win, causal)
