@@ -1,0 +1,187 @@
+"""Data-parallel training step for the DiT hot path: flat fp32 gradient buckets, all-reduce over
+NCCL/NVLink overlapped with the rest of backward, and the whole step replayed as one CUDA graph.
+
+Replaces what the reference gets from `DistributedDataParallel(model)` + `torch.compile`
+(owl_wms/trainers/rft_trainer.py:96-99, audio_rft_trainer.py:93) for this path:
+
+  * one bucket per DiT block (its 16 parameters, 18 d^2 + 15 d fp32 values) plus one for everything
+    else.  `param.grad` IS a view of the bucket, and the block's weight-gradient GEMMs / bias column
+    sums write straight into it (functional._wgrad sink), so there is no autograd copy and no
+    bucket-packing pass;
+  * a block's bucket is handed to NCCL on a side stream the moment that block's backward has
+    finished (blocks finish in reverse order), so the exchange of block i overlaps the backward of
+    blocks i-1..0.  NVSwitch gives every GPU full bandwidth to every peer, so bucket size is chosen for
+    overlap granularity (one block), not link count;
+  * launch-bound shapes (audio.yml: ~600 kernels of 5-50 us per step) are captured into a CUDA
+    graph -- the C ABI only enqueues on the current stream and never syncs, so capture is legal.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+f32 = torch.float32
+
+
+class GradSink:
+    """What functional._sink returns: the fp32 bucket view of one parameter + whether to add to it."""
+
+    __slots__ = ("view", "owner")
+
+    def __init__(self, view: torch.Tensor, owner: "GradBuckets"):
+        self.view, self.owner = view, owner
+
+    @property
+    def accumulate(self) -> bool:
+        return self.owner.accumulate
+
+
+def _align(n: int, a: int = 64) -> int:
+    return (n + a - 1) // a * a
+
+
+class GradBuckets:
+    def __init__(self, model: torch.nn.Module, process_group=None, comm_stream: Optional[torch.cuda.Stream] = None,
+                 average: bool = True):
+        from .nn.attn import DiTBlock
+        self.group = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.average = average
+        self.accumulate = False      # False on the first micro-batch of a step: sinks are overwritten, not added to
+        self._pending: List[int] = []
+        self.blocks: List[torch.nn.Module] = [m for m in model.modules() if isinstance(m, DiTBlock)]
+        groups: List[List[torch.nn.Parameter]] = []
+        seen = set()
+        for blk in self.blocks:
+            ps = [p for p in blk.parameters() if p.requires_grad]
+            groups.append(ps)
+            seen.update(id(p) for p in ps)
+        rest = [p for p in model.parameters() if p.requires_grad and id(p) not in seen]
+        self.rest_index = len(groups)
+        groups.append(rest)
+        self.flats: List[torch.Tensor] = []
+        dev = next(model.parameters()).device
+        for gi, ps in enumerate(groups):
+            n = sum(_align(p.numel()) for p in ps)
+            flat = torch.zeros(max(n, 1), device=dev, dtype=f32)
+            off = 0
+            for p in ps:
+                if p.dtype != f32:
+                    raise RuntimeError("GradBuckets needs fp32 master parameters (the autocast training regime)")
+                view = flat[off:off + p.numel()].view_as(p)
+                p.grad = view
+                if gi != self.rest_index:
+                    p._owl_grad_sink = GradSink(view, self)
+                off += _align(p.numel())
+            self.flats.append(flat)
+        self.is_cuda = dev.type == "cuda"
+        self.comm_stream = comm_stream if comm_stream is not None else (torch.cuda.Stream(dev) if self.is_cuda else None)
+        for i, blk in enumerate(self.blocks):
+            blk._stage.after_backward = (lambda i=i: self._block_done(i))
+        self.sync_grads = True       # set False on non-final accumulation micro-steps (DDP no_sync equivalent)
+
+    # ---- step protocol -------------------------------------------------------------------------
+    def begin_step(self):
+        """Call before the first micro-batch's forward."""
+        self.accumulate = False
+        self.flats[self.rest_index].zero_()   # these grads arrive through autograd's accumulate-in-place
+        self._pending.clear()
+
+    def next_micro_batch(self):
+        self.accumulate = True
+
+    def _reduce(self, flat: torch.Tensor):
+        if self.world == 1:
+            return
+        if self.is_cuda:
+            self.comm_stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.comm_stream):
+                dist.all_reduce(flat, op=dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM, group=self.group)
+        else:  # gloo (CPU tests of the host logic): no AVG op
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+            if self.average:
+                flat.div_(self.world)
+
+    def _block_done(self, i: int):
+        if self.sync_grads:
+            self._reduce(self.flats[i])
+
+    def finish_step(self):
+        """Call after backward: reduce the non-block bucket and join the communication stream."""
+        if self.sync_grads:
+            self._reduce(self.flats[self.rest_index])
+        if self.is_cuda and self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+
+    def grad_bytes(self) -> int:
+        return sum(f.numel() * 4 for f in self.flats)
+
+    def detach(self):
+        for blk in self.blocks:
+            blk._stage.after_backward = None
+            for p in blk.parameters():
+                if hasattr(p, "_owl_grad_sink"):
+                    del p._owl_grad_sink
+
+
+class TrainStep:
+    """fwd + bwd (+ bucketed all-reduce) of `loss_fn(model, *inputs)` with static input buffers; after
+    `warmup` eager runs the step is captured into a CUDA graph and replayed.
+
+    `inputs` given to __call__ may live on the host (pinned): they are copied into the static device
+    buffers on the step's stream, inside what the caller times."""
+
+    def __init__(self, model: torch.nn.Module, loss_fn: Callable, example_inputs: Sequence[torch.Tensor],
+                 buckets: Optional[GradBuckets] = None, use_graph: bool = True, warmup: int = 3):
+        self.model, self.loss_fn, self.buckets = model, loss_fn, buckets
+        self.static_in = [torch.empty_like(t, device=next(model.parameters()).device) for t in example_inputs]
+        for s, t in zip(self.static_in, example_inputs):
+            s.copy_(t)
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.loss: Optional[torch.Tensor] = None
+        self.launches_per_step = 0
+        if use_graph:
+            self._capture(warmup)
+
+    def _eager(self):
+        b = self.buckets
+        if b is not None:
+            b.begin_step()
+        else:
+            for p in self.model.parameters():
+                p.grad = None
+        loss = self.loss_fn(self.model, *self.static_in)
+        loss.backward()
+        if b is not None:
+            b.finish_step()
+        return loss.detach()
+
+    def _capture(self, warmup: int):
+        from . import ops
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup, 1)):
+                n0 = ops.launch_count()
+                self._eager()
+                self.launches_per_step = ops.launch_count() - n0
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = self._eager()
+
+    def __call__(self, *inputs: torch.Tensor) -> torch.Tensor:
+        for s, t in zip(self.static_in, inputs):
+            if t is not s:
+                s.copy_(t, non_blocking=True)
+        if self.graph is not None:
+            self.graph.replay()
+            return self.loss
+        from . import ops
+        n0 = ops.launch_count()
+        self.loss = self._eager()
+        self.launches_per_step = ops.launch_count() - n0
+        return self.loss

@@ -87,6 +87,7 @@ class WeightStage:
 
     def __init__(self):
         self._slots = {}
+        self.after_backward = None  # engine.GradBuckets: called when the owning block's backward is done
 
     def get(self, key: str, params, rows=None) -> torch.Tensor:
         """bf16 [sum(rows), K] concatenation of 2-D `params` (or fp32 concatenation of 1-D biases)."""
@@ -142,9 +143,10 @@ def _grad_like(g32: Optional[torch.Tensor], p: torch.Tensor):
     return g32 if p.dtype == f32 else g32.to(p.dtype)
 
 
-def _sink(p: torch.Tensor) -> Optional[torch.Tensor]:
-    """fp32 gradient sink installed by engine.GradBuckets: wgrad GEMMs accumulate straight into the
-    flat all-reduce bucket instead of materialising a gradient tensor for autograd to copy."""
+def _sink(p: torch.Tensor):
+    """engine.GradSink installed by engine.GradBuckets (.view = fp32 slice of the flat all-reduce bucket,
+    .accumulate = add or overwrite): wgrad GEMMs write straight into the bucket instead of
+    materialising a gradient tensor for autograd to copy."""
     return getattr(p, "_owl_grad_sink", None)
 
 
@@ -154,7 +156,7 @@ def _wgrad(dy: torch.Tensor, x: torch.Tensor, p: torch.Tensor, M: int) -> Option
     N, K = p.shape
     sink = _sink(p)
     if sink is not None:
-        ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=sink, accumulate=True)
+        ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=sink.view, accumulate=sink.accumulate)
         return None
     g = torch.empty(N, K, device=dy.device, dtype=f32)
     ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=g)
@@ -166,7 +168,7 @@ def _bgrad(dy: torch.Tensor, p: Optional[torch.Tensor]) -> Optional[torch.Tensor
         return None
     sink = _sink(p)
     if sink is not None:
-        ops.colsum(dy, sink, accumulate=True)
+        ops.colsum(dy, sink.view, accumulate=sink.accumulate)
         return None
     g = torch.empty(p.shape[0], device=dy.device, dtype=f32)
     ops.colsum(dy, g)
@@ -534,6 +536,7 @@ class DiTBlockFn(torch.autograd.Function):
                                   h2, z, s, y2, W["wqkv"], W["wout"], W["w1"], W["w2"], W["wc"], plan.cos, plan.sin, *P)
             ctx.meta = (B, L, d, R, T, offset, mask, x.dtype, cond.dtype, cond.shape,
                         None if scond is None else scond.shape)
+            ctx.stage = stage
         return x2.view(B, L, d) if x.dtype == bf16 else x2.view(B, L, d).to(x.dtype)
 
     @staticmethod
@@ -555,7 +558,7 @@ class DiTBlockFn(torch.autograd.Function):
         # ---- MLP branch: x2 = x1 + c2 * (s W2^T + b2)
         g_b2 = _fresh_or_sink(b2, need[np0 + 7])
         dy2 = ops.gate_bwd(dx2, y2, c2, dmod[:, 5 * d:6 * d], g_b2[0], T, dbias_accumulate=g_b2[1])
-        g_b2 = None if (g_b2[0] is None or g_b2[1]) else _grad_like(g_b2[0], b2)
+        g_b2 = None if (g_b2[0] is None or g_b2[2]) else _grad_like(g_b2[0], b2)
         dz = torch.empty(M, 4 * d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dy2, w216, M, 4 * d, d, mode=OWL_EPI_DSILU, aux0=z, out0=dz)
         g_w2 = _wgrad(dy2, s, w2, M) if need[np0 + 6] else None
@@ -571,7 +574,7 @@ class DiTBlockFn(torch.autograd.Function):
         # ---- attention branch: x1 = x + c1 * (o Wout^T + bout)
         g_bout = _fresh_or_sink(bout, need[np0 + 3])
         dy1 = ops.gate_bwd(dx1, y1, c1, dmod[:, 2 * d:3 * d], g_bout[0], T, dbias_accumulate=g_bout[1])
-        g_bout = None if (g_bout[0] is None or g_bout[1]) else _grad_like(g_bout[0], bout)
+        g_bout = None if (g_bout[0] is None or g_bout[2]) else _grad_like(g_bout[0], bout)
         do = torch.empty(B, L, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dy1, wout16, M, d, d, mode=OWL_EPI_STORE, out0=do)
         g_wout = _wgrad(dy1, o2, wout, M) if need[np0 + 2] else None
@@ -617,16 +620,18 @@ class DiTBlockFn(torch.autograd.Function):
         dx = dx.view(B, L, d)
         if xdtype != bf16:
             dx = dx.to(xdtype)
+        if ctx.stage.after_backward is not None:
+            ctx.stage.after_backward()
         return (dx if need[0] else None, dcond, dscond, None, None,
                 g_wqkv, g_bqkv, g_wout, g_bout, g_w1, g_b1, g_w2, g_b2,
                 g_wa1, g_ba1, g_wg1, g_bg1, g_wa2, g_ba2, g_wg2, g_bg2)
 
 
 def _fresh_or_sink(p: torch.Tensor, needed: bool):
-    """(fp32 destination for a fused bias column-sum, accumulate flag)."""
+    """(fp32 destination for a fused bias column-sum, accumulate flag, destination is a bucket sink)."""
     if not needed:
-        return None, False
+        return None, False, False
     sink = _sink(p)
     if sink is not None:
-        return sink, True
-    return torch.empty(p.shape[0], device=p.device, dtype=f32), False
+        return sink.view, sink.accumulate, True
+    return torch.empty(p.shape[0], device=p.device, dtype=f32), False, False

@@ -1,0 +1,262 @@
+"""Parity of the sm_100a DiT path (through the C ABI) against the reference's golden fixtures and
+against the CPU oracle at the configs' real shapes.  Bar (north_star): max relative error <= 2e-2 on
+activations and gradients, tensor-normalised (max|a-b| / max|b|), bf16."""
+import types
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import GOLDEN_CASES, audio_cfg, cfg_of, load_golden, relerr
+from oracle import dit_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+DEV = "cuda:0"
+
+
+def _nn():
+    import owl_audio_exps_b200.nn as N
+    return N
+
+
+def _build(cfg, state, rope, dtype=torch.float32):
+    """DiT with the fixture's weights and the fixture's RoPE tables (identical tables on both sides)."""
+    N = _nn()
+    model = N.DiT(cfg)
+    model.load_state_dict({k: v.float() for k, v in state.items()}, strict=True)
+    model = model.to(DEV).to(dtype)
+    for blk, (cos, sin) in zip(model.blocks, rope):
+        blk.attn.rope.cos = cos.to(DEV).float().contiguous()
+        blk.attn.rope.sin = sin.to(DEV).float().contiguous()
+    return model
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+@pytest.mark.parametrize("regime", ["fp32_params", "bf16_params"])
+def test_dit_golden(name, regime):
+    fx = load_golden(name)
+    cfg = cfg_of(fx)
+    model = _build(cfg, fx["state"], fx["rope"], torch.float32 if regime == "fp32_params" else torch.bfloat16)
+    x = fx["x"].to(DEV).requires_grad_(True)
+    cond = fx["cond"].to(DEV).requires_grad_(True)
+    doc = fx["doc_id"].to(DEV) if fx["doc_id"] is not None else None
+    y = model(x, cond, doc)
+    assert y.dtype == torch.bfloat16
+    assert relerr(y, fx["y"]) <= TOL
+    y.backward(fx["dy"].to(DEV))
+    assert relerr(x.grad, fx["dx"]) <= TOL
+    assert relerr(cond.grad, fx["dcond"]) <= TOL
+    worst = max((relerr(p.grad, fx["grads"][k]), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+    if regime == "fp32_params":
+        assert all(p.grad.dtype == torch.float32 for p in model.parameters())
+
+
+@pytest.mark.parametrize("name", ["audio_T1", "av_T5_ortho"])
+def test_standalone_modules_match_fused_block(name):
+    """DiTBlock assembled from the standalone AdaLN / Attn / Gate / MLP modules (the reference's own
+    forward, attn.py:130-143) == the fused schedule, forward and gradients."""
+    fx = load_golden(name)
+    cfg = cfg_of(fx)
+    model = _build(cfg, fx["state"], fx["rope"])
+    blk = model.blocks[1]
+    x = fx["x"].to(DEV).requires_grad_(True)
+    cond = fx["cond"].to(DEV).requires_grad_(True)
+    mask = model.get_block_mask(x.shape[1], None, cfg.local_window, 0, DEV)
+
+    def unfused(x, cond):
+        h = blk.adaln1(x, cond)
+        h = blk.attn(h, mask)
+        x = x + blk.gate1(h, cond)
+        h = blk.adaln2(x, cond)
+        h = blk.mlp(h)
+        return x + blk.gate2(h, cond)
+
+    y0 = blk(x, cond, mask)
+    g = torch.randn_like(y0)
+    y0.backward(g)
+    ref = {k: p.grad.clone() for k, p in blk.named_parameters()}
+    dx0, dc0 = x.grad.clone(), cond.grad.clone()
+    blk.zero_grad()
+    x.grad = cond.grad = None
+    y1 = unfused(x, cond)
+    y1.backward(g)
+    assert relerr(y1, y0) <= 1e-2
+    assert relerr(x.grad, dx0) <= 1.5e-2 and relerr(cond.grad, dc0) <= 1.5e-2
+    for k, p in blk.named_parameters():
+        assert relerr(p.grad, ref[k]) <= 1.5e-2, k
+
+
+def test_kv_rollout_golden():
+    """Prefill / cached-masked / decode / cache-update / truncate sequence of the reference, step by step."""
+    N = _nn()
+    fx = load_golden("kv_rollout")
+    cfg = cfg_of(fx)
+    model = _build(cfg, fx["state"], fx["rope"]).eval()
+    xs, conds, ref = fx["xs"].to(DEV), fx["conds"].to(DEV), fx["out"]
+    T = cfg.tokens_per_frame
+    with torch.no_grad():
+        cache = N.KVCache(cfg)
+        cache.reset(fx["B"])
+        cache.enable_cache_updates()
+        assert relerr(model(xs[:, :3 * T], conds[:, :3], None, cache), ref["prefill"]) <= TOL
+        cache.disable_cache_updates()
+        assert relerr(model(xs[:, 3 * T:4 * T], conds[:, 3:4], None, cache), ref["masked_cached"]) <= TOL
+        model.enable_decoding()
+        assert relerr(model(xs[:, 3 * T:4 * T], conds[:, 3:4], None, cache), ref["decode3"]) <= TOL
+        cache.enable_cache_updates()
+        assert relerr(model(xs[:, 3 * T:4 * T], conds[:, 3:4], None, cache), ref["decode3_cache"]) <= TOL
+        cache.disable_cache_updates()
+        assert [cache.length_at(i) for i in range(cfg.n_layers)] == ref["len_after"]
+        assert list(cache.offsets) == ref["offsets_after"]
+        cache.truncate(1, front=False)
+        assert relerr(model(xs[:, 4 * T:5 * T], conds[:, 4:5], None, cache), ref["decode4"]) <= TOL
+        k1, v1 = cache.cache[1]
+        assert relerr(k1, ref["k_layer1"]) <= TOL and relerr(v1, ref["v_layer1"]) <= TOL
+        assert tuple(cache.shape) == tuple(ref["k_layer1"].shape)
+
+
+def test_decode_backward_populates_grads():
+    """sanity/sf_sanity.py:32-53: decode-mode forward through the cache is differentiable; cached rows get no grad."""
+    N = _nn()
+    fx = load_golden("kv_rollout")
+    cfg = cfg_of(fx)
+    model = _build(cfg, fx["state"], fx["rope"])
+    xs, conds = fx["xs"].to(DEV), fx["conds"].to(DEV)
+    T = cfg.tokens_per_frame
+    cache = N.KVCache(cfg)
+    cache.reset(fx["B"])
+    with torch.no_grad():
+        cache.enable_cache_updates()
+        model(xs[:, :3 * T], conds[:, :3], None, cache)
+        cache.disable_cache_updates()
+    model.enable_decoding()
+    x = xs[:, 3 * T:4 * T].clone().requires_grad_(True)
+    y = model(x, conds[:, 3:4], None, cache)
+    # oracle gradient of the same decode step
+    W = {k: v.float().requires_grad_(True) for k, v in fx["state"].items()}
+    oc = O.OracleKVCache(cfg.n_layers, T)
+    with torch.no_grad():
+        oc.should_update = True
+        O.dit_forward(fx["xs"].float()[:, :3 * T], fx["conds"].float()[:, :3], W, cfg, fx["rope"], kv_cache=oc)
+        oc.should_update = False
+    xo = fx["xs"].float()[:, 3 * T:4 * T].clone().requires_grad_(True)
+    yo = O.dit_forward(xo, fx["conds"].float()[:, 3:4], W, cfg, fx["rope"], kv_cache=oc, decoding=True)
+    g = torch.randn(yo.shape, generator=torch.Generator().manual_seed(3)).to(torch.bfloat16)
+    yo.backward(g.float())
+    y.backward(g.to(DEV))
+    assert relerr(y, yo) <= TOL
+    assert relerr(x.grad, xo.grad) <= TOL
+    n_with_grad = sum(p.grad is not None for p in model.parameters())
+    assert n_with_grad == len(list(model.parameters()))
+    for k, p in model.named_parameters():
+        assert relerr(p.grad, W[k].grad) <= TOL, k
+
+
+def _oracle_weights(model):
+    return {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
+
+
+@pytest.mark.parametrize("B,L", [(1, 120), (2, 120)])
+def test_audio_yml_block_shapes_vs_oracle(B, L):
+    """configs/audio.yml geometry (d=1024, H=16, T=1, RoPE audio1d), 4 layers (global, local x3), random
+    init per the reference (mlp.py:13-20 + nn.Linear defaults), against the fp32 CPU oracle."""
+    N = _nn()
+    cfg = audio_cfg(n_layers=4)
+    torch.manual_seed(0)
+    model = N.DiT(cfg)
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(p.to(torch.bfloat16).float())
+    W = {k: v.requires_grad_(True) for k, v in _oracle_weights(model).items()}
+    rope = [(b.attn.rope.cos.clone(), b.attn.rope.sin.clone()) for b in model.blocks]
+    model = model.to(DEV)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(B, L, cfg.d_model, generator=g).to(torch.bfloat16)
+    cond = torch.randn(B, L, cfg.d_model, generator=g).to(torch.bfloat16)
+    dy = torch.randn(B, L, cfg.d_model, generator=g).to(torch.bfloat16)
+    xo, co = x.float().requires_grad_(True), cond.float().requires_grad_(True)
+    yo = O.dit_forward(xo, co, W, cfg, rope)
+    yo.backward(dy.float())
+    xg, cg = x.to(DEV).requires_grad_(True), cond.to(DEV).requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        y = model(xg, cg)
+    y.backward(dy.to(DEV))
+    assert relerr(y, yo) <= TOL
+    assert relerr(xg.grad, xo.grad) <= TOL and relerr(cg.grad, co.grad) <= TOL
+    worst = max((relerr(p.grad, W[k].grad), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+
+
+def test_av_shape_T65_vs_oracle():
+    """av_v5_8x8_sf / causvid block geometry scaled in width only: T=65 (8x8 video + 1 audio token),
+    16 frames, L=1040, window 16, ortho RoPE, d=256 (H=4, dh=64), 2 layers."""
+    N = _nn()
+    cfg = types.SimpleNamespace(d_model=256, n_heads=4, n_layers=2, tokens_per_frame=65, n_frames=16, sample_size=8,
+                                causal=True, has_audio=True, rope_impl="ortho", local_window=4, global_window=None,
+                                backbone="dit")
+    torch.manual_seed(1)
+    model = N.DiT(cfg)
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(p.to(torch.bfloat16).float())
+    W = {k: v.requires_grad_(True) for k, v in _oracle_weights(model).items()}
+    rope = [(b.attn.rope.cos.clone(), b.attn.rope.sin.clone()) for b in model.blocks]
+    model = model.to(DEV)
+    g = torch.Generator().manual_seed(1)
+    B, L = 2, 1040
+    x = torch.randn(B, L, 256, generator=g).to(torch.bfloat16)
+    cond = torch.randn(B, 16, 256, generator=g).to(torch.bfloat16)
+    dy = torch.randn(B, L, 256, generator=g).to(torch.bfloat16)
+    xo, co = x.float().requires_grad_(True), cond.float().requires_grad_(True)
+    yo = O.dit_forward(xo, co, W, cfg, rope)
+    yo.backward(dy.float())
+    xg, cg = x.to(DEV).requires_grad_(True), cond.to(DEV).requires_grad_(True)
+    y = model(xg, cg)
+    y.backward(dy.to(DEV))
+    assert relerr(y, yo) <= TOL
+    assert relerr(xg.grad, xo.grad) <= TOL and relerr(cg.grad, co.grad) <= TOL
+    worst = max((relerr(p.grad, W[k].grad), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+
+
+def test_gradient_checkpointing_same_grads():
+    """attn.py:187-188 (dit_v4_5B.yml: gradient_checkpointing true): recompute path == stored path."""
+    fx = load_golden("av_T5_ortho")
+    cfg = cfg_of(fx)
+    model = _build(cfg, fx["state"], fx["rope"]).train()
+    x = fx["x"].to(DEV).requires_grad_(True)
+    cond = fx["cond"].to(DEV).requires_grad_(True)
+    dy = fx["dy"].to(DEV)
+    model(x, cond).backward(dy)
+    ref = {k: p.grad.clone() for k, p in model.named_parameters()}
+    dx = x.grad.clone()
+    model.zero_grad()
+    x.grad = None
+    model.config.gradient_checkpointing = True
+    model(x, cond).backward(dy)
+    assert torch.equal(dx, x.grad)
+    for k, p in model.named_parameters():
+        assert torch.equal(p.grad, ref[k]), k
+
+
+def test_rms_eps_matches_torch():
+    """which eps does F.rms_norm(eps=None) use for bf16 CUDA tensors?  The kernels must match it."""
+    from owl_audio_exps_b200 import functional as OF
+    x = (torch.randn(64, 1024, device=DEV) * 3e-4).to(torch.bfloat16)
+    ref = F.rms_norm(x, (1024,))
+    got = OF.rms_norm(x)
+    assert relerr(got, ref) <= 1e-2
+    # and the value is distinguishable from the bf16-eps alternative on this input
+    alt = x.float() * torch.rsqrt(x.float().pow(2).mean(-1, keepdim=True) + torch.finfo(torch.bfloat16).eps)
+    assert relerr(alt, ref) > 5e-2
+
+
+def test_no_cpu_path():
+    N = _nn()
+    fx = load_golden("audio_T1")
+    cfg = cfg_of(fx)
+    model = N.DiT(cfg)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        model(fx["x"].float(), fx["cond"].float())
