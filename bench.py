@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""Benchmark of the DiT hot path: train tokens/s (fwd + bwd + gradient all-reduce of the DiT stack).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload audio|dit_v4|av] [--impl owl|reference]
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for what every field means.
+  value      whole-job tokens/s, inputs resident in HBM when the timed region starts (CUDA-graph replay)
+  e2e        same metric through the public call (DiT forward/backward via engine.TrainStep) with the
+             step's inputs in PINNED HOST memory: H2D copy of x/cond/target and D2H read of the loss
+             are inside the timed region, every step
+  roofline   the dominant kernel (tcgen05 GEMM for audio/av, tcgen05 attention for dit_v4) against the
+             measured bf16 peak: algorithmic FLOPs / CUDA-event time of its launches inside a step
+  cpu_baseline   the oracle port (oracle/dit_oracle.py, plain torch CPU) on the host cores, bounded sample
+--impl reference times that same CPU port as the reference arm (the reference is pure Python/PyTorch;
+its CPU path for this block IS torch CPU ops -- /root/reference does not exist on the GPU box).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+import types
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # configs/audio.yml: model section + train.batch_size 32, window 88200 samples / 735 = 120 latents
+    "audio": dict(cfg=dict(d_model=1024, n_heads=16, n_layers=16, tokens_per_frame=1, n_frames=10000, sample_size=120,
+                           causal=True, has_audio=True, rope_impl="audio1d", local_window=16, global_window=None,
+                           backbone="dit"), B=32, F=120, name="configs/audio.yml"),
+    # configs/dit_v4.yml: B=1, 1536 frames x 64 tokens
+    "dit_v4": dict(cfg=dict(d_model=1536, n_heads=24, n_layers=16, tokens_per_frame=64, n_frames=1536, sample_size=8,
+                            causal=True, has_audio=False, rope_impl="motion", rope_ats_delta=2.0, local_window=16,
+                            global_window=None, backbone="dit"), B=1, F=1536, name="configs/dit_v4.yml"),
+    # configs/av_v5_8x8_sf.yml block geometry (shape only): B=8, 16 frames x 65 tokens, 24 layers
+    "av": dict(cfg=dict(d_model=1536, n_heads=24, n_layers=24, tokens_per_frame=65, n_frames=16, sample_size=8,
+                        causal=True, has_audio=True, rope_impl="ortho", local_window=16, global_window=None,
+                        backbone="dit"), B=8, F=16, name="configs/av_v5_8x8_sf.yml (block geometry)"),
+}
+METRIC = "train tokens/sec (audio DiT stack fwd+bwd+grad all-reduce), whole job"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(tf=float(d["bf16_tflops"]), tf_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    hbm=float(d["hbm_gbs"]), src="measured (MEASURED_PEAKS.json, burst)")
+    return dict(tf=1590.0, tf_sustained=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        mx = max(float(r[1]) for r in self.rows if len(r) >= 7)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": mx, "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port timed on the host cores (cpu_baseline, and --impl reference)
+# ------------------------------------------------------------------------------------------------
+def cpu_port_step_time(workload, B, n_layers, steps, warmup, threads=None):
+    """Seconds per fwd+bwd of the DiT stack on CPU (fp32) via oracle.dit_forward; returns (s/step, tokens/step, sample)."""
+    from oracle import dit_oracle as O
+    import owl_audio_exps_b200.nn.rope as R
+    w = WORKLOADS[workload]
+    cfg = types.SimpleNamespace(**{**w["cfg"], "n_layers": n_layers})
+    F_ = w["F"] if workload != "dit_v4" else 32   # dense-mask SDPA is O(L^2): 98k tokens does not fit; 32 frames = 2048 tokens
+    L = F_ * cfg.tokens_per_frame
+    if threads:
+        torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    d = cfg.d_model
+    W = {}
+    for i in range(n_layers):
+        pre = f"blocks.{i}."
+        for name, (n, k) in {"attn.qkv": (3 * d, d), "attn.out": (d, d), "mlp.fc1": (4 * d, d), "mlp.fc2": (d, 4 * d),
+                             "adaln1.fc": (2 * d, d), "gate1.fc_c": (d, d), "adaln2.fc": (2 * d, d),
+                             "gate2.fc_c": (d, d)}.items():
+            W[pre + name + ".weight"] = (torch.randn(n, k) * k ** -0.5).requires_grad_(True)
+            W[pre + name + ".bias"] = torch.zeros(n, requires_grad=True)
+    rope = R.get_rope_cls(cfg.rope_impl)(cfg)
+    tables = [(rope.cos, rope.sin)] * n_layers
+    x = torch.randn(B, L, d)
+    cond = torch.randn(B, F_, d)
+    tgt = torch.randn(B, L, d)
+
+    def step():
+        for v in W.values():
+            v.grad = None
+        y = O.dit_forward(x, cond, W, cfg, tables)
+        torch.nn.functional.mse_loss(y, tgt).backward()
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    sample = f"{w['name']} DiT stack fwd+bwd, fp32 torch CPU, B={B}, L={L}, {n_layers} of {w['cfg']['n_layers']} layers"
+    return dt, B * L, sample, torch.get_num_threads()
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for the block (torch CPU ops via the oracle port)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    n_layers, B = 2, 1    # bounded sample: each step stays in the seconds range on any host
+    dt, toks, sample, cores = cpu_port_step_time(args.workload, B, n_layers, max(args.steps, 1), max(args.warmup, 1))
+    # per-layer cost is uniform: scale the measured layers to the full stack
+    dt_full = dt * w["cfg"]["n_layers"] / n_layers
+    val = toks / dt_full
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt_full * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": w["name"], "note": "CPU reference arm; time of measured layers scaled to the full depth"},
+        "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def loss_fn(model, x, cond, target):
+    y = model(x, cond)
+    return torch.nn.functional.mse_loss(y.float(), target.float())
+
+
+def run_owl(args):
+    import torch.distributed as dist
+    from owl_audio_exps_b200 import engine, ops
+    import owl_audio_exps_b200.nn as N
+    from oracle.dit_oracle import step_flops  # closed-form FLOP count only; no oracle compute here
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the sm_100a kernels are the only implementation)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w = WORKLOADS[args.workload]
+    cfg = types.SimpleNamespace(**w["cfg"])
+    if args.layers:
+        cfg.n_layers = args.layers
+    B, F_ = (args.batch or w["B"]), w["F"]
+    T, d = cfg.tokens_per_frame, cfg.d_model
+    L = F_ * T
+    torch.manual_seed(0)
+    model = N.DiT(cfg).to(dev)                       # fp32 master weights, reference init
+    n_params = sum(p.numel() for p in model.parameters())
+    buckets = engine.GradBuckets(model)
+    g = torch.Generator().manual_seed(1000 + rank)   # each rank draws its own batch (DistributedSampler analogue)
+    host = [torch.randn(B, L, d, generator=g).to(torch.bfloat16).pin_memory(),
+            torch.randn(B, F_, d, generator=g).to(torch.bfloat16).pin_memory(),
+            torch.randn(B, L, d, generator=g).to(torch.bfloat16).pin_memory()]
+    step = engine.TrainStep(model, loss_fn, host, buckets=buckets, use_graph=not args.no_graph, warmup=3)
+    h2d = sum(t.numel() * t.element_size() for t in host)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(n, from_host):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(n):
+            if from_host:
+                loss = step(*host)
+                _ = loss.item()                      # D2H read of the step's result, every step
+            else:
+                step(*step.static_in)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step(*step.static_in)
+    with ClockSampler(local) as clk:
+        ms = timed(args.steps, False)
+    for _ in range(2):
+        step(*host)
+    ms_e2e = timed(args.steps, True)
+    tokens = B * L * world
+    value = tokens * args.steps / (ms * 1e-3)
+    e2e = tokens * args.steps / (ms_e2e * 1e-3)
+
+    line = None
+    if rank == 0:
+        # ---- roofline of the dominant kernel: CUDA events around every launch of one eager step
+        fl = step_flops(B, L, d, T, cfg.n_layers, cfg.local_window, cfg.global_window)
+        eager = engine.TrainStep(model, loss_fn, host, buckets=buckets, use_graph=False)
+        eager(*step.static_in)
+        prof = None
+        for _ in range(3):
+            ops.profile_begin()
+            eager(*step.static_in)
+            prof = ops.profile_end()
+        gemm_ms = sum(v["ms"] for k, v in prof.items() if k.startswith("gemm"))
+        gemm_n = sum(v["n"] for k, v in prof.items() if k.startswith("gemm"))
+        att_ms = sum(v["ms"] for k, v in prof.items() if k.startswith("attn"))
+        att_n = sum(v["n"] for k, v in prof.items() if k.startswith("attn"))
+        total_ms = sum(v["ms"] for v in prof.values())
+        pk = _peaks()
+        gemm_tf = 3 * fl["linear_fwd"] / (gemm_ms * 1e-3) / 1e12
+        att_tf = 3.5 * fl["attn_fwd"] / (att_ms * 1e-3) / 1e12 if att_ms > 0 else 0.0
+        dom_gemm = gemm_ms >= att_ms
+        ach = gemm_tf if dom_gemm else att_tf
+        roofline = {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)" if dom_gemm else "attn fwd/bwd kernels (tcgen05)",
+                    "achieved": ach, "peak": pk["tf"], "unit": "TFLOP/s", "frac": ach / pk["tf"], "traffic": None,
+                    "peak_source": pk["src"], "launches_per_step": gemm_n if dom_gemm else att_n,
+                    "avg_launch_us": 1e3 * (gemm_ms / gemm_n if dom_gemm else att_ms / max(att_n, 1)),
+                    "share_of_step_kernel_time": (gemm_ms if dom_gemm else att_ms) / total_ms,
+                    "other": {"gemm_tflops": gemm_tf, "attn_tflops": att_tf,
+                              "kernel_ms_per_step": {k: round(v["ms"], 4) for k, v in sorted(prof.items())}}}
+        step_tf = fl["step"] * world * args.steps / (ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": w["name"], "per_gpu_batch": B, "tokens_per_sample": L, "d_model": d,
+                       "n_layers": cfg.n_layers, "n_heads": cfg.n_heads, "params": n_params, "parallelism": f"dp{world}",
+                       "step": "DiT stack fwd + bwd + fp32 grad all-reduce (bucket per block, overlapped); optimizer excluded",
+                       "cuda_graph": not args.no_graph,
+                       "l2": "per-step working set (weights+grads+activations, >4 GB) exceeds the 126 MB L2; no flush"},
+            "tokens_per_s_per_gpu": value / world,
+            "step_tflops_per_gpu": step_tf / world, "frac_of_bf16_peak_per_gpu": step_tf / world / pk["tf"],
+            "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": step.launches_per_step * args.steps,
+            "roofline": roofline, "clocks": clk.summary(),
+        }
+        if world == 1 and not args.no_cpu:
+            dt, toks, sample, cores = cpu_port_step_time(args.workload, 1, 2, 3, 1)
+            dt_full = dt * cfg.n_layers / 2
+            line["cpu_baseline"] = {"value": toks / dt_full, "unit": "tokens/s", "cores": cores, "kind": "port",
+                                    "sample": sample + "; scaled to full depth"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="owl", choices=["owl", "reference"])
+    ap.add_argument("--workload", default="audio", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--layers", type=int, default=0)
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_owl(args)
+
+
+if __name__ == "__main__":
+    main()

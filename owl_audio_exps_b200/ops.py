@@ -7,6 +7,7 @@ are allocated by the caller side (here) -- the library never allocates.
 from __future__ import annotations
 
 import ctypes as C
+import functools
 from typing import Optional
 
 import torch
@@ -49,8 +50,52 @@ def launch_count() -> int:
 
 
 # ------------------------------------------------------------------------------------------------
+# per-op CUDA-event timing (bench.py roofline / profiles): off unless profile_begin() was called
+# ------------------------------------------------------------------------------------------------
+_PROFILE = None
+
+
+def profile_begin():
+    global _PROFILE
+    _PROFILE = []
+
+
+def profile_end():
+    """-> {kind: {"ms": total, "n": launches, "flops": total algorithmic flops (GEMMs only)}}"""
+    global _PROFILE
+    rec, _PROFILE = _PROFILE, None
+    torch.cuda.synchronize()
+    out = {}
+    for kind, e0, e1, fl in rec or []:
+        d = out.setdefault(kind, {"ms": 0.0, "n": 0, "flops": 0.0})
+        d["ms"] += e0.elapsed_time(e1)
+        d["n"] += 1
+        d["flops"] += fl
+    return out
+
+
+def _prof(kind, flops=None):
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapped(*a, **k):
+            if _PROFILE is None:
+                return fn(*a, **k)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn(*a, **k)
+            e1.record()
+            kd = kind(*a, **k) if callable(kind) else kind
+            _PROFILE.append((kd, e0, e1, flops(*a, **k) if flops else 0.0))
+            return r
+        return wrapped
+    return deco
+
+
+# ------------------------------------------------------------------------------------------------
 # GEMM
 # ------------------------------------------------------------------------------------------------
+@_prof(lambda layout, *a, **k: ("gemm_nt", "gemm_nn", "gemm_tn")[layout],
+       lambda layout, a, b, M, N, K, **k: 2.0 * M * N * K)
 def gemm(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, *, mode: int = OWL_EPI_STORE,
          bias: Optional[torch.Tensor] = None, out0: Optional[torch.Tensor] = None,
          out1: Optional[torch.Tensor] = None, outf: Optional[torch.Tensor] = None,
@@ -96,6 +141,7 @@ def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None
 # ------------------------------------------------------------------------------------------------
 # memory-bound ops
 # ------------------------------------------------------------------------------------------------
+@_prof("cast_f32_bf16")
 def cast_f32_bf16(src: torch.Tensor, dst: Optional[torch.Tensor] = None) -> torch.Tensor:
     _req(src, torch.float32)
     if dst is None:
@@ -104,6 +150,7 @@ def cast_f32_bf16(src: torch.Tensor, dst: Optional[torch.Tensor] = None) -> torc
     return dst
 
 
+@_prof("silu")
 def silu(x: torch.Tensor) -> torch.Tensor:
     _req(x)
     y = torch.empty_like(x)
@@ -111,6 +158,7 @@ def silu(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+@_prof("dsilu_mul")
 def dsilu_mul(dy: torch.Tensor, z: torch.Tensor, dz: torch.Tensor) -> torch.Tensor:
     _req(dy), _req(z), _req(dz)
     _lib.check(_lib.load().owl_dsilu_mul_bf16(dy.data_ptr(), z.data_ptr(), dz.data_ptr(), z.numel(), _stream()),
@@ -118,6 +166,7 @@ def dsilu_mul(dy: torch.Tensor, z: torch.Tensor, dz: torch.Tensor) -> torch.Tens
     return dz
 
 
+@_prof("adaln_modulate_fwd")
 def adaln_modulate_fwd(x, a, b, T: int, eps: float, want_rstd: bool = True):
     """h = rms_norm(x) * (1 + a[frame]) + b[frame]; x [M,d]; a,b [M/T,d] column slices (or None)."""
     _req(x)
@@ -131,6 +180,7 @@ def adaln_modulate_fwd(x, a, b, T: int, eps: float, want_rstd: bool = True):
     return h, rstd
 
 
+@_prof("adaln_modulate_bwd")
 def adaln_modulate_bwd(dh, x, a, rstd, dres, da, db, T: int):
     """Returns dx; writes da, db (views with a row stride) in place."""
     M, d, _ = _rows(x)
@@ -143,6 +193,7 @@ def adaln_modulate_bwd(dh, x, a, rstd, dres, da, db, T: int):
     return dx
 
 
+@_prof("gate_fwd")
 def gate_fwd(x, c, res, T: int):
     M, d, _ = _rows(x)
     out = torch.empty_like(x)
@@ -151,6 +202,7 @@ def gate_fwd(x, c, res, T: int):
     return out
 
 
+@_prof("gate_bwd")
 def gate_bwd(dx, y, c, dc, dbias, T: int, dbias_accumulate: bool = False):
     """dy = dx * c[frame]; dc[frame] = sum dx*y (written in place); dbias (+)= colsum(dy)."""
     M, d, _ = _rows(dx)
@@ -162,6 +214,7 @@ def gate_bwd(dx, y, c, dc, dbias, T: int, dbias_accumulate: bool = False):
     return dy
 
 
+@_prof("colsum")
 def colsum(x, out, accumulate: bool = False):
     M, N, ld = _rows(x)
     _lib.check(_lib.load().owl_colsum_bf16(x.data_ptr(), ld, out.data_ptr(), int(accumulate), M, N, _stream()),
@@ -169,6 +222,7 @@ def colsum(x, out, accumulate: bool = False):
     return out
 
 
+@_prof("layer_norm")
 def layer_norm(x, eps: float = 1e-5):
     M, d, _ = _rows(x)
     y = torch.empty_like(x)
@@ -176,6 +230,7 @@ def layer_norm(x, eps: float = 1e-5):
     return y
 
 
+@_prof("qk_norm_rope_fwd")
 def qk_norm_rope_fwd(qkv, cos, sin, pos_offset: int, H: int, eps: float, q, k, v, want_rstd: bool = True):
     """qkv [B,L,3*H*dh] -> q,k,v written into caller views [B,H,L,dh] (dh contiguous, L stride dh)."""
     B, L, three_d = qkv.shape
@@ -192,6 +247,7 @@ def qk_norm_rope_fwd(qkv, cos, sin, pos_offset: int, H: int, eps: float, q, k, v
     return rq, rk
 
 
+@_prof("qk_norm_rope_bwd")
 def qk_norm_rope_bwd(dq, dk, dv, q, k, rq, rk, cos, sin, pos_offset: int):
     """dq/dk/dv share strides ([B,H,L,dh]); returns dqkv [B,L,3*H*dh]."""
     B, H, L, dh = dq.shape
@@ -205,6 +261,7 @@ def qk_norm_rope_bwd(dq, dk, dv, q, k, rq, rk, cos, sin, pos_offset: int):
     return dqkv
 
 
+@_prof("rope_apply")
 def rope_apply(x, cos, sin, pos_offset: int, inverse: bool = False):
     """x contiguous bf16 [..., L, dh] -> rotated copy (see owl_rope_apply)."""
     _req(x)
@@ -216,6 +273,7 @@ def rope_apply(x, cos, sin, pos_offset: int, inverse: bool = False):
     return y
 
 
+@_prof("kv_append")
 def kv_append(src, cache, pos: int):
     B, H, Ln, dh = src.shape
     rc = _lib.load().owl_kv_append(src.data_ptr(), src.stride(0), src.stride(1), cache.data_ptr(), cache.stride(0),
@@ -243,6 +301,7 @@ def _hm(t: torch.Tensor):
     return t.data_ptr(), t.stride(0), t.stride(1)
 
 
+@_prof("attn_fwd")
 def attn_fwd(q, k, v, *, tokens_per_frame: int, window_frames: int = 0, q_offset: int = 0, causal: bool = True,
              doc_id=None, want_lse: bool = True, check: bool = False):
     """q [B,H,Lq,dh], k/v [B,H,Lk,dh] -> o [B,Lq,H*dh] (token-major, ready for the out Linear), lse [B,H,Lq]."""
@@ -259,6 +318,7 @@ def attn_fwd(q, k, v, *, tokens_per_frame: int, window_frames: int = 0, q_offset
     return o, lse
 
 
+@_prof("attn_bwd")
 def attn_bwd(dout, o, q, k, v, lse, *, tokens_per_frame: int, window_frames: int = 0, q_offset: int = 0,
              causal: bool = True, doc_id=None, check: bool = False, dq=None, dk=None, dv=None):
     """Returns (dq, dk, dv) in [B,H,L,dh]."""
