@@ -67,7 +67,7 @@ enum {
   /* out0 = bf16(aux0[m,n] + aux1[m / rows_per_frame, n] * y)        (modulation.py:41-43 +       */
   /*                                                                  attn.py:135,141 residual)   */
   OWL_EPI_GATE_RESIDUAL = 2,
-  /* g = acc * silu'(aux0[m,n]); out0 = bf16(g) if out0 else outf (+)= g                          */
+  /* out0 = bf16(acc * silu'(aux0[m,n]))   (bf16 destination only)                                 */
   /*                                   (backward of F.silu, mlp.py:35 / modulation.py:17,38)      */
   OWL_EPI_DSILU = 3,
   /* outf[m,n] (fp32) = acc (+ outf[m,n] if accumulate)              (weight gradients)           */

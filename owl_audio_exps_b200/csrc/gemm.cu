@@ -26,33 +26,29 @@ namespace owl {
 static constexpr int BM = 128;
 static constexpr int BK = 64;
 static constexpr int kGemmThreads = 256;
+static constexpr int kSlotBytes = 16384;   // one staging panel: 128 rows x 128 bytes, 128B-swizzled
+static constexpr int kBarRegion = 1024;    // mbarriers + TMEM slot at the front of dynamic smem
+static constexpr int kMaxStages = 8;
+static constexpr int kSmemLimit = 232448;  // 227 KB opt-in maximum per CTA
 
 struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, splits, kb_per_split, kb_total;
-  int mode, accumulate, rows_per_frame, atomic_out;
+  int mode, rows_per_frame;
+  int stages;      // depth of the operand ring (runtime: whatever the staging panels leave free)
+  int f32_reduce;  // fp32 output goes out as TMA reduce-add (accumulate / split-K) instead of a store
+  int has_out1, aux0_tma, aux1_tma;
   const float* bias;
-  bf16* out0;
-  long long ld0;
-  bf16* out1;
-  long long ld1;
-  float* outf;
-  long long ldf;
-  const bf16* aux0;
-  long long lda0;
-  const bf16* aux1;
+  const bf16* aux1;  // gate rows for rows_per_frame > 1 (read directly: 32 consecutive rows share <= 2 gate rows)
   long long lda1;
 };
 
 template <int BN>
 struct GemmCfg {
-  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
-  // ring + barriers (full, empty per stage; tmem full/empty x2) + tmem slot, + 1024 alignment slack
-  static constexpr int kSmemBytes = kStages * kStageBytes + (2 * kStages + 4) * 8 + 16 + 1024;
 };
 
 __device__ __forceinline__ float silu_f(float z) { return z * sigmoidf_fast(z); }
@@ -60,102 +56,41 @@ __device__ __forceinline__ float dsilu_f(float z) {
   const float s = sigmoidf_fast(z);
   return s * (1.f + z * (1.f - s));
 }
-
-__device__ __forceinline__ void load8_bf16(const bf16* p, float (&f)[8]) {
-  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+__device__ __forceinline__ void unpack8u(const uint4& v, float (&f)[8]) {
   f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
   f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
 }
-__device__ __forceinline__ void store8_bf16(bf16* p, const float (&f)[8]) {
+__device__ __forceinline__ uint4 pack8u(const float (&f)[8]) {
   uint4 v;
   v.x = pack_bf16(f[0], f[1]); v.y = pack_bf16(f[2], f[3]); v.z = pack_bf16(f[4], f[5]); v.w = pack_bf16(f[6], f[7]);
-  *reinterpret_cast<uint4*>(p) = v;
+  return v;
 }
+// byte offset of 16-byte chunk c (0..7) of row r inside a 128B-swizzled [128][128 B] panel
+__device__ __forceinline__ uint32_t panel_off(int r, int c) { return r * 128 + ((c ^ (r & 7)) << 4); }
 
-// Epilogue for 8 consecutive columns [col, col+8) of output row `row`; acc holds the fp32 accumulators.
-__device__ __forceinline__ void epilogue8(const GemmParams& p, long long row, int col, float (&acc)[8]) {
-  if (p.bias != nullptr) {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-    acc[0] += b0.x; acc[1] += b0.y; acc[2] += b0.z; acc[3] += b0.w;
-    acc[4] += b1.x; acc[5] += b1.y; acc[6] += b1.z; acc[7] += b1.w;
-  }
-  switch (p.mode) {
-    case OWL_EPI_STORE: {
-      store8_bf16(p.out0 + row * p.ld0 + col, acc);
-      break;
-    }
-    case OWL_EPI_BIAS_SILU: {
-      float s[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        acc[j] = round_bf16(acc[j]);  // the reference's Linear output is bf16 before F.silu (mlp.py:34-35)
-        s[j] = silu_f(acc[j]);
-      }
-      store8_bf16(p.out0 + row * p.ld0 + col, acc);
-      store8_bf16(p.out1 + row * p.ld1 + col, s);
-      break;
-    }
-    case OWL_EPI_GATE_RESIDUAL: {
-      float r[8], g[8];
-      load8_bf16(p.aux0 + row * p.lda0 + col, r);
-      load8_bf16(p.aux1 + (row / p.rows_per_frame) * p.lda1 + col, g);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = round_bf16(acc[j]);
-      if (p.out1 != nullptr) store8_bf16(p.out1 + row * p.ld1 + col, acc);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) r[j] += g[j] * acc[j];
-      store8_bf16(p.out0 + row * p.ld0 + col, r);
-      break;
-    }
-    case OWL_EPI_DSILU: {
-      float z[8];
-      load8_bf16(p.aux0 + row * p.lda0 + col, z);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] *= dsilu_f(z[j]);
-      if (p.out0 != nullptr) {
-        store8_bf16(p.out0 + row * p.ld0 + col, acc);
-        break;
-      }
-    }  // fallthrough: fp32 destination
-    case OWL_EPI_F32: {
-      float* o = p.outf + row * p.ldf + col;
-      if (p.atomic_out) {
-        atomicAdd(reinterpret_cast<float4*>(o), make_float4(acc[0], acc[1], acc[2], acc[3]));
-        atomicAdd(reinterpret_cast<float4*>(o + 4), make_float4(acc[4], acc[5], acc[6], acc[7]));
-      } else {
-        float4 v0 = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        float4 v1 = make_float4(acc[4], acc[5], acc[6], acc[7]);
-        if (p.accumulate) {
-          const float4 o0 = *reinterpret_cast<const float4*>(o);
-          const float4 o1 = *reinterpret_cast<const float4*>(o + 4);
-          v0.x += o0.x; v0.y += o0.y; v0.z += o0.z; v0.w += o0.w;
-          v1.x += o1.x; v1.y += o1.y; v1.z += o1.z; v1.w += o1.w;
-        }
-        *reinterpret_cast<float4*>(o) = v0;
-        *reinterpret_cast<float4*>(o + 4) = v1;
-      }
-      break;
-    }
-    default: break;
-  }
-}
-
+// Persistent warp-specialised GEMM.  Epilogue: each of the 128 epilogue threads owns one accumulator row
+// (the tcgen05.ld 32x32b layout); results are packed into a 128B-swizzled shared-memory panel and leave the
+// SM as ONE TMA store per 128x64 (bf16) / 128x32 (fp32) panel, so global writes are full 128-byte lines.
+// Residual / pre-activation / gate operands arrive the same way (TMA load, prefetched one panel ahead).
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
+                 const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                  const GemmParams p) {
   using Cfg = GemmCfg<BN>;
-  constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + kStages * Cfg::kABytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
-  uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* tfull_bar = empty_bar + kMaxStages;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* aux_bar = tempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 2);
+  const int kStages = p.stages;
+  uint8_t* smem_a = smem + kBarRegion;
+  uint8_t* smem_b = smem_a + kStages * Cfg::kABytes;
+  uint8_t* stag = smem_b + kStages * Cfg::kBBytes;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -163,6 +98,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO0);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -172,6 +108,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 128);
+      mbar_init(&aux_bar[s], 1);
     }
     fence_barrier_init();
   }
@@ -252,39 +189,135 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4) {
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int q = warp & 3;           // TMEM lane quarter this warp may access
+    const int r = q * 32 + lane;      // row inside the tile
+    const bool leader = threadIdx.x == 128;
+    const bool f32out = p.mode == OWL_EPI_F32;
+    const bool has_aux = (p.aux0_tma | p.aux1_tma) != 0;
+    const int P = f32out ? BN / 32 : BN / 64;  // panels per tile
+    const int pcols = f32out ? 32 : 64;
+    uint8_t* s_out0 = stag;
+    uint8_t* s_out1 = stag + kSlotBytes;
+    uint8_t* s_aux0 = stag + (1 + p.has_out1) * kSlotBytes;                // two slots
+    uint8_t* s_aux1 = s_aux0 + (p.aux0_tma ? 2 : 0) * kSlotBytes;          // two slots
+    const uint32_t aux_bytes = static_cast<uint32_t>((p.aux0_tma + p.aux1_tma) * kSlotBytes);
+    auto issue_aux = [&](int t, int pn, int g) {  // leader only
+      const int m0 = (t % p.tiles_m) * BM, n0 = ((t / p.tiles_m) % p.tiles_n) * BN + pn * 64;
+      const int s = g & 1;
+      mbar_arrive_expect_tx(&aux_bar[s], aux_bytes);
+      if (p.aux0_tma) tma_load_2d(s_aux0 + s * kSlotBytes, &tmX0, &aux_bar[s], n0, m0);
+      if (p.aux1_tma) tma_load_2d(s_aux1 + s * kSlotBytes, &tmX1, &aux_bar[s], n0, m0);
+    };
     int as = 0;
     uint32_t aphase = 0;
+    int g = 0;  // running panel counter (aux slot / parity)
+    if (leader && has_aux && static_cast<int>(blockIdx.x) < total_tiles) issue_aux(blockIdx.x, 0, 0);
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int tm = t % p.tiles_m;
       const int tn = (t / p.tiles_m) % p.tiles_n;
       const int m0 = tm * BM, n0 = tn * BN;
-      const long long row = m0 + q * 32 + lane;
+      const long long row = m0 + r;
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        if (row < p.M) {
+      for (int pn = 0; pn < P; ++pn, ++g) {
+        if (leader && has_aux) {  // prefetch the next panel's operands
+          if (pn + 1 < P) issue_aux(t, pn + 1, g + 1);
+          else if (t + static_cast<int>(gridDim.x) < total_tiles) issue_aux(t + gridDim.x, 0, g + 1);
+        }
+        uint32_t acc[64];
+        {
+          uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&acc[0]);
+          tmem_ld_x32(taddr + pn * pcols, lo);
+          if (!f32out) {
+            uint32_t (&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&acc[32]);
+            tmem_ld_x32(taddr + pn * pcols + 32, hi);
+          }
+          tmem_ld_wait();
+        }
+        if (pn == P - 1) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          tc_fence_before();
+          mbar_arrive(&tempty_bar[as]);
+        }
+        if (has_aux) mbar_wait(&aux_bar[g & 1], (g >> 1) & 1);
+        const int c0 = n0 + pn * pcols;
+        uint4 o0[8], o1[8];
+        if (f32out) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            const int col = n0 + c * 32 + g * 8;
-            if (col < p.N) {
-              float acc[8];
+          for (int c = 0; c < 8; ++c) o0[c] = make_uint4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+        } else {
+          const uint8_t* x0 = s_aux0 + (g & 1) * kSlotBytes;
+          const uint8_t* x1 = s_aux1 + (g & 1) * kSlotBytes;
 #pragma unroll
-              for (int j = 0; j < 8; ++j) acc[j] = __uint_as_float(r[g * 8 + j]);
-              epilogue8(p, row, col, acc);
+          for (int c = 0; c < 8; ++c) {
+            const int col = c0 + c * 8;
+            float a[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = __uint_as_float(acc[c * 8 + j]);
+            if (p.bias != nullptr && col < p.N) {
+              const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+              const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+              a[0] += b0.x; a[1] += b0.y; a[2] += b0.z; a[3] += b0.w;
+              a[4] += b1.x; a[5] += b1.y; a[6] += b1.z; a[7] += b1.w;
+            }
+            if (p.mode == OWL_EPI_STORE) {
+              o0[c] = pack8u(a);
+            } else if (p.mode == OWL_EPI_BIAS_SILU) {
+              float sv[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                a[j] = round_bf16(a[j]);  // the reference's Linear output is bf16 before F.silu (mlp.py:34-35)
+                sv[j] = silu_f(a[j]);
+              }
+              o0[c] = pack8u(a);
+              o1[c] = pack8u(sv);
+            } else if (p.mode == OWL_EPI_GATE_RESIDUAL) {
+              float res[8], gt[8];
+              unpack8u(*reinterpret_cast<const uint4*>(x0 + panel_off(r, c)), res);
+              if (p.aux1_tma) {
+                unpack8u(*reinterpret_cast<const uint4*>(x1 + panel_off(r, c)), gt);
+              } else if (row < p.M && col < p.N) {
+                unpack8u(__ldg(reinterpret_cast<const uint4*>(p.aux1 + (row / p.rows_per_frame) * p.lda1 + col)), gt);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) gt[j] = 0.f;
+              }
+#pragma unroll
+              for (int j = 0; j < 8; ++j) a[j] = round_bf16(a[j]);
+              o1[c] = pack8u(a);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) res[j] += gt[j] * a[j];
+              o0[c] = pack8u(res);
+            } else {  // OWL_EPI_DSILU
+              float z[8];
+              unpack8u(*reinterpret_cast<const uint4*>(x0 + panel_off(r, c)), z);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) a[j] *= dsilu_f(z[j]);
+              o0[c] = pack8u(a);
             }
           }
         }
+        if (leader) tma_store_wait_read0();  // the previous panel's stores have drained the staging slots
+        named_bar_sync(1, 128);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = o0[c];
+        if (p.has_out1) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = o1[c];
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (leader && c0 < p.N) {
+          if (p.f32_reduce) tma_reduce_add_2d(&tmO0, s_out0, c0, m0);
+          else tma_store_2d(&tmO0, s_out0, c0, m0);
+          if (p.has_out1) tma_store_2d(&tmO1, s_out1, c0, m0);
+          tma_store_commit();
+        }
       }
-      tc_fence_before();
-      mbar_arrive(&tempty_bar[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    if (leader) tma_store_wait_all0();
   }
 
   tc_fence_before();
@@ -315,30 +348,51 @@ __global__ void gemm_check_kernel(int layout, int M, int N, int K, const bf16* _
   }
 }
 
+struct GemmMaps {
+  CUtensorMap A, B, O0, O1, X0, X1;
+};
+
 template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid,
-                       cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
-  static bool configured = false;  // idempotent attribute; a benign race at worst sets it twice
-  if (!configured) {
+static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
+  static int configured = 0;  // largest size configured so far; a benign race at worst sets it twice
+  if (configured < smem_bytes) {
     cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         Cfg::kSmemBytes);
+                                         kSmemLimit);
     if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
+    configured = kSmemLimit;
   }
-  gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, kGemmThreads, smem_bytes, stream>>>(tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
   return launch_status();
 }
 
 template <int BN>
-static int launch_gemm_layout(int layout, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid,
+static int launch_gemm_layout(int layout, const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes,
                               cudaStream_t stream) {
   switch (layout) {
-    case OWL_GEMM_NT: return launch_gemm<BN, false, false>(tmA, tmB, p, grid, stream);
-    case OWL_GEMM_NN: return launch_gemm<BN, false, true>(tmA, tmB, p, grid, stream);
-    case OWL_GEMM_TN: return launch_gemm<BN, true, true>(tmA, tmB, p, grid, stream);
+    case OWL_GEMM_NT: return launch_gemm<BN, false, false>(tm, p, grid, smem_bytes, stream);
+    case OWL_GEMM_NN: return launch_gemm<BN, false, true>(tm, p, grid, smem_bytes, stream);
+    case OWL_GEMM_TN: return launch_gemm<BN, true, true>(tm, p, grid, smem_bytes, stream);
     default: return OWL_ERR_BAD_ARG;
   }
+}
+
+// Tile width by a wave-quantisation model: time ~ waves x (per-tile main loop + fixed per-tile cost).
+// Narrow tiles pay more shared-memory bandwidth per flop (eff) but quantise better on 148 SMs.
+static int pick_bn(int tiles_m, long long N, int max_bn, int sms) {
+  int best = 64;
+  double best_cost = 1e30;
+  const int cand[3] = {256, 128, 64};
+  const double eff[3] = {1.0, 1.12, 1.45};
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cand[i];
+    if (bn > max_bn) continue;
+    if (bn > 64 && N <= bn / 2) continue;  // mostly padding
+    const long long tiles = static_cast<long long>(tiles_m) * ((N + bn - 1) / bn);
+    const long long waves = (tiles + sms - 1) / sms;
+    const double cost = static_cast<double>(waves) * (bn * eff[i] + 24.0);
+    if (cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
 }
 
 }  // namespace owl
@@ -360,56 +414,58 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
 
   GemmParams p{};
   p.M = static_cast<int>(M); p.N = static_cast<int>(N); p.K = static_cast<int>(K);
-  p.mode = epi->mode; p.accumulate = epi->accumulate; p.rows_per_frame = epi->rows_per_frame > 0 ? epi->rows_per_frame : 1;
+  p.mode = epi->mode;
+  p.rows_per_frame = epi->rows_per_frame > 0 ? epi->rows_per_frame : 1;
   p.bias = epi->bias;
-  p.out0 = static_cast<bf16*>(epi->out0); p.ld0 = epi->ld0;
-  p.out1 = static_cast<bf16*>(epi->out1); p.ld1 = epi->ld1;
-  p.outf = epi->outf; p.ldf = epi->ldf;
-  p.aux0 = static_cast<const bf16*>(epi->aux0); p.lda0 = epi->lda0;
-  p.aux1 = static_cast<const bf16*>(epi->aux1); p.lda1 = epi->lda1;
+  const void* out0 = epi->out0;
+  const void* out1 = epi->out1;
+  const void* aux0 = epi->aux0;
+  const void* aux1 = epi->aux1;
 
   // per-mode argument validation
   bool f32_out = false;
   switch (p.mode) {
     case OWL_EPI_STORE:
-      if (!p.out0) return OWL_ERR_BAD_ARG;
+      if (!out0) return OWL_ERR_BAD_ARG;
+      out1 = nullptr;
       break;
     case OWL_EPI_BIAS_SILU:
-      if (!p.out0 || !p.out1) return OWL_ERR_BAD_ARG;
+      if (!out0 || !out1) return OWL_ERR_BAD_ARG;
       break;
     case OWL_EPI_GATE_RESIDUAL:
-      if (!p.out0 || !p.aux0 || !p.aux1) return OWL_ERR_BAD_ARG;
+      if (!out0 || !aux0 || !aux1) return OWL_ERR_BAD_ARG;
       if (M % p.rows_per_frame) return OWL_ERR_BAD_ARG;
       break;
     case OWL_EPI_DSILU:
-      if (!p.aux0 || (!p.out0 && !p.outf)) return OWL_ERR_BAD_ARG;
-      f32_out = p.out0 == nullptr;
+      if (!aux0) return OWL_ERR_BAD_ARG;
+      if (!out0) return OWL_ERR_UNSUPPORTED;  // fp32 destination for the silu' epilogue is not implemented
+      out1 = nullptr;
       break;
     case OWL_EPI_F32:
-      if (!p.outf) return OWL_ERR_BAD_ARG;
+      if (!epi->outf) return OWL_ERR_BAD_ARG;
       f32_out = true;
+      out1 = nullptr;
       break;
     default: return OWL_ERR_BAD_ARG;
   }
-  if ((p.out0 && (p.ld0 % 8 || !aligned16(p.out0))) || (p.out1 && (p.ld1 % 8 || !aligned16(p.out1))) ||
-      (p.outf && (p.ldf % 4 || !aligned16(p.outf))) || (p.aux0 && (p.lda0 % 8 || !aligned16(p.aux0))) ||
-      (p.aux1 && (p.lda1 % 8 || !aligned16(p.aux1))) || (p.bias && !aligned16(p.bias)))
+  if ((out0 && !f32_out && (epi->ld0 % 8 || !aligned16(out0))) || (out1 && (epi->ld1 % 8 || !aligned16(out1))) ||
+      (f32_out && (epi->ldf % 4 || !aligned16(epi->outf))) || (aux0 && (epi->lda0 % 8 || !aligned16(aux0))) ||
+      (aux1 && (epi->lda1 % 8 || !aligned16(aux1))) || (p.bias && !aligned16(p.bias)))
     return OWL_ERR_ALIGN;
+  const bool uses_aux = p.mode == OWL_EPI_GATE_RESIDUAL || p.mode == OWL_EPI_DSILU;
+  p.has_out1 = out1 != nullptr;
+  p.aux0_tma = uses_aux ? 1 : 0;
+  p.aux1_tma = (p.mode == OWL_EPI_GATE_RESIDUAL && p.rows_per_frame == 1) ? 1 : 0;
+  p.aux1 = static_cast<const bf16*>(aux1);
+  p.lda1 = epi->lda1;
 
-  // tile shape: widest BN that still gives every SM a tile
   const int sms = sm_count();
   const int tiles_m = static_cast<int>((M + BM - 1) / BM);
-  int bn = 256;
-  if (N <= 64) bn = 64;
-  else if (N <= 128) bn = 128;
-  else {
-    const long long t256 = static_cast<long long>(tiles_m) * ((N + 255) / 256);
-    if (t256 < sms || N % 256 != 0) bn = 128;
-  }
+  const int bn = pick_bn(tiles_m, N, uses_aux ? 128 : 256, sms);
   const int tiles_n = static_cast<int>((N + bn - 1) / bn);
   const int kb_total = static_cast<int>((K + BK - 1) / BK);
   int splits = 1;
-  if (p.mode == OWL_EPI_F32) {
+  if (f32_out) {
     const int mn_tiles = tiles_m * tiles_n;
     if (mn_tiles < sms && kb_total >= 8) {
       splits = (sms + mn_tiles - 1) / mn_tiles;
@@ -421,30 +477,50 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   int kb_per_split = (kb_total + splits - 1) / splits;
   splits = (kb_total + kb_per_split - 1) / kb_per_split;  // no empty splits
   p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per_split; p.kb_total = kb_total;
-  p.atomic_out = (f32_out && splits > 1) ? 1 : 0;
+  p.f32_reduce = (f32_out && (splits > 1 || epi->accumulate)) ? 1 : 0;
+
+  // shared memory: barrier region + operand ring + staging panels
+  const int n_slots = 1 + p.has_out1 + 2 * p.aux0_tma + 2 * p.aux1_tma;
+  const int stage_bytes = BM * BK * 2 + bn * BK * 2;
+  int stages = (kSmemLimit - 1024 - kBarRegion - n_slots * kSlotBytes) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > kb_per_split + 1) stages = kb_per_split + 1;
+  if (stages < 2) return OWL_ERR_UNSUPPORTED;
+  p.stages = stages;
+  const int smem_bytes = 1024 + kBarRegion + stages * stage_bytes + n_slots * kSlotBytes;
 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (p.atomic_out && !p.accumulate) {
-    cudaError_t e = cudaMemset2DAsync(p.outf, static_cast<size_t>(p.ldf) * 4, 0, static_cast<size_t>(N) * 4,
+  if (f32_out && splits > 1 && !epi->accumulate) {
+    cudaError_t e = cudaMemset2DAsync(epi->outf, static_cast<size_t>(epi->ldf) * 4, 0, static_cast<size_t>(N) * 4,
                                       static_cast<size_t>(M), s);
     if (e != cudaSuccess) return static_cast<int>(e);
   }
 
-  CUtensorMap tmA, tmB;
+  GemmMaps tm;
   int rc;
-  if (a_mn) rc = make_tmap_2d_bf16(&tmA, A, static_cast<uint64_t>(K), static_cast<uint64_t>(M), lda, 64, 64);
-  else rc = make_tmap_2d_bf16(&tmA, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), lda, 64, BM);
+  if (a_mn) rc = make_tmap_2d_bf16(&tm.A, A, static_cast<uint64_t>(K), static_cast<uint64_t>(M), lda, 64, 64);
+  else rc = make_tmap_2d_bf16(&tm.A, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), lda, 64, BM);
   if (rc != OWL_OK) return rc;
-  if (b_mn) rc = make_tmap_2d_bf16(&tmB, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64, 64);
-  else rc = make_tmap_2d_bf16(&tmB, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldb, 64, bn);
+  if (b_mn) rc = make_tmap_2d_bf16(&tm.B, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64, 64);
+  else rc = make_tmap_2d_bf16(&tm.B, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldb, 64, bn);
   if (rc != OWL_OK) return rc;
+  if (f32_out) rc = make_tmap_2d_f32(&tm.O0, epi->outf, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->ldf, 32, BM);
+  else rc = make_tmap_2d_bf16(&tm.O0, out0, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->ld0, 64, BM);
+  if (rc != OWL_OK) return rc;
+  tm.O1 = tm.O0; tm.X0 = tm.O0; tm.X1 = tm.O0;  // placeholders for unused maps
+  if (out1 && (rc = make_tmap_2d_bf16(&tm.O1, out1, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->ld1, 64, BM)) != OWL_OK)
+    return rc;
+  if (p.aux0_tma && (rc = make_tmap_2d_bf16(&tm.X0, aux0, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->lda0, 64, BM)) != OWL_OK)
+    return rc;
+  if (p.aux1_tma && (rc = make_tmap_2d_bf16(&tm.X1, aux1, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->lda1, 64, BM)) != OWL_OK)
+    return rc;
 
   const long long total = static_cast<long long>(tiles_m) * tiles_n * splits;
   const int grid = static_cast<int>(total < sms ? total : sms);
   switch (bn) {
-    case 64: return launch_gemm_layout<64>(layout, tmA, tmB, p, grid, s);
-    case 128: return launch_gemm_layout<128>(layout, tmA, tmB, p, grid, s);
-    default: return launch_gemm_layout<256>(layout, tmA, tmB, p, grid, s);
+    case 64: return launch_gemm_layout<64>(layout, tm, p, grid, smem_bytes, s);
+    case 128: return launch_gemm_layout<128>(layout, tm, p, grid, smem_bytes, s);
+    default: return launch_gemm_layout<256>(layout, tm, p, grid, smem_bytes, s);
   }
 }
 

@@ -40,6 +40,21 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
 }
 
+int make_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                     uint32_t box_cols, uint32_t box_rows) {
+  encode_tiled_fn enc = get_encode();
+  if (!enc) return OWL_ERR_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld_elems * 4) % 16) return OWL_ERR_ALIGN;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * 4};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
+}
+
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t s1_elems,
                       uint64_t s2_elems, uint32_t b0, uint32_t b1) {
   encode_tiled_fn enc = get_encode();

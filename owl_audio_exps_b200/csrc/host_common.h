@@ -18,6 +18,10 @@ namespace owl {
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                       uint32_t box_cols, uint32_t box_rows);
 
+// 2-D fp32 row-major tensor [rows, cols]; box = {box_cols (<= 32), box_rows}; 128-byte swizzle.
+int make_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                     uint32_t box_cols, uint32_t box_rows);
+
 // 3-D bf16 tensor [n2, n1, n0] (n0 contiguous) with element strides s1, s2; box {b0, b1, 1}; 128B swizzle.
 int make_tmap_3d_bf16(CUtensorMap* out, const void* base, uint64_t n0, uint64_t n1, uint64_t n2, uint64_t s1_elems,
                       uint64_t s2_elems, uint32_t b0, uint32_t b1);
