@@ -125,6 +125,15 @@ int owl_dsilu_mul_bf16(const void* dy, const void* z, void* dz, int64_t n, owl_s
 int owl_adaln_modulate_fwd(const void* x, const void* a, const void* b, int64_t ld_ab, void* h, float* rstd,
                            int64_t M, int64_t d, int64_t T, float eps, owl_stream_t stream);
 
+/* Gated residual + adaLN modulate in one pass                       (attn.py:135-138, modulation.py:20-25,41-43)
+ *   xsum[m,:] = x[m,:] + gate[m / T,:] * y[m,:]          (the residual of the attention branch)
+ *   h[m,:]    = rms_norm(xsum[m,:]) * (1 + a[m / T,:]) + b[m / T,:]
+ * Same traffic as doing the residual in the producing GEMM's epilogue (x, y read once; xsum, h written
+ * once) but keeps that GEMM on the wide-tile store-only epilogue.                                   */
+int owl_residual_adaln_fwd(const void* x, const void* y, const void* gate, int64_t ld_g, const void* a, const void* b,
+                           int64_t ld_ab, void* xsum, void* h, float* rstd, int64_t M, int64_t d, int64_t T, float eps,
+                           owl_stream_t stream);
+
 /* adaLN modulate backward.  Given dh [M,d]:
  *   dx[m,:]  = rms_norm_bwd(dh * (1 + a)) (+ dres[m,:] if dres != NULL)   (residual path grad)
  *   da[f,:]  = sum_{m in frame f} dh[m,:] * xhat[m,:]

@@ -51,6 +51,7 @@ SIGNATURES = {
     "owl_silu_bf16": ([vp, vp, i64, vp], C.c_int),
     "owl_dsilu_mul_bf16": ([vp, vp, vp, i64, vp], C.c_int),
     "owl_adaln_modulate_fwd": ([vp, vp, vp, i64, vp, vp, i64, i64, i64, f32, vp], C.c_int),
+    "owl_residual_adaln_fwd": ([vp, vp, vp, i64, vp, vp, i64, vp, vp, vp, i64, i64, i64, f32, vp], C.c_int),
     "owl_adaln_modulate_bwd": ([vp, vp, vp, i64, vp, vp, vp, vp, vp, i64, i64, i64, i64, vp], C.c_int),
     "owl_gate_fwd": ([vp, vp, i64, vp, vp, i64, i64, i64, vp], C.c_int),
     "owl_gate_bwd": ([vp, vp, vp, i64, vp, vp, i64, vp, C.c_int, i64, i64, i64, vp], C.c_int),

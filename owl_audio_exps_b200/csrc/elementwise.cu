@@ -101,11 +101,13 @@ static inline int grid_for(int64_t work_items, int threads) {
 template <int NV>
 __global__ void __launch_bounds__(kRowThreads)
 adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const bf16* __restrict__ b, int64_t ld_ab,
-                 bf16* __restrict__ h, float* __restrict__ rstd_out, int64_t M, int d, int T, float eps) {
+                 bf16* __restrict__ h, float* __restrict__ rstd_out, int64_t M, int d, int T, float eps,
+                 const bf16* __restrict__ y, const bf16* __restrict__ gate, int64_t ld_g, bf16* __restrict__ xsum) {
   const int lane = threadIdx.x & 31;
   const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
   for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
     const bf16* xr = x + row * d;
+    const int64_t frow = row / T;
     uint4 xv[NV];
     float ss = 0.f;
 #pragma unroll
@@ -115,6 +117,16 @@ adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const b
         xv[i] = ldg16(xr + c);
         float f[8];
         unpack8(xv[i], f);
+        if (y != nullptr) {  // x <- x + gate[frame] * y, the residual of the previous branch (attn.py:135,141)
+          float fy[8], fg[8];
+          unpack8(ldg16(y + row * d + c), fy);
+          unpack8(ldg16(gate + frow * ld_g + c), fg);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = fmaf(fg[j], fy[j], f[j]);
+          xv[i] = pack8(f);  // the residual stream is bf16: normalise exactly what is stored
+          stg16(xsum + row * d + c, xv[i]);
+          unpack8(xv[i], f);
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) ss += f[j] * f[j];
       }
@@ -122,7 +134,6 @@ adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const b
     ss = warp_sum(ss);
     const float rstd = rsqrtf(ss / static_cast<float>(d) + eps);
     if (rstd_out != nullptr && lane == 0) rstd_out[row] = rstd;
-    const int64_t frow = row / T;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * 8;
@@ -463,7 +474,25 @@ int owl_adaln_modulate_fwd(const void* x, const void* a, const void* b, int64_t 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   OWL_DISPATCH_NV(d, (adaln_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
                          static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
-                         static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps)));
+                         static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps, nullptr, nullptr,
+                         0, nullptr)));
+  return launch_status();
+}
+
+int owl_residual_adaln_fwd(const void* x, const void* y, const void* gate, int64_t ld_g, const void* a, const void* b,
+                           int64_t ld_ab, void* xsum, void* h, float* rstd, int64_t M, int64_t d, int64_t T, float eps,
+                           owl_stream_t stream) {
+  OWL_REQUIRE(x && y && gate && xsum && h && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE((a == nullptr) == (b == nullptr), OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(x) && aligned16(y) && aligned16(gate) && aligned16(xsum) && aligned16(h) && aligned16(a) &&
+                  aligned16(b) && ld_g % 8 == 0 && (a == nullptr || ld_ab % 8 == 0),
+              OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  OWL_DISPATCH_NV(d, (adaln_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
+                         static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
+                         static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps,
+                         static_cast<const bf16*>(y), static_cast<const bf16*>(gate), ld_g, static_cast<bf16*>(xsum))));
   return launch_status();
 }
 

@@ -17,6 +17,7 @@
 // Split-K (fp32 output only) turns the store into red.global.add so small weight-gradient GEMMs
 // still fill 148 SMs.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "host_common.h"
 #include "sm100.cuh"
@@ -25,7 +26,7 @@ namespace owl {
 
 static constexpr int BM = 128;
 static constexpr int BK = 64;
-static constexpr int kGemmThreads = 256;
+static constexpr int kGemmThreads = 384;  // 4 control warps + 2 epilogue groups of 4 warps
 static constexpr int kSlotBytes = 16384;   // one staging panel: 128 rows x 128 bytes, 128B-swizzled
 static constexpr int kBarRegion = 1024;    // mbarriers + TMEM slot at the front of dynamic smem
 static constexpr int kMaxStages = 8;
@@ -51,10 +52,20 @@ struct GemmCfg {
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
 };
 
-__device__ __forceinline__ float silu_f(float z) { return z * sigmoidf_fast(z); }
+// sigmoid through ONE MUFU op (tanh.approx) instead of ex2 + rcp: the epilogue of a K = d GEMM has only
+// ~8k cycles per 128x256 tile, and 2 MUFU ops x 32k elements at 16/clk/SM would eat half of that.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float silu_f(float z) {
+  const float h = 0.5f * z;
+  return fmaf(h, tanh_approx(h), h);
+}
 __device__ __forceinline__ float dsilu_f(float z) {
-  const float s = sigmoidf_fast(z);
-  return s * (1.f + z * (1.f - s));
+  const float s = fmaf(0.5f, tanh_approx(0.5f * z), 0.5f);
+  return s * fmaf(z, 1.f - s, 1.f);
 }
 __device__ __forceinline__ void unpack8u(const uint4& v, float (&f)[8]) {
   f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
@@ -107,7 +118,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 128);
+      mbar_init(&tempty_bar[s], 256);
       mbar_init(&aux_bar[s], 1);
     }
     fence_barrier_init();
@@ -189,29 +200,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4) {
+    // Two epilogue groups of 4 warps; group g owns panels g, g+2, ... of every tile, with its own staging
+    // slots, named barrier, TMA-store queue and aux operand slot, so the latencies of one group's panel
+    // (tcgen05.ld, TMA-store drain, barriers) overlap the other group's.
+    const int grp = (warp - 4) >> 2;
     const int q = warp & 3;           // TMEM lane quarter this warp may access
     const int r = q * 32 + lane;      // row inside the tile
-    const bool leader = threadIdx.x == 128;
+    const bool leader = (threadIdx.x & 127) == 0;
+    const int bar_id = 1 + grp;
     const bool f32out = p.mode == OWL_EPI_F32;
     const bool has_aux = (p.aux0_tma | p.aux1_tma) != 0;
     const int P = f32out ? BN / 32 : BN / 64;  // panels per tile
     const int pcols = f32out ? 32 : 64;
-    uint8_t* s_out0 = stag;
-    uint8_t* s_out1 = stag + kSlotBytes;
-    uint8_t* s_aux0 = stag + (1 + p.has_out1) * kSlotBytes;                // two slots
-    uint8_t* s_aux1 = s_aux0 + (p.aux0_tma ? 2 : 0) * kSlotBytes;          // two slots
+    const int n_out = 1 + p.has_out1;
+    uint8_t* s_out0 = stag + grp * n_out * kSlotBytes;
+    uint8_t* s_out1 = s_out0 + kSlotBytes;
+    uint8_t* s_aux0 = stag + 2 * n_out * kSlotBytes + grp * kSlotBytes;            // [2] slots: one per group
+    uint8_t* s_aux1 = stag + (2 * n_out + 2 * p.aux0_tma) * kSlotBytes + grp * kSlotBytes;
     const uint32_t aux_bytes = static_cast<uint32_t>((p.aux0_tma + p.aux1_tma) * kSlotBytes);
-    auto issue_aux = [&](int t, int pn, int g) {  // leader only
+    auto issue_aux = [&](int t, int pn) {  // group leader only
       const int m0 = (t % p.tiles_m) * BM, n0 = ((t / p.tiles_m) % p.tiles_n) * BN + pn * 64;
-      const int s = g & 1;
-      mbar_arrive_expect_tx(&aux_bar[s], aux_bytes);
-      if (p.aux0_tma) tma_load_2d(s_aux0 + s * kSlotBytes, &tmX0, &aux_bar[s], n0, m0);
-      if (p.aux1_tma) tma_load_2d(s_aux1 + s * kSlotBytes, &tmX1, &aux_bar[s], n0, m0);
+      mbar_arrive_expect_tx(&aux_bar[grp], aux_bytes);
+      if (p.aux0_tma) tma_load_2d(s_aux0, &tmX0, &aux_bar[grp], n0, m0);
+      if (p.aux1_tma) tma_load_2d(s_aux1, &tmX1, &aux_bar[grp], n0, m0);
     };
     int as = 0;
     uint32_t aphase = 0;
-    int g = 0;  // running panel counter (aux slot / parity)
-    if (leader && has_aux && static_cast<int>(blockIdx.x) < total_tiles) issue_aux(blockIdx.x, 0, 0);
+    uint32_t xphase = 0;  // parity of this group's aux barrier
+    if (leader && has_aux && grp < P && static_cast<int>(blockIdx.x) < total_tiles) issue_aux(blockIdx.x, grp);
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int tm = t % p.tiles_m;
       const int tn = (t / p.tiles_m) % p.tiles_n;
@@ -220,11 +236,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN);
+      if (grp >= P) {  // BN = 64 bf16: a single panel, nothing for the second group in this tile
+        tc_fence_before();
+        mbar_arrive(&tempty_bar[as]);
+      }
 #pragma unroll 1
-      for (int pn = 0; pn < P; ++pn, ++g) {
-        if (leader && has_aux) {  // prefetch the next panel's operands
-          if (pn + 1 < P) issue_aux(t, pn + 1, g + 1);
-          else if (t + static_cast<int>(gridDim.x) < total_tiles) issue_aux(t + gridDim.x, 0, g + 1);
+      for (int pn = grp; pn < P; pn += 2) {
+        const bool last = pn + 2 >= P;
+        uint4 x0r[8];
+        if (has_aux) {
+          mbar_wait(&aux_bar[grp], xphase);
+          xphase ^= 1;
+          if (p.aux0_tma) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) x0r[c] = *reinterpret_cast<const uint4*>(s_aux0 + panel_off(r, c));
+          }
         }
         uint32_t acc[64];
         {
@@ -236,19 +262,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           tmem_ld_wait();
         }
-        if (pn == P - 1) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+        if (last) {  // this thread has read all it needs: hand the TMEM buffer back to the MMA warp
           tc_fence_before();
           mbar_arrive(&tempty_bar[as]);
         }
-        if (has_aux) mbar_wait(&aux_bar[g & 1], (g >> 1) & 1);
+        if (leader) tma_store_wait_read0();  // this group's previous stores have drained its staging slots
+        named_bar_sync(bar_id, 128);         // ... and every thread holds its aux0 chunks in registers
+        if (leader && has_aux && !p.aux1_tma) {  // refill the aux slot for this group's next panel right away
+          if (!last) issue_aux(t, pn + 2);
+          else if (t + static_cast<int>(gridDim.x) < total_tiles) issue_aux(t + gridDim.x, grp);
+        }
         const int c0 = n0 + pn * pcols;
-        uint4 o0[8], o1[8];
         if (f32out) {
 #pragma unroll
-          for (int c = 0; c < 8; ++c) o0[c] = make_uint4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+          for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) =
+                make_uint4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
         } else {
-          const uint8_t* x0 = s_aux0 + (g & 1) * kSlotBytes;
-          const uint8_t* x1 = s_aux1 + (g & 1) * kSlotBytes;
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
             const int col = c0 + c * 8;
@@ -262,7 +292,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               a[4] += b1.x; a[5] += b1.y; a[6] += b1.z; a[7] += b1.w;
             }
             if (p.mode == OWL_EPI_STORE) {
-              o0[c] = pack8u(a);
+              *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(a);
             } else if (p.mode == OWL_EPI_BIAS_SILU) {
               float sv[8];
 #pragma unroll
@@ -270,13 +300,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 a[j] = round_bf16(a[j]);  // the reference's Linear output is bf16 before F.silu (mlp.py:34-35)
                 sv[j] = silu_f(a[j]);
               }
-              o0[c] = pack8u(a);
-              o1[c] = pack8u(sv);
+              *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(a);
+              *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = pack8u(sv);
             } else if (p.mode == OWL_EPI_GATE_RESIDUAL) {
               float res[8], gt[8];
-              unpack8u(*reinterpret_cast<const uint4*>(x0 + panel_off(r, c)), res);
+              unpack8u(x0r[c], res);
               if (p.aux1_tma) {
-                unpack8u(*reinterpret_cast<const uint4*>(x1 + panel_off(r, c)), gt);
+                unpack8u(*reinterpret_cast<const uint4*>(s_aux1 + panel_off(r, c)), gt);
               } else if (row < p.M && col < p.N) {
                 unpack8u(__ldg(reinterpret_cast<const uint4*>(p.aux1 + (row / p.rows_per_frame) * p.lda1 + col)), gt);
               } else {
@@ -285,34 +315,32 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
 #pragma unroll
               for (int j = 0; j < 8; ++j) a[j] = round_bf16(a[j]);
-              o1[c] = pack8u(a);
+              if (p.has_out1) *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = pack8u(a);
 #pragma unroll
               for (int j = 0; j < 8; ++j) res[j] += gt[j] * a[j];
-              o0[c] = pack8u(res);
+              *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(res);
             } else {  // OWL_EPI_DSILU
               float z[8];
-              unpack8u(*reinterpret_cast<const uint4*>(x0 + panel_off(r, c)), z);
+              unpack8u(x0r[c], z);
 #pragma unroll
               for (int j = 0; j < 8; ++j) a[j] *= dsilu_f(z[j]);
-              o0[c] = pack8u(a);
+              *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(a);
             }
           }
         }
-        if (leader) tma_store_wait_read0();  // the previous panel's stores have drained the staging slots
-        named_bar_sync(1, 128);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = o0[c];
-        if (p.has_out1) {
-#pragma unroll
-          for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = o1[c];
-        }
         fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (leader && c0 < p.N) {
-          if (p.f32_reduce) tma_reduce_add_2d(&tmO0, s_out0, c0, m0);
-          else tma_store_2d(&tmO0, s_out0, c0, m0);
-          if (p.has_out1) tma_store_2d(&tmO1, s_out1, c0, m0);
-          tma_store_commit();
+        named_bar_sync(bar_id, 128);
+        if (leader) {
+          if (c0 < p.N) {
+            if (p.f32_reduce) tma_reduce_add_2d(&tmO0, s_out0, c0, m0);
+            else tma_store_2d(&tmO0, s_out0, c0, m0);
+            if (p.has_out1) tma_store_2d(&tmO1, s_out1, c0, m0);
+            tma_store_commit();
+          }
+          if (p.aux1_tma) {  // the gate panel was read from smem during the math: refill only now
+            if (!last) issue_aux(t, pn + 2);
+            else if (t + static_cast<int>(gridDim.x) < total_tiles) issue_aux(t + gridDim.x, grp);
+          }
         }
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
@@ -376,21 +404,43 @@ static int launch_gemm_layout(int layout, const GemmMaps& tm, const GemmParams& 
   }
 }
 
-// Tile width by a wave-quantisation model: time ~ waves x (per-tile main loop + fixed per-tile cost).
-// Narrow tiles pay more shared-memory bandwidth per flop (eff) but quantise better on 148 SMs.
-static int pick_bn(int tiles_m, long long N, int max_bn, int sms) {
-  int best = 64;
-  double best_cost = 1e30;
+// Tile width and split-K factor by a wave-quantisation model:
+//   time ~ waves x (k-blocks per tile x BN x eff(BN) + fixed per-tile cost)
+// Narrow tiles pay more shared-memory bandwidth per flop (eff) but quantise better on 148 SMs; split-K
+// (fp32 reduce-add outputs only) fills the machine when there are few output tiles.
+struct GemmPlan {
+  int bn, splits, stages, n_slots;
+};
+
+static int slots_for(const GemmParams& p) { return 2 * (1 + p.has_out1) + 2 * p.aux0_tma + 2 * p.aux1_tma; }
+
+static int stages_for(int bn, int n_slots) {
+  const int stage_bytes = BM * BK * 2 + bn * BK * 2;
+  int st = (kSmemLimit - 1024 - kBarRegion - n_slots * kSlotBytes) / stage_bytes;
+  return st > kMaxStages ? kMaxStages : st;
+}
+
+static GemmPlan plan_gemm(int tiles_m, long long N, int kb_total, bool can_split, int n_slots, int sms) {
+  GemmPlan best{64, 1, 2, n_slots};
+  double best_cost = 1e300;
   const int cand[3] = {256, 128, 64};
-  const double eff[3] = {1.0, 1.12, 1.45};
+  const double eff[3] = {1.0, 1.6, 2.8};  // measured on B200: 128-wide tiles are smem/L2-operand bound
   for (int i = 0; i < 3; ++i) {
     const int bn = cand[i];
-    if (bn > max_bn) continue;
     if (bn > 64 && N <= bn / 2) continue;  // mostly padding
+    const int stages = stages_for(bn, n_slots);
+    if (stages < 3) continue;
     const long long tiles = static_cast<long long>(tiles_m) * ((N + bn - 1) / bn);
-    const long long waves = (tiles + sms - 1) / sms;
-    const double cost = static_cast<double>(waves) * (bn * eff[i] + 24.0);
-    if (cost < best_cost) { best_cost = cost; best = bn; }
+    const int max_splits = can_split ? (kb_total / 4 > 0 ? kb_total / 4 : 1) : 1;
+    for (int sp = 1; sp <= max_splits && sp <= 32; ++sp) {
+      const int kbps = (kb_total + sp - 1) / sp;
+      const int real_sp = (kb_total + kbps - 1) / kbps;
+      const long long waves = (tiles * real_sp + sms - 1) / sms;
+      const double fixed = 400.0 + (real_sp > 1 ? 150.0 : 0.0);  // reduce-add traffic of a split tile
+      const double cost = static_cast<double>(waves) * (kbps * bn * eff[i] + fixed);
+      if (cost < best_cost) { best_cost = cost; best = GemmPlan{bn, real_sp, stages, n_slots}; }
+      if (tiles * sp >= 2LL * sms) break;
+    }
   }
   return best;
 }
@@ -461,33 +511,39 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
 
   const int sms = sm_count();
   const int tiles_m = static_cast<int>((M + BM - 1) / BM);
-  const int bn = pick_bn(tiles_m, N, uses_aux ? 128 : 256, sms);
-  const int tiles_n = static_cast<int>((N + bn - 1) / bn);
   const int kb_total = static_cast<int>((K + BK - 1) / BK);
-  int splits = 1;
-  if (f32_out) {
-    const int mn_tiles = tiles_m * tiles_n;
-    if (mn_tiles < sms && kb_total >= 8) {
-      splits = (sms + mn_tiles - 1) / mn_tiles;
-      const int max_splits = kb_total / 4;  // >= 4 k-blocks (256 contraction steps) per split
-      if (splits > max_splits) splits = max_splits;
-      if (splits < 1) splits = 1;
+  GemmPlan plan = plan_gemm(tiles_m, N, kb_total, f32_out, slots_for(p), sms);
+  if (const char* e = getenv("OWL_GEMM_BN")) {  // tuning aid (tools/gemm_shapes.py): force the tile width
+    const int v = atoi(e);
+    if ((v == 64 || v == 128 || v == 256) && stages_for(v, plan.n_slots) >= 2) {
+      plan.bn = v;
+      plan.stages = stages_for(v, plan.n_slots);
+      if (!f32_out) plan.splits = 1;
     }
   }
-  int kb_per_split = (kb_total + splits - 1) / splits;
-  splits = (kb_total + kb_per_split - 1) / kb_per_split;  // no empty splits
+  if (const char* e = getenv("OWL_GEMM_SPLITS")) {
+    const int v = atoi(e);
+    if (f32_out && v >= 1 && v <= kb_total) plan.splits = v;
+  }
+  if (const char* e = getenv("OWL_GEMM_STAGES")) {
+    const int v = atoi(e);
+    if (v >= 2 && v <= plan.stages) plan.stages = v;
+  }
+  const int bn = plan.bn;
+  const int tiles_n = static_cast<int>((N + bn - 1) / bn);
+  int splits = plan.splits;
+  const int kb_per_split = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per_split - 1) / kb_per_split;
   p.tiles_m = tiles_m; p.tiles_n = tiles_n; p.splits = splits; p.kb_per_split = kb_per_split; p.kb_total = kb_total;
   p.f32_reduce = (f32_out && (splits > 1 || epi->accumulate)) ? 1 : 0;
 
   // shared memory: barrier region + operand ring + staging panels
-  const int n_slots = 1 + p.has_out1 + 2 * p.aux0_tma + 2 * p.aux1_tma;
   const int stage_bytes = BM * BK * 2 + bn * BK * 2;
-  int stages = (kSmemLimit - 1024 - kBarRegion - n_slots * kSlotBytes) / stage_bytes;
-  if (stages > kMaxStages) stages = kMaxStages;
+  int stages = plan.stages;
   if (stages > kb_per_split + 1) stages = kb_per_split + 1;
-  if (stages < 2) return OWL_ERR_UNSUPPORTED;
+  if (stages < 2) stages = 2;
   p.stages = stages;
-  const int smem_bytes = 1024 + kBarRegion + stages * stage_bytes + n_slots * kSlotBytes;
+  const int smem_bytes = 1024 + kBarRegion + stages * stage_bytes + plan.n_slots * kSlotBytes;
 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (f32_out && splits > 1 && !epi->accumulate) {

@@ -481,10 +481,11 @@ class DiTBlockFn(torch.autograd.Function):
       4  qkv   = h1 Wqkv^T + bqkv                             [M,3d]     GEMM
       5  q,k,v = rope(rms_norm(.)) + head split (+KV append)  [B,H,L,dh] QK-norm+RoPE kernel
       6  o,lse = attention(q,k,v,mask)                        [M,d]      tcgen05 attention (token-major out)
-      7  y1 = o Wout^T + bout ; x1 = x + c1*y1                [M,d]      GEMM, gate+residual epilogue
-      8  h2    = rms_norm(x1)*(1+a2)+b2 ; rstd2               [M,d]      adaLN kernel
+      7  y1 = o Wout^T + bout                                 [M,d]      GEMM
+      8  x1 = x + c1*y1 ; h2 = rms_norm(x1)*(1+a2)+b2 ; rstd2 [M,d]      residual+adaLN kernel (one pass)
       9  z = h2 W1^T + b1 ; s = silu(z)                       [M,4d]     GEMM, bias+SiLU epilogue
-      10 y2 = s W2^T + b2 ; x2 = x1 + c2*y2                   [M,d]      GEMM, gate+residual epilogue
+      10 y2 = s W2^T + b2                                     [M,d]      GEMM
+      11 x2 = x1 + c2*y2                                      [M,d]      gate+residual kernel
     The backward mirrors it with dgrad (NN) and wgrad (TN, fp32) GEMMs; silu', the residual-gradient
     add, the per-frame da/db/dc reductions and the bias column sums are fused into kernel epilogues or
     the single-pass memory-bound kernels.
@@ -516,19 +517,16 @@ class DiTBlockFn(torch.autograd.Function):
         del qkv
         o2 = o.view(M, d)
 
-        x1 = torch.empty(M, d, device=x16.device, dtype=bf16)
-        y1 = torch.empty(M, d, device=x16.device, dtype=bf16) if need_grad else None
-        ops.gemm(OWL_GEMM_NT, o2, W["wout"], M, d, d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["bout"], out0=x1, out1=y1,
-                 aux0=x16, aux1=c1, rows_per_frame=T)
-
-        h2, rstd2 = ops.adaln_modulate_fwd(x1, a2, b2, T, RMS_EPS, want_rstd=need_grad)
+        # out projection (store-only epilogue); its gate and residual ride on the next norm's single pass
+        y1 = torch.empty(M, d, device=x16.device, dtype=bf16)
+        ops.gemm(OWL_GEMM_NT, o2, W["wout"], M, d, d, mode=OWL_EPI_STORE, bias=W["bout"], out0=y1)
+        x1, h2, rstd2 = ops.residual_adaln_fwd(x16, y1, c1, a2, b2, T, RMS_EPS, want_rstd=need_grad)
         z = torch.empty(M, 4 * d, device=x16.device, dtype=bf16)
         s = torch.empty(M, 4 * d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=z, out1=s)
-        x2 = torch.empty(M, d, device=x16.device, dtype=bf16)
-        y2 = torch.empty(M, d, device=x16.device, dtype=bf16) if need_grad else None
-        ops.gemm(OWL_GEMM_NT, s, W["w2"], M, d, 4 * d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["b2"], out0=x2, out1=y2,
-                 aux0=x1, aux1=c2, rows_per_frame=T)
+        y2 = torch.empty(M, d, device=x16.device, dtype=bf16)
+        ops.gemm(OWL_GEMM_NT, s, W["w2"], M, d, 4 * d, mode=OWL_EPI_STORE, bias=W["b2"], out0=y2)
+        x2 = ops.gate_fwd(y2, c2, x1, T)
 
         if need_grad:
             q, k_all, v_all, lse, rq, rk, offset, mask = asaved

@@ -180,6 +180,20 @@ def adaln_modulate_fwd(x, a, b, T: int, eps: float, want_rstd: bool = True):
     return h, rstd
 
 
+@_prof("residual_adaln_fwd")
+def residual_adaln_fwd(x, y, gate, a, b, T: int, eps: float, want_rstd: bool = True):
+    """xsum = x + gate[frame]*y ; h = rms_norm(xsum)*(1+a[frame])+b[frame].  Returns (xsum, h, rstd)."""
+    _req(x), _req(y)
+    M, d, _ = _rows(x)
+    xsum, h = torch.empty_like(x), torch.empty_like(x)
+    rstd = torch.empty(M, device=x.device, dtype=torch.float32) if want_rstd else None
+    rc = _lib.load().owl_residual_adaln_fwd(x.data_ptr(), y.data_ptr(), gate.data_ptr(), _rows(gate)[2], _p(a), _p(b),
+                                            _rows(a)[2] if a is not None else 0, xsum.data_ptr(), h.data_ptr(),
+                                            _p(rstd), M, d, T, eps, _stream())
+    _lib.check(rc, "owl_residual_adaln_fwd")
+    return xsum, h, rstd
+
+
 @_prof("adaln_modulate_bwd")
 def adaln_modulate_bwd(dh, x, a, rstd, dres, da, db, T: int):
     """Returns dx; writes da, db (views with a row stride) in place."""
