@@ -165,6 +165,10 @@ def run_reference(args):
 # GPU arm
 # ------------------------------------------------------------------------------------------------
 def loss_fn(model, x, cond, target):
+    # in the trainers x = proj_in(latents) and cond = t_embed(ts) carry gradients (audiorft.py:46-49), so the
+    # stack's input gradients (dx of block 0, dcond through every conditioning projection) are part of the step
+    x = x.detach().requires_grad_(True)
+    cond = cond.detach().requires_grad_(True)
     y = model(x, cond)
     return torch.nn.functional.mse_loss(y.float(), target.float())
 

@@ -38,6 +38,31 @@ class GradSink:
         return self.owner.accumulate
 
 
+class CondSink:
+    """What functional.CondBank looks for on the DiT stack's WeightStage: the fp32 gradient of ALL layers'
+    conditioning projections as one [n_layers*6d, d] matrix (+ [n_layers*6d] biases) inside one flat bucket,
+    so a group of layers' weight gradients is ONE GEMM written in place."""
+
+    __slots__ = ("gw", "gb", "owner", "index")
+
+    def __init__(self, gw, gb, owner: "GradBuckets", index: int):
+        self.gw, self.gb, self.owner, self.index = gw, gb, owner, index
+
+    @property
+    def accumulate(self) -> bool:
+        return self.owner.accumulate
+
+    def after_group(self, r0: int, r1: int):
+        self.owner._cond_rows_done(self.index, r0, r1)
+
+    # the sink belongs to a live engine: copies of the model (EMA) and pickles do not carry it
+    def __deepcopy__(self, memo):
+        return None
+
+    def __reduce__(self):
+        return (type(None), ())
+
+
 def _align(n: int, a: int = 64) -> int:
     return (n + a - 1) // a * a
 
@@ -45,7 +70,7 @@ def _align(n: int, a: int = 64) -> int:
 class GradBuckets:
     def __init__(self, model: torch.nn.Module, process_group=None, comm_stream: Optional[torch.cuda.Stream] = None,
                  average: bool = True):
-        from .nn.attn import DiTBlock
+        from .nn.attn import DiT, DiTBlock
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.average = average
@@ -54,10 +79,26 @@ class GradBuckets:
         self.blocks: List[torch.nn.Module] = [m for m in model.modules() if isinstance(m, DiTBlock)]
         groups: List[List[torch.nn.Parameter]] = []
         seen = set()
+        # conditioning projections of a whole DiT stack live in ONE bucket, weights of all layers first
+        # (rows in CondBank order: per layer adaln1.fc | gate1.fc_c | adaln2.fc | gate2.fc_c), then biases
+        self.cond_stacks = []        # (dit, bucket index, n weight elements, d)
+        cond_groups = []
+        for dit in (m for m in model.modules() if isinstance(m, DiT)):
+            cps = [b.cond_params() for b in dit.blocks]
+            ws = [p for ps in cps for p in ps[0::2]]
+            bs = [p for ps in cps for p in ps[1::2]]
+            d = ws[0].shape[1] if ws else 0
+            ok = ws and all(p.requires_grad and p.dtype == f32 and id(p) not in seen for p in ws + bs) and d % 64 == 0
+            if ok:
+                cond_groups.append((dit, ws + bs, sum(p.numel() for p in ws), d))
+                seen.update(id(p) for p in ws + bs)
         for blk in self.blocks:
-            ps = [p for p in blk.parameters() if p.requires_grad]
+            ps = [p for p in blk.parameters() if p.requires_grad and id(p) not in seen]
             groups.append(ps)
             seen.update(id(p) for p in ps)
+        for dit, ps, nw, d in cond_groups:
+            self.cond_stacks.append((dit, len(groups), nw, d))
+            groups.append(ps)
         rest = [p for p in model.parameters() if p.requires_grad and id(p) not in seen]
         self.rest_index = len(groups)
         groups.append(rest)
@@ -80,6 +121,12 @@ class GradBuckets:
         self.comm_stream = comm_stream if comm_stream is not None else (torch.cuda.Stream(dev) if self.is_cuda else None)
         for i, blk in enumerate(self.blocks):
             blk._stage.after_backward = (lambda i=i: self._block_done(i))
+        self._cond_low: List[int] = []   # per cond bucket: weight rows [low, n_rows) already handed to NCCL this step
+        for ci, (dit, gi, nw, d) in enumerate(self.cond_stacks):
+            flat = self.flats[gi]
+            n_rows = nw // d
+            dit._stage.cond_sink = CondSink(flat[:nw].view(n_rows, d), flat[nw:nw + n_rows], self, ci)
+            self._cond_low.append(n_rows)
         self.sync_grads = True       # set False on non-final accumulation micro-steps (DDP no_sync equivalent)
 
     # ---- step protocol -------------------------------------------------------------------------
@@ -88,9 +135,22 @@ class GradBuckets:
         self.accumulate = False
         self.flats[self.rest_index].zero_()   # these grads arrive through autograd's accumulate-in-place
         self._pending.clear()
+        self._reset_cond()
+
+    def _reset_cond(self):
+        for ci, (dit, gi, nw, d) in enumerate(self.cond_stacks):
+            self._cond_low[ci] = nw // d
 
     def next_micro_batch(self):
         self.accumulate = True
+        self._reset_cond()
+
+    def _cond_rows_done(self, ci: int, r0: int, r1: int):
+        """CondBank finished the weight gradient of rows [r0, r1) (groups complete from the tail)."""
+        dit, gi, nw, d = self.cond_stacks[ci]
+        if self.sync_grads and r1 == self._cond_low[ci]:
+            self._reduce(self.flats[gi][r0 * d:r1 * d])
+            self._cond_low[ci] = r0
 
     def _reduce(self, flat: torch.Tensor):
         if self.world == 1:
@@ -111,6 +171,12 @@ class GradBuckets:
     def finish_step(self):
         """Call after backward: reduce the non-block bucket and join the communication stream."""
         if self.sync_grads:
+            for ci, (dit, gi, nw, d) in enumerate(self.cond_stacks):
+                low = self._cond_low[ci]           # weight rows not reduced yet (all of them on the per-block path)
+                if low > 0:
+                    self._reduce(self.flats[gi][:low * d])
+                self._reduce(self.flats[gi][nw:])  # biases
+                self._cond_low[ci] = 0
             self._reduce(self.flats[self.rest_index])
         if self.is_cuda and self.world > 1:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
@@ -119,6 +185,8 @@ class GradBuckets:
         return sum(f.numel() * 4 for f in self.flats)
 
     def detach(self):
+        for dit, gi, nw, d in self.cond_stacks:
+            dit._stage.cond_sink = None
         for blk in self.blocks:
             blk._stage.after_backward = None
             for p in blk.parameters():

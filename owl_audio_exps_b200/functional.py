@@ -88,6 +88,7 @@ class WeightStage:
     def __init__(self):
         self._slots = {}
         self.after_backward = None  # engine.GradBuckets: called when the owning block's backward is done
+        self.cond_sink = None       # engine.CondSink on a DiT stack's stage: bucket views for the CondBank
 
     def get(self, key: str, params, rows=None) -> torch.Tensor:
         """bf16 [sum(rows), K] concatenation of 2-D `params` (or fp32 concatenation of 1-D biases)."""
@@ -449,6 +450,155 @@ def rope_only(x, cos, sin, offset: int = 0):
 
 
 # ------------------------------------------------------------------------------------------------
+# conditioning bank: the 4 x n_layers modulation projections of a DiT stack as ONE GEMM
+# ------------------------------------------------------------------------------------------------
+COND_PARAMS_PER_LAYER = 8   # adaln1.fc.{weight,bias}, gate1.fc_c.{weight,bias}, adaln2.fc.{...}, gate2.fc_c.{...}
+
+
+class CondBank:
+    """Per-forward state of the batched conditioning projections of a DiT stack.
+
+    `cond` is layer-invariant (attn.py:185-189 passes the same tensor to every block), and every block
+    applies four Linear(silu(cond)) to it (modulation.py:10,31).  With one token per frame (audio.yml)
+    these are a third of all linear FLOPs, issued as 16 x 6 small GEMMs.  The bank computes
+        mod_all[R, n_layers*6d] = silu(cond) Wc_all^T + bc_all
+    once per DiT.forward, blocks read their [R, 6d] column slice, write their dmod slice into
+    `dmod_all` during backward, and the weight gradients are taken `group` layers at a time as those
+    layers' backward completes (so the all-reduce of that slice overlaps the remaining backward)."""
+
+    def __init__(self, n_layers: int, d: int, stage: "WeightStage", group: int = 4):
+        self.n_layers, self.d, self.stage, self.group = n_layers, d, stage, max(1, group)
+        self.mod_all = None      # bf16 [R, n_layers*6d]
+        self.dmod_all = None     # bf16 [R, n_layers*6d], allocated by the first block backward
+        self.scond16 = None
+        self.gw = self.gb = None  # fp32 [n_layers*6d, d] / [n_layers*6d]: bucket sink views or private buffers
+        self.accumulate = False
+        self.after_group = None  # engine hook: (row_lo, row_hi) of gw finished
+        self.want_wgrad = False
+        self.token_grad = None
+        self._done = set()
+        self._flushed = 0        # layers [_flushed_lo, n_layers) already went through the group wgrad
+        self._lo = n_layers
+
+    def mod(self, layer: int) -> torch.Tensor:
+        w = 6 * self.d
+        return self.mod_all[:, layer * w:(layer + 1) * w]
+
+    def dmod(self, layer: int) -> torch.Tensor:
+        if self.dmod_all is None:
+            self.dmod_all = torch.empty_like(self.mod_all)
+        w = 6 * self.d
+        return self.dmod_all[:, layer * w:(layer + 1) * w]
+
+    def block_done(self, layer: int):
+        """Called by DiTBlockFn.backward once the block's dmod slice is complete (blocks finish in
+        reverse order): takes the weight gradient of every complete group of layers at the tail."""
+        self._done.add(layer)
+        while self._lo > 0:
+            lo = max(0, (self._lo - 1) // self.group * self.group)
+            if not all(l in self._done for l in range(lo, self._lo)):
+                break
+            self._wgrad_rows(lo, self._lo)
+            self._lo = lo
+
+    def flush(self):
+        """Take whatever has not been through a group wgrad yet (blocks that never ran backward
+        contribute zeros: their dmod slice is cleared first)."""
+        if self._lo > 0 and self.want_wgrad:
+            if self.dmod_all is None:
+                self.dmod_all = torch.zeros_like(self.mod_all)
+            for l in range(self._lo):
+                if l not in self._done:
+                    self.dmod(l).zero_()
+            self._wgrad_rows(0, self._lo)
+        self._lo = 0
+
+    def _wgrad_rows(self, lo: int, hi: int):
+        if not self.want_wgrad:
+            return
+        w = 6 * self.d
+        r0, r1 = lo * w, hi * w
+        R = self.mod_all.shape[0]
+        dm = self.dmod_all[:, r0:r1]
+        ops.gemm(OWL_GEMM_TN, dm, self.scond16, r1 - r0, self.d, R, mode=OWL_EPI_F32, outf=self.gw[r0:r1],
+                 accumulate=self.accumulate)
+        ops.colsum(dm, self.gb[r0:r1], accumulate=self.accumulate)
+        if self.after_group is not None:
+            self.after_group(r0, r1)
+
+
+class CondBankFn(torch.autograd.Function):
+    """token = f(scond, P...) with side effect bank.mod_all.  The returned 1-element `token` only
+    carries the autograd edge: every block takes it as an input, so this node's backward runs after all
+    blocks' backward and finishes the job (remaining group wgrads, then dscond = dmod_all Wc_all)."""
+
+    @staticmethod
+    def forward(ctx, scond, bank: CondBank, *P):
+        d = bank.d
+        scond16 = _as_bf16(scond).view(-1, d)
+        R = scond16.shape[0]
+        ws, bs = list(P[0::2]), list(P[1::2])
+        wc = bank.stage.get("wc_all", ws)
+        bc = bank.stage.get("bc_all", bs)
+        N = wc.shape[0]
+        bank.mod_all = torch.empty(R, N, device=scond16.device, dtype=bf16)
+        ops.gemm(OWL_GEMM_NT, scond16, wc, R, N, d, mode=OWL_EPI_STORE, bias=bc, out0=bank.mod_all)
+        bank.scond16 = scond16
+        bank.want_wgrad = any(ctx.needs_input_grad[2:])
+        if any(ctx.needs_input_grad):
+            sink = getattr(bank.stage, "cond_sink", None)
+            if bank.want_wgrad:
+                if sink is not None:
+                    bank.gw, bank.gb, bank.accumulate, bank.after_group = sink.gw, sink.gb, sink.accumulate, sink.after_group
+                else:
+                    bank.gw = torch.empty(N, d, device=scond16.device, dtype=f32)
+                    bank.gb = torch.empty(N, device=scond16.device, dtype=f32)
+            ctx.sunk = sink is not None
+            ctx.save_for_backward(wc, *P)
+            ctx.bank = bank
+            ctx.meta = (scond.shape, scond.dtype)
+            bank.token_grad = torch.zeros(1, device=scond16.device, dtype=f32)
+        return torch.zeros(1, device=scond16.device, dtype=f32)
+
+    @staticmethod
+    def backward(ctx, dtoken):
+        bank = ctx.bank
+        wc = ctx.saved_tensors[0]
+        P = ctx.saved_tensors[1:]
+        d, N = bank.d, wc.shape[0]
+        bank.flush()
+        dscond = None
+        if ctx.needs_input_grad[0]:
+            shape, dtype = ctx.meta
+            R = bank.mod_all.shape[0]
+            if bank.dmod_all is None:
+                bank.dmod_all = torch.zeros_like(bank.mod_all)
+            dscond = torch.empty(R, d, device=wc.device, dtype=bf16)
+            ops.gemm(OWL_GEMM_NN, bank.dmod_all, wc, R, d, N, mode=OWL_EPI_STORE, out0=dscond)
+            dscond = dscond.view(shape).to(dtype)
+        grads = [None] * len(P)
+        if bank.want_wgrad and not ctx.sunk:
+            r = 0
+            for i in range(0, len(P), 2):
+                n = P[i].shape[0]
+                if ctx.needs_input_grad[2 + i]:
+                    grads[i] = _grad_like(bank.gw[r:r + n], P[i])
+                if ctx.needs_input_grad[3 + i]:
+                    grads[i + 1] = _grad_like(bank.gb[r:r + n], P[i + 1])
+                r += n
+        bank.dmod_all = bank.mod_all = None
+        return (dscond, None, *grads)
+
+
+def cond_bank(scond, blocks_params, d: int, stage: "WeightStage", group: int = 4):
+    """-> (bank, token).  blocks_params: per layer (wa1, ba1, wg1, bg1, wa2, ba2, wg2, bg2)."""
+    bank = CondBank(len(blocks_params), d, stage, group)
+    flat = [p for ps in blocks_params for p in ps]
+    token = CondBankFn.apply(scond, bank, *flat)
+    return bank, token
+
+
+# ------------------------------------------------------------------------------------------------
 # the fused DiT block (attn.py:130-143): 13 launches forward, 22 backward
 # ------------------------------------------------------------------------------------------------
 _BLOCK_PARAMS = ("attn.qkv.weight", "attn.qkv.bias", "attn.out.weight", "attn.out.bias",
@@ -457,18 +607,21 @@ _BLOCK_PARAMS = ("attn.qkv.weight", "attn.qkv.bias", "attn.out.weight", "attn.ou
                  "adaln2.fc.weight", "adaln2.fc.bias", "gate2.fc_c.weight", "gate2.fc_c.bias")
 
 
-def stage_block_weights(stage: WeightStage, P):
+def stage_block_weights(stage: WeightStage, P, with_cond: bool = True):
     """bf16 operands + fp32 biases of one block.  The four conditioning projections (adaln1.fc,
     gate1.fc_c, adaln2.fc, gate2.fc_c; modulation.py:10,31) share their input silu(cond), so they are
     staged as ONE [6d, d] operand: columns [a1 | b1 | c1 | a2 | b2 | c2] of a single GEMM."""
     (wqkv, bqkv, wout, bout, w1, b1, w2, b2, wa1, ba1, wg1, bg1, wa2, ba2, wg2, bg2) = P
-    return dict(
+    W = dict(
         wqkv=stage.get("wqkv", [wqkv]), bqkv=stage.get("bqkv", [bqkv]),
         wout=stage.get("wout", [wout]), bout=stage.get("bout", [bout]),
         w1=stage.get("w1", [w1]), b1=stage.get("b1", [b1]),
         w2=stage.get("w2", [w2]), b2=stage.get("b2", [b2]),
-        wc=stage.get("wc", [wa1, wg1, wa2, wg2]), bc=stage.get("bc", [ba1, bg1, ba2, bg2]),
     )
+    if with_cond:  # not needed when the stack's CondBank already projected the conditioning
+        W["wc"] = stage.get("wc", [wa1, wg1, wa2, wg2])
+        W["bc"] = stage.get("bc", [ba1, bg1, ba2, bg2])
+    return W
 
 
 class DiTBlockFn(torch.autograd.Function):
@@ -492,7 +645,7 @@ class DiTBlockFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, cond, scond, plan: AttnPlan, stage: WeightStage, *P):
+    def forward(ctx, x, cond, scond, token, plan: AttnPlan, stage: WeightStage, bank, *P):
         B, L, d = x.shape
         R = cond.shape[0] * cond.shape[1]
         M = B * L
@@ -500,13 +653,17 @@ class DiTBlockFn(torch.autograd.Function):
             raise RuntimeError(f"tokens ({L}) must be a multiple of conditioning frames ({cond.shape[1]})")
         T = M // R
         need_grad = any(ctx.needs_input_grad)
-        W = stage_block_weights(stage, P)
+        W = stage_block_weights(stage, P, with_cond=bank is None)
         x16 = _as_bf16(x).view(M, d)
         cond16 = _as_bf16(cond).view(R, d)
-        scond16 = ops.silu(cond16) if scond is None else scond.view(R, d)
-
-        mod = torch.empty(R, 6 * d, device=x16.device, dtype=bf16)
-        ops.gemm(OWL_GEMM_NT, scond16, W["wc"], R, 6 * d, d, mode=OWL_EPI_STORE, bias=W["bc"], out0=mod)
+        if bank is not None:
+            # conditioning bank (CondBank): the stack already projected silu(cond) for every layer
+            scond16 = bank.scond16
+            mod = bank.mod(plan.layer_idx)
+        else:
+            scond16 = ops.silu(cond16) if scond is None else scond.view(R, d)
+            mod = torch.empty(R, 6 * d, device=x16.device, dtype=bf16)
+            ops.gemm(OWL_GEMM_NT, scond16, W["wc"], R, 6 * d, d, mode=OWL_EPI_STORE, bias=W["bc"], out0=mod)
         a1, b1, c1 = mod[:, 0:d], mod[:, d:2 * d], mod[:, 2 * d:3 * d]
         a2, b2, c2 = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], mod[:, 5 * d:6 * d]
 
@@ -531,10 +688,13 @@ class DiTBlockFn(torch.autograd.Function):
         if need_grad:
             q, k_all, v_all, lse, rq, rk, offset, mask = asaved
             ctx.save_for_backward(x16, cond16, scond16, mod, rstd1, h1, q, k_all, v_all, lse, rq, rk, o2, y1, x1, rstd2,
-                                  h2, z, s, y2, W["wqkv"], W["wout"], W["w1"], W["w2"], W["wc"], plan.cos, plan.sin, *P)
+                                  h2, z, s, y2, W["wqkv"], W["wout"], W["w1"], W["w2"],
+                                  W["wc"] if bank is None else None, plan.cos, plan.sin, *P)
             ctx.meta = (B, L, d, R, T, offset, mask, x.dtype, cond.dtype, cond.shape,
                         None if scond is None else scond.shape)
             ctx.stage = stage
+            ctx.bank = bank
+            ctx.layer = plan.layer_idx
         return x2.view(B, L, d) if x.dtype == bf16 else x2.view(B, L, d).to(x.dtype)
 
     @staticmethod
@@ -548,10 +708,11 @@ class DiTBlockFn(torch.autograd.Function):
         M = B * L
         dev = x16.device
         need = ctx.needs_input_grad
-        np0 = 5  # index of the first parameter among forward's inputs
+        np0 = 7  # index of the first parameter among forward's inputs
+        bank = ctx.bank
         dx2 = _as_bf16(dx2).view(M, d)
         c1, a2, c2, a1 = mod[:, 2 * d:3 * d], mod[:, 3 * d:4 * d], mod[:, 5 * d:6 * d], mod[:, 0:d]
-        dmod = torch.empty(R, 6 * d, device=dev, dtype=bf16)
+        dmod = bank.dmod(ctx.layer) if bank is not None else torch.empty(R, 6 * d, device=dev, dtype=bf16)
 
         # ---- MLP branch: x2 = x1 + c2 * (s W2^T + b2)
         g_b2 = _fresh_or_sink(b2, need[np0 + 7])
@@ -588,7 +749,13 @@ class DiTBlockFn(torch.autograd.Function):
 
         # ---- conditioning projections: mod = silu(cond) Wc^T + bc
         g_wa1 = g_wg1 = g_wa2 = g_wg2 = g_ba1 = g_bg1 = g_ba2 = g_bg2 = None
-        if any(need[np0 + 8:np0 + 16]):
+        dtoken = None
+        if bank is not None:
+            # the bank takes the projections' gradients for whole groups of layers (CondBank.block_done)
+            bank.block_done(ctx.layer)
+            if need[3] and ctx.layer == 0:
+                dtoken = bank.token_grad
+        elif any(need[np0 + 8:np0 + 16]):
             sinks = [_sink(p) for p in (wa1, wg1, wa2, wg2)]
             if all(s_ is not None for s_ in sinks):
                 for p, lo, hi in ((wa1, 0, 2 * d), (wg1, 2 * d, 3 * d), (wa2, 3 * d, 5 * d), (wg2, 5 * d, 6 * d)):
@@ -605,7 +772,9 @@ class DiTBlockFn(torch.autograd.Function):
                 g_ba1, g_bg1 = _grad_like(gbc[0:2 * d], ba1), _grad_like(gbc[2 * d:3 * d], bg1)
                 g_ba2, g_bg2 = _grad_like(gbc[3 * d:5 * d], ba2), _grad_like(gbc[5 * d:6 * d], bg2)
         dcond = dscond = None
-        if scond_shape is not None:
+        if bank is not None:
+            pass
+        elif scond_shape is not None:
             if need[2]:
                 dscond = torch.empty(R, d, device=dev, dtype=bf16)
                 ops.gemm(OWL_GEMM_NN, dmod, wc16, R, d, 6 * d, mode=OWL_EPI_STORE, out0=dscond)
@@ -620,7 +789,7 @@ class DiTBlockFn(torch.autograd.Function):
             dx = dx.to(xdtype)
         if ctx.stage.after_backward is not None:
             ctx.stage.after_backward()
-        return (dx if need[0] else None, dcond, dscond, None, None,
+        return (dx if need[0] else None, dcond, dscond, dtoken, None, None, None,
                 g_wqkv, g_bqkv, g_wout, g_bout, g_w1, g_b1, g_w2, g_b2,
                 g_wa1, g_ba1, g_wg1, g_bg1, g_wa2, g_ba2, g_wg2, g_bg2)
 

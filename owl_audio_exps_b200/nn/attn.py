@@ -92,10 +92,15 @@ class DiTBlock(nn.Module):
                 self.adaln1.fc.weight, self.adaln1.fc.bias, self.gate1.fc_c.weight, self.gate1.fc_c.bias,
                 self.adaln2.fc.weight, self.adaln2.fc.bias, self.gate2.fc_c.weight, self.gate2.fc_c.bias)
 
-    def forward(self, x, cond, block_mask, kv_cache=None, scond=None):
-        """attn.py:130-143.  `scond` (optional, extension): silu(cond) precomputed once per DiT.forward --
-        the reference recomputes it in each of the block's four modulation layers (modulation.py:17,38)."""
-        return OF.DiTBlockFn.apply(x, cond, scond, self.attn.plan(block_mask, kv_cache), self._stage,
+    def cond_params(self):
+        return self.block_params()[8:]
+
+    def forward(self, x, cond, block_mask, kv_cache=None, scond=None, bank=None, token=None):
+        """attn.py:130-143.  Extensions used by DiT.forward: `scond` = silu(cond) precomputed once per
+        stack forward (the reference recomputes it in each of the block's four modulation layers,
+        modulation.py:17,38); `bank`/`token` = the stack's batched conditioning projections
+        (functional.CondBank) -- the block then reads its modulation vectors instead of projecting them."""
+        return OF.DiTBlockFn.apply(x, cond, scond, token, self.attn.plan(block_mask, kv_cache), self._stage, bank,
                                    *self.block_params())
 
 
@@ -108,6 +113,8 @@ class DiT(nn.Module):
         self.local_layers = [(layer_idx % config.local_idx != 0) for layer_idx in range(config.n_layers)]
         self.blocks = nn.ModuleList([DiTBlock(config, idx, local) for idx, local in enumerate(self.local_layers)])
         self.decoding = False
+        self.cond_group = 4          # layers per conditioning-bank weight-gradient GEMM (functional.CondBank)
+        self._stage = OF.WeightStage()
 
     def enable_decoding(self):
         self.decoding = True
@@ -133,12 +140,17 @@ class DiT(nn.Module):
 
         scond = OF.silu(cond)  # layer-invariant: once per forward instead of 4x per block
         ckpt = self.training and getattr(self.config, "gradient_checkpointing", False)
+        bank = token = None
+        if not ckpt and self.cond_group > 0:
+            # all 4 x n_layers conditioning projections as one GEMM (cond is the same for every block)
+            bank, token = OF.cond_bank(scond, [b.cond_params() for b in self.blocks], self.config.d_model,
+                                       self._stage, self.cond_group)
         for layer_idx, block in enumerate(self.blocks):
             block_mask = local_block_mask if self.local_layers[layer_idx] else global_block_mask
             if ckpt:
                 x = checkpoint(block, x, cond, block_mask, kv_cache, scond)
             else:
-                x = block(x, cond, block_mask, kv_cache, scond)
+                x = block(x, cond, block_mask, kv_cache, scond, bank, token)
         return x
 
 

@@ -24,17 +24,32 @@ class Wrapped(torch.nn.Module):
 def test_bucket_layout_and_sinks():
     m = Wrapped()
     b = engine.GradBuckets(m)
-    assert len(b.flats) == CFG["n_layers"] + 1 and b.rest_index == CFG["n_layers"]
+    nl = CFG["n_layers"]
+    # one bucket per block (its 8 non-conditioning parameters), one for the whole stack's conditioning
+    # projections (functional.CondBank layout), one for everything else
+    assert len(b.flats) == nl + 2 and b.rest_index == nl + 1
     d = CFG["d_model"]
     assert sum(p.numel() for p in m.transformer.blocks[0].parameters()) == 18 * d * d + 15 * d
+    cond_flat = b.flats[nl]
+    assert cond_flat.numel() == nl * (6 * d * d + 6 * d)
+    sink = m.transformer._stage.cond_sink
+    assert sink.gw.shape == (nl * 6 * d, d) and sink.gb.shape == (nl * 6 * d,)
+    assert sink.gw.data_ptr() == cond_flat.data_ptr()
     for i, blk in enumerate(m.transformer.blocks):
+        cond_ids = {id(p) for p in blk.cond_params()}
         for p in blk.parameters():
             s = p._owl_grad_sink
             assert s.view.data_ptr() == p.grad.data_ptr() and p.grad.dtype == torch.float32
             assert s.view.data_ptr() % 16 == 0           # TMA / float4 alignment of every sink
-            lo, hi = b.flats[i].data_ptr(), b.flats[i].data_ptr() + b.flats[i].numel() * 4
+            flat = cond_flat if id(p) in cond_ids else b.flats[i]
+            lo, hi = flat.data_ptr(), flat.data_ptr() + flat.numel() * 4
             assert lo <= s.view.data_ptr() < hi
         assert blk._stage.after_backward is not None
+        # rows of the stacked conditioning gradient are in CondBank order: a1|b1, c1, a2|b2, c2 per layer
+        wa1, _, wg1, _, wa2, _, wg2, _ = blk.cond_params()
+        base = sink.gw.data_ptr() + i * 6 * d * d * 4
+        assert wa1.grad.data_ptr() == base and wg1.grad.data_ptr() == base + 2 * d * d * 4
+        assert wa2.grad.data_ptr() == base + 3 * d * d * 4 and wg2.grad.data_ptr() == base + 5 * d * d * 4
     assert not hasattr(m.proj_in.weight, "_owl_grad_sink") and m.proj_in.weight.grad is not None
     assert b.accumulate is False
     b.begin_step()
@@ -54,9 +69,12 @@ def _worker(rank, world, port, out):
     b.begin_step()
     for p in m.parameters():                      # stand-in for the wgrad kernels: rank-dependent gradients
         p.grad.fill_(float(rank + 1))
+    d6 = 6 * CFG["d_model"]
     for i in reversed(range(CFG["n_layers"])):    # blocks finish backward in reverse order
         m.transformer.blocks[i]._stage.after_backward()
-    b.finish_step()
+        if i == 2:                                # CondBank: the tail group of layers is reduced early ...
+            m.transformer._stage.cond_sink.after_group(2 * d6, 3 * d6)
+    b.finish_step()                               # ... the remaining rows and the biases here
     ok = all(torch.allclose(p.grad, torch.full_like(p.grad, 1.5)) for p in m.parameters())
     # no_sync equivalent: nothing is exchanged
     b.sync_grads = False
