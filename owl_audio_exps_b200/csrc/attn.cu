@@ -96,6 +96,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // setup above overlapped the previous kernel; global memory (TMA loads, lse/delta, stores) from here on
+  pdl_launch();
   const uint32_t tS = tmem_base, tO = tmem_base + 128;
 
   if (warp == 0) {
@@ -275,7 +277,7 @@ static int launch_attn_fwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const
     configured = true;
   }
   const long long grid = static_cast<long long>(p.B) * p.H * p.n_qtiles;
-  attn_fwd_kernel<DH><<<static_cast<unsigned>(grid), kFwdThreads, Cfg::kSmemBytes, s>>>(tmQ, tmK, tmV, p);
+  (void)launch_k(attn_fwd_kernel<DH>, dim3(static_cast<unsigned>(grid)), dim3(kFwdThreads), Cfg::kSmemBytes, s, tmQ, tmK, tmV, p);
   return launch_status();
 }
 

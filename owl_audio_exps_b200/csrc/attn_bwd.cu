@@ -34,6 +34,7 @@ struct AttnBwdParams {
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ o, long long o_sb, long long o_sl,
                   float* __restrict__ delta, int B, int H, int Lq, int dh) {
+  pdl_prologue();
   const int G = dh >> 3;
   const long long total = static_cast<long long>(B) * Lq * H * G;
   const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -161,6 +162,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // setup above overlapped the previous kernel; global memory (TMA loads, lse/delta, stores) from here on
+  pdl_launch();
   const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDQ = tmem_base + 256;
 
   if (warp == 0) {
@@ -326,6 +329,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // setup above overlapped the previous kernel; global memory (TMA loads, lse/delta, stores) from here on
+  pdl_launch();
   const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + DH;
 
   if (warp == 0) {
@@ -461,10 +466,10 @@ static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmDO, cons
   }
   const long long gq = static_cast<long long>(p.B) * p.H * p.n_qtiles;
   const long long gk = static_cast<long long>(p.B) * p.H * p.n_ktiles;
-  attn_bwd_dq_kernel<DH><<<static_cast<unsigned>(gq), kBwdThreads, DqCfg<DH>::kSmemBytes, s>>>(tmQ, tmDO, tmK, tmV, p);
+  (void)launch_k(attn_bwd_dq_kernel<DH>, dim3(static_cast<unsigned>(gq)), dim3(kBwdThreads), DqCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
   int rc = launch_status();
   if (rc != OWL_OK) return rc;
-  attn_bwd_dkv_kernel<DH><<<static_cast<unsigned>(gk), kBwdThreads, DkvCfg<DH>::kSmemBytes, s>>>(tmQ, tmDO, tmK, tmV, p);
+  (void)launch_k(attn_bwd_dkv_kernel<DH>, dim3(static_cast<unsigned>(gk)), dim3(kBwdThreads), DkvCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
   return launch_status();
 }
 
@@ -501,7 +506,7 @@ int owl_attn_bwd(const void* dout, const void* o, int64_t o_sb, int64_t o_sl, co
   cudaStream_t s = static_cast<cudaStream_t>(stream);
 
   const long long total = B * Lq * H * (dh / 8);
-  attn_delta_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, s>>>(
+  (void)launch_k(attn_delta_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, s,
       static_cast<const bf16*>(dout), static_cast<const bf16*>(o), o_sb, o_sl, delta, p.B, p.H, p.Lq,
       static_cast<int>(dh));
   if ((rc = launch_status()) != OWL_OK) return rc;

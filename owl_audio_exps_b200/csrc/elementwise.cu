@@ -34,6 +34,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 // cast / silu
 // ------------------------------------------------------------------------------------------------
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int64_t n) {
+  pdl_prologue();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   const int64_t n8 = n >> 3;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
@@ -49,6 +50,7 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, bf16* __rest
 }
 
 __global__ void silu_bf16_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int64_t n) {
+  pdl_prologue();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   const int64_t n8 = n >> 3;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
@@ -67,6 +69,7 @@ __global__ void silu_bf16_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
 // dz = dy * silu'(z)   (backward of F.silu when it is not fused into a GEMM epilogue)
 __global__ void dsilu_mul_bf16_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ z, bf16* __restrict__ dz,
                                       int64_t n) {
+  pdl_prologue();
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
   const int64_t n8 = n >> 3;
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
@@ -103,6 +106,7 @@ __global__ void __launch_bounds__(kRowThreads)
 adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const bf16* __restrict__ b, int64_t ld_ab,
                  bf16* __restrict__ h, float* __restrict__ rstd_out, int64_t M, int d, int T, float eps,
                  const bf16* __restrict__ y, const bf16* __restrict__ gate, int64_t ld_g, bf16* __restrict__ xsum) {
+  pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
   for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
@@ -167,6 +171,7 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
                      int64_t ld_ab, const float* __restrict__ rstd_in, const bf16* __restrict__ dres,
                      bf16* __restrict__ dx, bf16* __restrict__ da, bf16* __restrict__ db, int64_t ld_dab, int64_t M,
                      int d, int T) {
+  pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
   const bool write_ab = (T == 1) && (da != nullptr);
@@ -234,6 +239,7 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
 __global__ void __launch_bounds__(64)
 frame_reduce_kernel(const bf16* __restrict__ p, const bf16* __restrict__ q, const float* __restrict__ scale,
                     bf16* __restrict__ out_pq, bf16* __restrict__ out_p, int64_t ld_out, int d, int T) {
+  pdl_prologue();
   const int c = (blockIdx.y * 64 + threadIdx.x) * 8;
   if (c >= d) return;
   const int64_t f = blockIdx.x;
@@ -264,6 +270,7 @@ frame_reduce_kernel(const bf16* __restrict__ p, const bf16* __restrict__ q, cons
 // ------------------------------------------------------------------------------------------------
 __global__ void gate_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ c, int64_t ld_c,
                                 const bf16* __restrict__ res, bf16* __restrict__ out, int64_t M, int d, int T) {
+  pdl_prologue();
   const int dv = d >> 3;
   const int64_t total = M * dv;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -288,6 +295,7 @@ __global__ void gate_fwd_kernel(const bf16* __restrict__ x, const bf16* __restri
 __global__ void gate_bwd_kernel(const bf16* __restrict__ dx, const bf16* __restrict__ y, const bf16* __restrict__ c,
                                 int64_t ld_c, bf16* __restrict__ dy, bf16* __restrict__ dc, int64_t ld_dc, int64_t M,
                                 int d, int T) {
+  pdl_prologue();
   const int dv = d >> 3;
   const int64_t total = M * dv;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -318,6 +326,7 @@ __global__ void gate_bwd_kernel(const bf16* __restrict__ dx, const bf16* __restr
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 colsum_kernel(const bf16* __restrict__ x, int64_t ld, float* __restrict__ out, int64_t M, int N) {
+  pdl_prologue();
   __shared__ float part[8][256 + 8];
   const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int c = (blockIdx.x * 32 + cg) * 8;
@@ -350,6 +359,7 @@ colsum_kernel(const bf16* __restrict__ x, int64_t ld, float* __restrict__ out, i
 __global__ void kv_append_kernel(const bf16* __restrict__ src, int64_t src_sb, int64_t src_sh,
                                  bf16* __restrict__ cache, int64_t c_sb, int64_t c_sh, int64_t pos, int64_t B, int H,
                                  int64_t Ln, int dh) {
+  pdl_prologue();
   const int64_t per_head = Ln * dh / 8;
   const int64_t total = B * H * per_head;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
@@ -366,6 +376,7 @@ __global__ void kv_append_kernel(const bf16* __restrict__ src, int64_t src_sb, i
 template <int NV>
 __global__ void __launch_bounds__(kRowThreads)
 layer_norm_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int64_t M, int d, float eps) {
+  pdl_prologue();
   const int lane = threadIdx.x & 31;
   const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
   for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
@@ -443,24 +454,21 @@ extern "C" {
 int owl_cast_f32_bf16(const float* src, void* dst, int64_t n, owl_stream_t stream) {
   OWL_REQUIRE(src && dst && n > 0, OWL_ERR_BAD_ARG);
   OWL_REQUIRE(aligned16(src) && aligned16(dst), OWL_ERR_ALIGN);
-  cast_f32_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, static_cast<bf16*>(dst), n);
+  (void)launch_k(cast_f32_bf16_kernel, dim3(grid_for((n + 7) / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), src, static_cast<bf16*>(dst), n);
   return launch_status();
 }
 
 int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream) {
   OWL_REQUIRE(x && y && n > 0, OWL_ERR_BAD_ARG);
   OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
-  silu_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), static_cast<bf16*>(y), n);
+  (void)launch_k(silu_bf16_kernel, dim3(grid_for((n + 7) / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), static_cast<bf16*>(y), n);
   return launch_status();
 }
 
 int owl_dsilu_mul_bf16(const void* dy, const void* z, void* dz, int64_t n, owl_stream_t stream) {
   OWL_REQUIRE(dy && z && dz && n > 0, OWL_ERR_BAD_ARG);
   OWL_REQUIRE(aligned16(dy) && aligned16(z) && aligned16(dz), OWL_ERR_ALIGN);
-  dsilu_mul_bf16_kernel<<<grid_for((n + 7) / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(dy), static_cast<const bf16*>(z), static_cast<bf16*>(dz), n);
+  (void)launch_k(dsilu_mul_bf16_kernel, dim3(grid_for((n + 7) / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(dy), static_cast<const bf16*>(z), static_cast<bf16*>(dz), n);
   return launch_status();
 }
 
@@ -472,8 +480,7 @@ int owl_adaln_modulate_fwd(const void* x, const void* a, const void* b, int64_t 
   OWL_REQUIRE(aligned16(x) && aligned16(h) && aligned16(a) && aligned16(b) && (a == nullptr || ld_ab % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  OWL_DISPATCH_NV(d, (adaln_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
-                         static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
+  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
                          static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps, nullptr, nullptr,
                          0, nullptr)));
   return launch_status();
@@ -489,8 +496,7 @@ int owl_residual_adaln_fwd(const void* x, const void* y, const void* gate, int64
                   aligned16(b) && ld_g % 8 == 0 && (a == nullptr || ld_ab % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  OWL_DISPATCH_NV(d, (adaln_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
-                         static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
+  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
                          static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps,
                          static_cast<const bf16*>(y), static_cast<const bf16*>(gate), ld_g, static_cast<bf16*>(xsum))));
   return launch_status();
@@ -506,15 +512,14 @@ int owl_adaln_modulate_bwd(const void* dh, const void* x, const void* a, int64_t
                   aligned16(db) && (a == nullptr || ld_ab % 8 == 0) && (da == nullptr || ld_dab % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  OWL_DISPATCH_NV(d, (adaln_bwd_row_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
-                         static_cast<const bf16*>(dh), static_cast<const bf16*>(x), static_cast<const bf16*>(a), ld_ab,
+  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_bwd_row_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(dh), static_cast<const bf16*>(x), static_cast<const bf16*>(a), ld_ab,
                          rstd, static_cast<const bf16*>(dres), static_cast<bf16*>(dx), static_cast<bf16*>(da),
                          static_cast<bf16*>(db), ld_dab, M, static_cast<int>(d), static_cast<int>(T))));
   int rc = launch_status();
   if (rc != OWL_OK) return rc;
   if (T > 1 && da != nullptr) {
     dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
-    frame_reduce_kernel<<<grid, 64, 0, s>>>(static_cast<const bf16*>(dh), static_cast<const bf16*>(x), rstd,
+    (void)launch_k(frame_reduce_kernel, dim3(grid), dim3(64), 0, s, static_cast<const bf16*>(dh), static_cast<const bf16*>(x), rstd,
                                             static_cast<bf16*>(da), static_cast<bf16*>(db), ld_dab,
                                             static_cast<int>(d), static_cast<int>(T));
     rc = launch_status();
@@ -527,8 +532,7 @@ int owl_gate_fwd(const void* x, const void* c, int64_t ld_c, const void* res, vo
   OWL_REQUIRE(x && c && out && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
   OWL_REQUIRE(d % 8 == 0, OWL_ERR_UNSUPPORTED);
   OWL_REQUIRE(aligned16(x) && aligned16(c) && aligned16(res) && aligned16(out) && ld_c % 8 == 0, OWL_ERR_ALIGN);
-  gate_fwd_kernel<<<grid_for(M * (d / 8), 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), static_cast<const bf16*>(c), ld_c, static_cast<const bf16*>(res),
+  (void)launch_k(gate_fwd_kernel, dim3(grid_for(M * (d / 8), 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), static_cast<const bf16*>(c), ld_c, static_cast<const bf16*>(res),
       static_cast<bf16*>(out), M, static_cast<int>(d), static_cast<int>(T));
   return launch_status();
 }
@@ -548,8 +552,10 @@ int owl_colsum_bf16(const void* x, int64_t ld, float* out, int accumulate, int64
   const int64_t cap = (static_cast<int64_t>(sm_count()) * 4 + gx - 1) / gx;
   if (splits > cap) splits = cap;
   if (splits < 1) splits = 1;
-  colsum_kernel<<<dim3(gx, static_cast<unsigned>(splits)), 256, 0, s>>>(static_cast<const bf16*>(x), ld, out, M,
-                                                                         static_cast<int>(N));
+  LaunchOpts o;
+  o.pdl = accumulate != 0;  // otherwise the kernel follows the memset node above, not a kernel
+  (void)launch_kx(o, colsum_kernel, dim3(gx, static_cast<unsigned>(splits)), dim3(256), 0, s,
+                  static_cast<const bf16*>(x), ld, out, M, static_cast<int>(N));
   return launch_status();
 }
 
@@ -562,14 +568,13 @@ int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, voi
                   (dc == nullptr || ld_dc % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  gate_bwd_kernel<<<grid_for(M * (d / 8), 256), 256, 0, s>>>(
-      static_cast<const bf16*>(dx), static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c,
+  (void)launch_k(gate_bwd_kernel, dim3(grid_for(M * (d / 8), 256)), dim3(256), 0, s, static_cast<const bf16*>(dx), static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c,
       static_cast<bf16*>(dy), static_cast<bf16*>(dc), ld_dc, M, static_cast<int>(d), static_cast<int>(T));
   int rc = launch_status();
   if (rc != OWL_OK) return rc;
   if (T > 1 && dc != nullptr) {
     dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
-    frame_reduce_kernel<<<grid, 64, 0, s>>>(static_cast<const bf16*>(dx), static_cast<const bf16*>(y), nullptr,
+    (void)launch_k(frame_reduce_kernel, dim3(grid), dim3(64), 0, s, static_cast<const bf16*>(dx), static_cast<const bf16*>(y), nullptr,
                                             static_cast<bf16*>(dc), nullptr, ld_dc, static_cast<int>(d),
                                             static_cast<int>(T));
     rc = launch_status();
@@ -586,8 +591,7 @@ int owl_kv_append(const void* src, int64_t src_sb, int64_t src_sh, void* cache, 
   OWL_REQUIRE(aligned16(src) && aligned16(cache) && src_sb % 8 == 0 && src_sh % 8 == 0 && cache_sb % 8 == 0 &&
                   cache_sh % 8 == 0,
               OWL_ERR_ALIGN);
-  kv_append_kernel<<<grid_for(B * H * Ln * dh / 8, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(src), src_sb, src_sh, static_cast<bf16*>(cache), cache_sb, cache_sh, pos, B,
+  (void)launch_k(kv_append_kernel, dim3(grid_for(B * H * Ln * dh / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(src), src_sb, src_sh, static_cast<bf16*>(cache), cache_sb, cache_sh, pos, B,
       static_cast<int>(H), Ln, static_cast<int>(dh));
   return launch_status();
 }
@@ -597,8 +601,7 @@ int owl_layer_norm_fwd(const void* x, void* y, int64_t M, int64_t d, float eps, 
   OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
   OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  OWL_DISPATCH_NV(d, (layer_norm_fwd_kernel<NV><<<row_grid(M), kRowThreads, 0, s>>>(
-                         static_cast<const bf16*>(x), static_cast<bf16*>(y), M, static_cast<int>(d), eps)));
+  OWL_DISPATCH_NV(d, ((void)launch_k(layer_norm_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<bf16*>(y), M, static_cast<int>(d), eps)));
   return launch_status();
 }
 

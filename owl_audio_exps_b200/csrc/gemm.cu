@@ -28,7 +28,8 @@ static constexpr int BM = 128;
 static constexpr int BK = 64;
 static constexpr int kGemmThreads = 384;  // 4 control warps + 2 epilogue groups of 4 warps
 static constexpr int kSlotBytes = 16384;   // one staging panel: 128 rows x 128 bytes, 128B-swizzled
-static constexpr int kBarRegion = 1024;    // mbarriers + TMEM slot at the front of dynamic smem
+static constexpr int kBarRegion = 2048;    // mbarriers + TMEM slot (first 1 KB), bias rows of the two epilogue groups (2 x 512 B);
+                                           // 2 KB still leaves room for 4 x 48 KB stages + 2 staging panels in 227 KB
 static constexpr int kMaxStages = 8;
 static constexpr int kSmemLimit = 232448;  // 227 KB opt-in maximum per CTA
 
@@ -143,6 +144,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail; from here on
+  // global memory is touched (TMA loads, bias, stores)
+  pdl_wait();
+  pdl_launch();
 
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
 
@@ -238,6 +243,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint8_t* s_out1 = s_out0 + kSlotBytes;
     uint8_t* s_aux0 = stag + 2 * n_out * kSlotBytes + grp * kSlotBytes;            // [2] slots: one per group
     uint8_t* s_aux1 = stag + (2 * n_out + 2 * p.aux0_tma) * kSlotBytes + grp * kSlotBytes;
+    // this tile's bias row, staged once per tile: a global load per 8-column chunk inside the panel loop put
+    // an L2 round trip on the epilogue's critical path 8 times per panel (ncu: 30 % of epilogue samples)
+    // (a group only needs the 2 x 64 columns of ITS panels: 512 B, second KB of the barrier region)
+    float4* s_bias = reinterpret_cast<float4*>(smem + 1024) + grp * 32;
+    const bool has_bias = p.bias != nullptr && !f32out;
     const uint32_t aux_bytes = static_cast<uint32_t>((p.aux0_tma + p.aux1_tma) * kSlotBytes);
     auto issue_aux = [&](int t, int pn) {  // group leader only
       const int m0 = (t % p.tiles_m) * TM + rank * BM, n0 = ((t / p.tiles_m) % p.tiles_n) * BN + pn * 64;
@@ -259,6 +269,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int tn = (t / p.tiles_m) % p.tiles_n;
       const int m0 = tm * TM + rank * BM, n0 = tn * BN;
       const long long row = m0 + r;
+      if (has_bias) {
+        // safe to overwrite: every thread of the group finished reading the previous tile's row before the
+        // last named barrier of that tile; visible to the group after the first named barrier below
+        const int i = threadIdx.x & 127;
+        if (i < 32 && (grp + 2 * (i >> 4)) * 64 < BN) {  // 16 float4 per panel; local panel i>>4 = panel grp + 2*(i>>4)
+          const int col = n0 + (grp + 2 * (i >> 4)) * 64 + (i & 15) * 4;
+          s_bias[i] = col < p.N ? __ldg(reinterpret_cast<const float4*>(p.bias + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN);
@@ -305,9 +324,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             float a[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) a[j] = __uint_as_float(acc[c * 8 + j]);
-            if (p.bias != nullptr && col < p.N) {
-              const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-              const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+            if (has_bias) {
+              const float4 b0 = s_bias[(pn >> 1) * 16 + c * 2];
+              const float4 b1 = s_bias[(pn >> 1) * 16 + c * 2 + 1];
               a[0] += b0.x; a[1] += b0.y; a[2] += b0.z; a[3] += b0.w;
               a[4] += b1.x; a[5] += b1.y; a[6] += b1.z; a[7] += b1.w;
             }
@@ -403,7 +422,7 @@ struct GemmMaps {
 };
 
 template <int BN, bool A_MN, bool B_MN, int CTAS>
-static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
+static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, bool pdl, cudaStream_t stream) {
   static bool configured = false;  // idempotent attribute; a benign race at worst sets it twice
   auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>;
   if (!configured) {
@@ -411,37 +430,25 @@ static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int sm
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
   }
-  if (CTAS == 1) {
-    kern<<<grid, kGemmThreads, smem_bytes, stream>>>(tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
-  } else {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(static_cast<unsigned>(grid));
-    cfg.blockDim = dim3(kGemmThreads);
-    cfg.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;  // the two CTAs of a pair share a TPC
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
-    if (e != cudaSuccess) {
-      (void)cudaGetLastError();
-      return static_cast<int>(e);
-    }
+  LaunchOpts o;
+  o.pdl = pdl;
+  o.cluster_x = CTAS;  // the two CTAs of a pair share a TPC
+  cudaError_t e = launch_kx(o, kern, dim3(static_cast<unsigned>(grid)), dim3(kGemmThreads),
+                            static_cast<size_t>(smem_bytes), stream, tm.A, tm.B, tm.O0, tm.O1, tm.X0, tm.X1, p);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return static_cast<int>(e);
   }
   return launch_status();
 }
 
 template <int BN, int CTAS>
-static int launch_gemm_layout(int layout, const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes,
+static int launch_gemm_layout(int layout, const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, bool pdl,
                               cudaStream_t stream) {
   switch (layout) {
-    case OWL_GEMM_NT: return launch_gemm<BN, false, false, CTAS>(tm, p, grid, smem_bytes, stream);
-    case OWL_GEMM_NN: return launch_gemm<BN, false, true, CTAS>(tm, p, grid, smem_bytes, stream);
-    case OWL_GEMM_TN: return launch_gemm<BN, true, true, CTAS>(tm, p, grid, smem_bytes, stream);
+    case OWL_GEMM_NT: return launch_gemm<BN, false, false, CTAS>(tm, p, grid, smem_bytes, pdl, stream);
+    case OWL_GEMM_NN: return launch_gemm<BN, false, true, CTAS>(tm, p, grid, smem_bytes, pdl, stream);
+    case OWL_GEMM_TN: return launch_gemm<BN, true, true, CTAS>(tm, p, grid, smem_bytes, pdl, stream);
     default: return OWL_ERR_BAD_ARG;
   }
 }
@@ -598,7 +605,9 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   const int smem_bytes = 1024 + kBarRegion + stages * stage_bytes + plan.n_slots * kSlotBytes;
 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  bool pdl = true;
   if (f32_out && splits > 1 && !epi->accumulate) {
+    pdl = false;  // the kernel follows a memset node, not a kernel
     cudaError_t e = cudaMemset2DAsync(epi->outf, static_cast<size_t>(epi->ldf) * 4, 0, static_cast<size_t>(N) * 4,
                                       static_cast<size_t>(M), s);
     if (e != cudaSuccess) return static_cast<int>(e);
@@ -626,11 +635,11 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   const long long total = static_cast<long long>(tiles_m) * tiles_n * splits;
   const int workers = sms / ctas;
   const int grid = static_cast<int>(total < workers ? total : workers) * ctas;
-  if (ctas == 2) return launch_gemm_layout<256, 2>(layout, tm, p, grid, smem_bytes, s);
+  if (ctas == 2) return launch_gemm_layout<256, 2>(layout, tm, p, grid, smem_bytes, pdl, s);
   switch (bn) {
-    case 64: return launch_gemm_layout<64, 1>(layout, tm, p, grid, smem_bytes, s);
-    case 128: return launch_gemm_layout<128, 1>(layout, tm, p, grid, smem_bytes, s);
-    default: return launch_gemm_layout<256, 1>(layout, tm, p, grid, smem_bytes, s);
+    case 64: return launch_gemm_layout<64, 1>(layout, tm, p, grid, smem_bytes, pdl, s);
+    case 128: return launch_gemm_layout<128, 1>(layout, tm, p, grid, smem_bytes, pdl, s);
+    default: return launch_gemm_layout<256, 1>(layout, tm, p, grid, smem_bytes, pdl, s);
   }
 }
 

@@ -1,6 +1,8 @@
 // Host-side helpers shared by the C-ABI launchers (see host_common.h).
 #include "host_common.h"
 
+#include <stdlib.h>
+
 #include <atomic>
 #include <mutex>
 
@@ -101,6 +103,15 @@ int sm_count() {
     (void)cudaGetLastError();
   }
   return n;
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("OWL_PDL");
+    on = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
 }
 
 }  // namespace owl

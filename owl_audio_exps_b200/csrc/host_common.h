@@ -42,6 +42,49 @@ inline int launch_status(int n = 1) {
   return e == cudaSuccess ? OWL_OK : static_cast<int>(e);
 }
 
+// OWL_PDL=0 turns programmatic dependent launch off (plain stream serialisation).
+bool pdl_enabled();
+
+// Kernel launch used by every product kernel: cudaLaunchKernelEx with the programmatic-stream-serialisation
+// attribute (see sm100.cuh pdl_wait) and, for CTA pairs, the cluster dimension.
+struct LaunchOpts {
+  bool pdl = true;     // false: the preceding stream operation is not a kernel (memset) -> plain serialisation
+  int cluster_x = 1;   // 2: CTA pair
+};
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kx(const LaunchOpts& o, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                             cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (o.pdl && pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (o.cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = static_cast<unsigned>(o.cluster_x);
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<Args&&>(args)...);
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                            Args&&... args) {
+  return launch_kx(LaunchOpts{}, kern, grid, block, smem, stream, static_cast<Args&&>(args)...);
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace owl

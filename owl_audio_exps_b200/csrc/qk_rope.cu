@@ -23,6 +23,7 @@ qk_norm_rope_fwd_kernel(const bf16* __restrict__ qkv, const float* __restrict__ 
                         int64_t q_sh, bf16* __restrict__ k, int64_t k_sb, int64_t k_sh, bf16* __restrict__ v,
                         int64_t v_sb, int64_t v_sh, float* __restrict__ rstd_q, float* __restrict__ rstd_k, int64_t B,
                         int64_t L, int H, int dh, float eps) {
+  pdl_prologue();
   const int G = dh >> 3;
   const int64_t total = B * L * 3 * H * G;
   const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -84,6 +85,7 @@ qk_norm_rope_bwd_kernel(const bf16* __restrict__ dq, const bf16* __restrict__ dk
                         const float* __restrict__ rstd_k, const float* __restrict__ cos_tab,
                         const float* __restrict__ sin_tab, int64_t pos_offset, bf16* __restrict__ dqkv, int64_t B,
                         int64_t L, int H, int dh) {
+  pdl_prologue();
   const int G = dh >> 3;
   const int64_t total = B * L * 3 * H * G;
   const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -150,6 +152,7 @@ qk_norm_rope_bwd_kernel(const bf16* __restrict__ dq, const bf16* __restrict__ dk
 __global__ void __launch_bounds__(256)
 rope_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ cos_tab, const float* __restrict__ sin_tab,
                   int64_t pos_offset, bf16* __restrict__ y, int64_t R, int64_t L, int dh, int inverse) {
+  pdl_prologue();
   const int half = dh >> 1, Q = half >> 2;
   const int64_t total = R * L * Q;
   const int64_t t = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -215,8 +218,7 @@ int owl_qk_norm_rope_fwd(const void* qkv, const float* cos_tab, const float* sin
     return OWL_ERR_ALIGN;
   const int64_t total = B * L * 3 * H * (dh / 8);
   const int64_t blocks = (total + 255) / 256;
-  qk_norm_rope_fwd_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(qkv), cos_tab, sin_tab, pos_offset, static_cast<bf16*>(q), q_sb, q_sh,
+  (void)launch_k(qk_norm_rope_fwd_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(qkv), cos_tab, sin_tab, pos_offset, static_cast<bf16*>(q), q_sb, q_sh,
       static_cast<bf16*>(k), k_sb, k_sh, static_cast<bf16*>(v), v_sb, v_sh, rstd_q, rstd_k, B, L, static_cast<int>(H),
       static_cast<int>(dh), eps);
   return launch_status();
@@ -236,8 +238,7 @@ int owl_qk_norm_rope_bwd(const void* dq, const void* dk, const void* dv, int64_t
     return OWL_ERR_ALIGN;
   const int64_t total = B * L * 3 * H * (dh / 8);
   const int64_t blocks = (total + 255) / 256;
-  qk_norm_rope_bwd_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(dq), static_cast<const bf16*>(dk), static_cast<const bf16*>(dv), g_sb, g_sh,
+  (void)launch_k(qk_norm_rope_bwd_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(dq), static_cast<const bf16*>(dk), static_cast<const bf16*>(dv), g_sb, g_sh,
       static_cast<const bf16*>(q), q_sb, q_sh, static_cast<const bf16*>(k), k_sb, k_sh, rstd_q, rstd_k, cos_tab,
       sin_tab, pos_offset, static_cast<bf16*>(dqkv), B, L, static_cast<int>(H), static_cast<int>(dh));
   return launch_status();
@@ -249,8 +250,7 @@ int owl_rope_apply(const void* x, const float* cos_tab, const float* sin_tab, in
   if (dh % 8 != 0) return OWL_ERR_UNSUPPORTED;
   if (!aligned16(x) || !aligned16(y) || !aligned16(cos_tab) || !aligned16(sin_tab)) return OWL_ERR_ALIGN;
   const int64_t total = R * L * (dh / 8);
-  rope_apply_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), cos_tab, sin_tab, pos_offset, static_cast<bf16*>(y), R, L, static_cast<int>(dh),
+  (void)launch_k(rope_apply_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), cos_tab, sin_tab, pos_offset, static_cast<bf16*>(y), R, L, static_cast<int>(dh),
       inverse);
   return launch_status();
 }

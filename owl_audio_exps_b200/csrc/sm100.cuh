@@ -236,6 +236,19 @@ __device__ __forceinline__ uint32_t n_clusters_x() {
   asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r));
   return r;
 }
+// Programmatic dependent launch (PDL).  Every product kernel is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization (host_common.h: launch_k), so its CTAs may be scheduled while
+// the previous kernel in the stream is still draining: its prologue (barrier init, TMEM allocation, descriptor
+// prefetch, index math) overlaps that kernel's tail.  pdl_wait() blocks until the previous kernel has completed and
+// its writes are visible -- it must precede the first global-memory access; pdl_launch() lets the NEXT kernel
+// start being scheduled.  Both are no-ops when the kernel was launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() {
+  pdl_wait();
+  pdl_launch();
+}
+
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
