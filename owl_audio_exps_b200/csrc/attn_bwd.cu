@@ -288,7 +288,10 @@ struct DkvCfg {
   static constexpr int kTmemCols = 512;  // S [0,128), dP [128,256), dV [256,256+DH), dK [256+DH, 256+2DH)
 };
 
-template <int DH>
+// FUSE_DQ (DH = 64, the whole problem is ONE query tile x ONE key tile, e.g. audio.yml's L = 120): this CTA also
+// holds the only dS tile any query row will ever see, so dQ = dS K is one more MMA into TMEM columns [384, 448)
+// and the separate dq kernel (which recomputes S and dP) is not launched.
+template <int DH, bool FUSE_DQ>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
                     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
@@ -332,6 +335,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   pdl_wait();  // setup above overlapped the previous kernel; global memory (TMA loads, lse/delta, stores) from here on
   pdl_launch();
   const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + DH;
+  const uint32_t tDQ = tmem_base + 256 + 2 * DH;  // FUSE_DQ only (DH = 64: columns [384, 448))
 
   if (warp == 0) {
     if (lane == 0 && n_q > 0) {
@@ -387,6 +391,12 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int k = 0; k < kTile / 16; ++k)
           umma_bf16_ss(tDK, desc_mnmajor(sDS, k), desc_mnmajor(sQ, k), idesc_acc, (it > 0 || k > 0) ? 1u : 0u);
+        if (FUSE_DQ) {  // dQ[i, :] = sum_j dS[i, j] K[j, :]: dS as the K-major A operand, K as the MN-major B operand
+          constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, false, true);
+#pragma unroll
+          for (int k = 0; k < kTile / 16; ++k)
+            umma_bf16_ss(tDQ, desc_kmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+        }
         umma_commit(&qdo_empty[s]);
         umma_commit(acc_done);
         if (kStages == 1 && it + 1 < n_q) issue_sdp(it + 1);
@@ -438,10 +448,19 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       tc_fence_after();
       store_acc_row<DH>(tDV + lane_addr, dvr, j < p.Lk);
       store_acc_row<DH>(tDK + lane_addr, dkr, j < p.Lk);
-    } else if (j < p.Lk) {
-      for (int c = 0; c < DH / 8; ++c) {
-        *reinterpret_cast<uint4*>(dkr + c * 8) = make_uint4(0, 0, 0, 0);
-        *reinterpret_cast<uint4*>(dvr + c * 8) = make_uint4(0, 0, 0, 0);
+      if (FUSE_DQ)  // query row `row` of the single query tile
+        store_acc_row<DH>(tDQ + lane_addr, p.dq + b * p.dq_sb + h * p.dq_sh + static_cast<long long>(row) * DH,
+                          row < p.Lq);
+    } else {
+      if (j < p.Lk) {
+        for (int c = 0; c < DH / 8; ++c) {
+          *reinterpret_cast<uint4*>(dkr + c * 8) = make_uint4(0, 0, 0, 0);
+          *reinterpret_cast<uint4*>(dvr + c * 8) = make_uint4(0, 0, 0, 0);
+        }
+      }
+      if (FUSE_DQ && row < p.Lq) {
+        bf16* dqr = p.dq + b * p.dq_sb + h * p.dq_sh + static_cast<long long>(row) * DH;
+        for (int c = 0; c < DH / 8; ++c) *reinterpret_cast<uint4*>(dqr + c * 8) = make_uint4(0, 0, 0, 0);
       }
     }
   }
@@ -455,21 +474,32 @@ template <int DH>
 static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmDO, const CUtensorMap& tmK,
                            const CUtensorMap& tmV, const AttnBwdParams& p, cudaStream_t s) {
   static bool configured = false;
+  constexpr bool kCanFuse = DH == 64;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(attn_bwd_dq_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          DqCfg<DH>::kSmemBytes);
     if (e != cudaSuccess) return static_cast<int>(e);
-    e = cudaFuncSetAttribute(attn_bwd_dkv_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(attn_bwd_dkv_kernel<DH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              DkvCfg<DH>::kSmemBytes);
     if (e != cudaSuccess) return static_cast<int>(e);
+    if (kCanFuse) {
+      e = cudaFuncSetAttribute(attn_bwd_dkv_kernel<DH, kCanFuse>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               DkvCfg<DH>::kSmemBytes);
+      if (e != cudaSuccess) return static_cast<int>(e);
+    }
     configured = true;
   }
   const long long gq = static_cast<long long>(p.B) * p.H * p.n_qtiles;
   const long long gk = static_cast<long long>(p.B) * p.H * p.n_ktiles;
+  if (kCanFuse && p.n_qtiles == 1 && p.n_ktiles == 1) {  // single tile: dq rides on the dkv kernel
+    (void)launch_k(attn_bwd_dkv_kernel<DH, kCanFuse>, dim3(static_cast<unsigned>(gk)), dim3(kBwdThreads),
+                   DkvCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
+    return launch_status();
+  }
   (void)launch_k(attn_bwd_dq_kernel<DH>, dim3(static_cast<unsigned>(gq)), dim3(kBwdThreads), DqCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
   int rc = launch_status();
   if (rc != OWL_OK) return rc;
-  (void)launch_k(attn_bwd_dkv_kernel<DH>, dim3(static_cast<unsigned>(gk)), dim3(kBwdThreads), DkvCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
+  (void)launch_k(attn_bwd_dkv_kernel<DH, false>, dim3(static_cast<unsigned>(gk)), dim3(kBwdThreads), DkvCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
   return launch_status();
 }
 
