@@ -198,7 +198,7 @@ def run_owl(args):
     torch.manual_seed(0)
     model = N.DiT(cfg).to(dev)                       # fp32 master weights, reference init
     n_params = sum(p.numel() for p in model.parameters())
-    buckets = engine.GradBuckets(model)
+    buckets = engine.GradBuckets(model, wgrad_side_stream=os.environ.get("OWL_WGRAD_SIDE", "1") != "0")
     g = torch.Generator().manual_seed(1000 + rank)   # each rank draws its own batch (DistributedSampler analogue)
     host = [torch.randn(B, L, d, generator=g).to(torch.bfloat16).pin_memory(),
             torch.randn(B, F_, d, generator=g).to(torch.bfloat16).pin_memory(),

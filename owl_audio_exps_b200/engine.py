@@ -69,7 +69,7 @@ def _align(n: int, a: int = 64) -> int:
 
 class GradBuckets:
     def __init__(self, model: torch.nn.Module, process_group=None, comm_stream: Optional[torch.cuda.Stream] = None,
-                 average: bool = True):
+                 average: bool = True, wgrad_side_stream: bool = True):
         from .nn.attn import DiT, DiTBlock
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
@@ -128,6 +128,10 @@ class GradBuckets:
             dit._stage.cond_sink = CondSink(flat[:nw].view(n_rows, d), flat[nw:nw + n_rows], self, ci)
             self._cond_low.append(n_rows)
         self.sync_grads = True       # set False on non-final accumulation micro-steps (DDP no_sync equivalent)
+        # weight-gradient GEMMs / bias column sums go to a second stream (functional._Side)
+        self.side_stream = torch.cuda.Stream(dev) if (self.is_cuda and wgrad_side_stream) else None
+        from . import functional as OF
+        OF.set_side_stream(self.side_stream)
 
     # ---- step protocol -------------------------------------------------------------------------
     def begin_step(self):
@@ -157,6 +161,8 @@ class GradBuckets:
             return
         if self.is_cuda:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
+            if self.side_stream is not None:
+                self.comm_stream.wait_stream(self.side_stream)
             with torch.cuda.stream(self.comm_stream):
                 dist.all_reduce(flat, op=dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM, group=self.group)
         else:  # gloo (CPU tests of the host logic): no AVG op
@@ -170,6 +176,8 @@ class GradBuckets:
 
     def finish_step(self):
         """Call after backward: reduce the non-block bucket and join the communication stream."""
+        from . import functional as OF
+        OF.side_join()
         if self.sync_grads:
             for ci, (dit, gi, nw, d) in enumerate(self.cond_stacks):
                 low = self._cond_low[ci]           # weight rows not reduced yet (all of them on the per-block path)
@@ -185,6 +193,8 @@ class GradBuckets:
         return sum(f.numel() * 4 for f in self.flats)
 
     def detach(self):
+        from . import functional as OF
+        OF.set_side_stream(None)
         for dit, gi, nw, d in self.cond_stacks:
             dit._stage.cond_sink = None
         for blk in self.blocks:

@@ -151,13 +151,66 @@ def _sink(p: torch.Tensor):
     return getattr(p, "_owl_grad_sink", None)
 
 
+class _Side:
+    """Weight-gradient side stream (installed by engine.GradBuckets; None = everything on the current stream).
+
+    Weight gradients and bias column sums have no consumer until the gradient exchange, so with bucket sinks
+    they are enqueued on a second stream: their persistent CTAs fill the SMs the main chain's partial waves,
+    small memory-bound kernels and kernel boundaries leave idle.  Operands are kept referenced (`keep`) until
+    the main stream has waited on an event recorded behind the side work, so the caching allocator cannot hand
+    their memory to a later main-stream allocation while the side stream still reads it."""
+    stream = None
+    keep: list = []
+    pending: list = []   # [(event recorded on the side stream, tensors to release once the main stream waited on it)]
+
+
+def set_side_stream(stream) -> None:
+    _Side.stream = stream
+    _Side.keep, _Side.pending = [], []
+
+
+def _on_side(fn, *keep) -> None:
+    side = _Side.stream
+    if side is None:
+        fn()
+        return
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        fn()
+    _Side.keep.extend(keep)
+
+
+def side_mark() -> None:
+    """End of a unit of backward (one block): stamp the side stream, retire what older stamps protected."""
+    side = _Side.stream
+    if side is None:
+        return
+    if _Side.keep:
+        ev = torch.cuda.Event()
+        ev.record(side)
+        _Side.pending.append((ev, _Side.keep))
+        _Side.keep = []
+    while len(_Side.pending) > 2:
+        ev, _ = _Side.pending.pop(0)
+        torch.cuda.current_stream().wait_event(ev)
+
+
+def side_join() -> None:
+    side = _Side.stream
+    if side is None:
+        return
+    torch.cuda.current_stream().wait_stream(side)
+    _Side.keep, _Side.pending = [], []
+
+
 def _wgrad(dy: torch.Tensor, x: torch.Tensor, p: torch.Tensor, M: int) -> Optional[torch.Tensor]:
     """dW[N,K] = dy[M,N]^T x[M,K] in fp32.  Returns the gradient for autograd, or None when it was
     accumulated into the parameter's bucket sink."""
     N, K = p.shape
     sink = _sink(p)
     if sink is not None:
-        ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=sink.view, accumulate=sink.accumulate)
+        _on_side(lambda: ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=sink.view,
+                                  accumulate=sink.accumulate), dy, x)
         return None
     g = torch.empty(N, K, device=dy.device, dtype=f32)
     ops.gemm(OWL_GEMM_TN, dy, x, N, K, M, mode=OWL_EPI_F32, outf=g)
@@ -169,7 +222,7 @@ def _bgrad(dy: torch.Tensor, p: Optional[torch.Tensor]) -> Optional[torch.Tensor
         return None
     sink = _sink(p)
     if sink is not None:
-        ops.colsum(dy, sink.view, accumulate=sink.accumulate)
+        _on_side(lambda: ops.colsum(dy, sink.view, accumulate=sink.accumulate), dy)
         return None
     g = torch.empty(p.shape[0], device=dy.device, dtype=f32)
     ops.colsum(dy, g)
@@ -475,6 +528,7 @@ class CondBank:
         self.accumulate = False
         self.after_group = None  # engine hook: (row_lo, row_hi) of gw finished
         self.want_wgrad = False
+        self.sunk = False        # gw/gb are engine bucket views (then the group wgrads may run on the side stream)
         self.token_grad = None
         self._done = set()
         self._flushed = 0        # layers [_flushed_lo, n_layers) already went through the group wgrad
@@ -520,9 +574,15 @@ class CondBank:
         r0, r1 = lo * w, hi * w
         R = self.mod_all.shape[0]
         dm = self.dmod_all[:, r0:r1]
-        ops.gemm(OWL_GEMM_TN, dm, self.scond16, r1 - r0, self.d, R, mode=OWL_EPI_F32, outf=self.gw[r0:r1],
-                 accumulate=self.accumulate)
-        ops.colsum(dm, self.gb[r0:r1], accumulate=self.accumulate)
+
+        def run():
+            ops.gemm(OWL_GEMM_TN, dm, self.scond16, r1 - r0, self.d, R, mode=OWL_EPI_F32, outf=self.gw[r0:r1],
+                     accumulate=self.accumulate)
+            ops.colsum(dm, self.gb[r0:r1], accumulate=self.accumulate)
+        if self.sunk:
+            _on_side(run, self.dmod_all, self.scond16)
+        else:
+            run()   # private gradient buffers are handed to autograd on the current stream
         if self.after_group is not None:
             self.after_group(r0, r1)
 
@@ -550,6 +610,7 @@ class CondBankFn(torch.autograd.Function):
             if bank.want_wgrad:
                 if sink is not None:
                     bank.gw, bank.gb, bank.accumulate, bank.after_group = sink.gw, sink.gb, sink.accumulate, sink.after_group
+                    bank.sunk = True
                 else:
                     bank.gw = torch.empty(N, d, device=scond16.device, dtype=f32)
                     bank.gb = torch.empty(N, device=scond16.device, dtype=f32)
@@ -587,6 +648,7 @@ class CondBankFn(torch.autograd.Function):
                     grads[i + 1] = _grad_like(bank.gb[r:r + n], P[i + 1])
                 r += n
         bank.dmod_all = bank.mod_all = None
+        side_mark()
         return (dscond, None, *grads)
 
 
@@ -787,6 +849,7 @@ class DiTBlockFn(torch.autograd.Function):
         dx = dx.view(B, L, d)
         if xdtype != bf16:
             dx = dx.to(xdtype)
+        side_mark()
         if ctx.stage.after_backward is not None:
             ctx.stage.after_backward()
         return (dx if need[0] else None, dcond, dscond, dtoken, None, None, None,
