@@ -187,6 +187,9 @@ def run_owl(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NVSwitch carries the 1.24 GB/step exchange on a handful of CTAs; the rest of the SMs stay with backward
+        if os.environ.get("OWL_NCCL_CTAS"):
+            os.environ["NCCL_MAX_CTAS"] = os.environ["OWL_NCCL_CTAS"]
         dist.init_process_group("nccl", device_id=dev)
     w = WORKLOADS[args.workload]
     cfg = types.SimpleNamespace(**w["cfg"])
@@ -245,6 +248,7 @@ def run_owl(args):
     if rank == 0:
         # ---- roofline of the dominant kernel: CUDA events around every launch of one eager step
         fl = step_flops(B, L, d, T, cfg.n_layers, cfg.local_window, cfg.global_window)
+        buckets.sync_grads = False   # rank 0 only from here on: no collectives (the other ranks are at the barrier)
         eager = engine.TrainStep(model, loss_fn, host, buckets=buckets, use_graph=False)
         eager(*step.static_in)
         prof = None
@@ -293,8 +297,18 @@ def run_owl(args):
                                     "sample": sample + "; scaled to full depth"}
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        # End of job without NCCL: the other ranks wait on the rendezvous store (not on a collective) until rank 0
+        # has finished its rank-0-only profiling passes, then every rank leaves without tearing the communicator
+        # down (destroy_process_group after captured NCCL graphs can block).
+        import datetime
+        store = dist.distributed_c10d._get_default_store()
+        if rank == 0:
+            store.set("owl_bench_done", "1")
+        else:
+            store.wait(["owl_bench_done"], datetime.timedelta(seconds=1800))
+        sys.stdout.flush()
+        torch.cuda.synchronize()
+        os._exit(0)
 
 
 def main():

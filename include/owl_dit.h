@@ -41,6 +41,10 @@ const char* owl_error_string(int code);
 /* Number of kernels this library has launched from this process (monotonic; for bench.py's
  * `gpu_launches`).  Host-side counter only. */
 uint64_t owl_launch_count(void);
+/* SMs the persistent GEMM leaves free (0..64, default 0).  The data-parallel engine sets this to the number of
+ * NCCL CTAs when gradients are exchanged concurrently with backward (DDP overlap, rft_trainer.py:96): a persistent
+ * grid sized to ALL SMs would queue one CTA behind the communication kernel and stretch that GEMM to two waves. */
+int owl_set_reserved_sms(int n);
 
 /* ------------------------------------------------------------------------------------------------
  * GEMM  (tcgen05.mma, TMEM accumulators, TMA-fed, persistent, warp-specialised)

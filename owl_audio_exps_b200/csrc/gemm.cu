@@ -565,7 +565,7 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
   p.aux1 = static_cast<const bf16*>(aux1);
   p.lda1 = epi->lda1;
 
-  const int sms = sm_count();
+  const int sms = gemm_sm_count() & ~1;  // even: CTA pairs
   const int kb_total = static_cast<int>((K + BK - 1) / BK);
   int force_ctas = 0;
   if (const char* e = getenv("OWL_GEMM_CTAS")) force_ctas = atoi(e) == 2 ? 2 : (atoi(e) == 1 ? 1 : 0);

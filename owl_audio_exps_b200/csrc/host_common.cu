@@ -105,6 +105,12 @@ int sm_count() {
   return n;
 }
 
+static std::atomic<int> g_reserved_sms{0};
+int gemm_sm_count() {
+  const int n = sm_count() - g_reserved_sms.load(std::memory_order_relaxed);
+  return n < 2 ? 2 : n;
+}
+
 bool pdl_enabled() {
   static int on = -1;
   if (on < 0) {
@@ -134,5 +140,11 @@ const char* owl_error_string(int code) {
 }
 
 uint64_t owl_launch_count(void) { return owl::g_launches.load(); }
+
+int owl_set_reserved_sms(int n) {
+  if (n < 0 || n > 64) return OWL_ERR_BAD_ARG;
+  owl::g_reserved_sms.store(n);
+  return OWL_OK;
+}
 
 }  // extern "C"
