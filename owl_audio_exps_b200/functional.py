@@ -87,6 +87,7 @@ class WeightStage:
 
     def __init__(self):
         self._slots = {}
+        self._bufs = {}             # persistent bf16 staging buffers (shapes are fixed: same memory every step)
         self.after_backward = None  # engine.GradBuckets: called when the owning block's backward is done
         self.cond_sink = None       # engine.CondSink on a DiT stack's stage: bucket views for the CondBank
 
@@ -104,7 +105,10 @@ class WeightStage:
             out = p0.detach()
         else:
             n = sum(p.shape[0] for p in params)
-            out = torch.empty(n, p0.shape[1], device=p0.device, dtype=bf16)
+            out = self._bufs.get(key)
+            if out is None or out.shape != (n, p0.shape[1]) or out.device != p0.device:
+                out = torch.empty(n, p0.shape[1], device=p0.device, dtype=bf16)
+                self._bufs[key] = out
             r = 0
             for p in params:
                 dst = out[r:r + p.shape[0]]
@@ -119,6 +123,7 @@ class WeightStage:
 
     def clear(self):
         self._slots.clear()
+        self._bufs.clear()
 
     # EMA deep-copies the model and checkpoints pickle it: the staged operands never travel
     def __deepcopy__(self, memo):
