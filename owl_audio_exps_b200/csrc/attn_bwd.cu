@@ -274,7 +274,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 // ------------------------------------------------------------------------------------------------
 // dkv kernel
 // ------------------------------------------------------------------------------------------------
-template <int DH>
+template <int DH, bool SINGLE = false>
 struct DkvCfg {
   static constexpr int kStages = DH == 64 ? 2 : 1;
   static constexpr int kTileBytes = kTile * DH * 2;
@@ -286,17 +286,36 @@ struct DkvCfg {
   static constexpr int kOffBar = kOffDS + kTile * kTile * 2;
   static constexpr int kSmemBytes = kOffBar + 128;
   static constexpr int kTmemCols = 512;  // S [0,128), dP [128,256), dV [256,256+DH), dK [256+DH, 256+2DH)
+  static constexpr uint32_t kColDV = 256, kColDK = 256 + DH, kColDQ = 256 + 2 * DH;
+};
+// Single-tile problem (one query tile x one key tile, DH = 64): sized for TWO CTAs per SM, because 512 (b, h) CTAs of a
+// few microseconds each are latency-bound, not throughput-bound.  V is dead once dP = dO V^T has completed, so the
+// P tile starts in V's 16 KB; the dV / dK / dQ accumulators reuse the S / dP columns, which every thread has finished
+// reading (P and dS are in shared memory) before the second group of MMAs is issued.
+template <>
+struct DkvCfg<64, true> {
+  static constexpr int kStages = 1;
+  static constexpr int kTileBytes = kTile * 64 * 2;      // 16 KB
+  static constexpr int kOffV = kTileBytes;               // K at 0
+  static constexpr int kOffP = kOffV;                    // 32 KB: V's panel + 16 KB
+  static constexpr int kOffDS = kOffP + kTile * kTile * 2;
+  static constexpr int kOffQ = kOffDS + kTile * kTile * 2;
+  static constexpr int kOffDO = kOffQ + kTileBytes;
+  static constexpr int kOffBar = kOffDO + kTileBytes;    // 112 KB
+  static constexpr int kSmemBytes = kOffBar + 128;
+  static constexpr int kTmemCols = 256;                  // S [0,128), dP [128,256); then dV [0,64), dK [64,128), dQ [128,192)
+  static constexpr uint32_t kColDV = 0, kColDK = 64, kColDQ = 128;
 };
 
 // FUSE_DQ (DH = 64, the whole problem is ONE query tile x ONE key tile, e.g. audio.yml's L = 120): this CTA also
 // holds the only dS tile any query row will ever see, so dQ = dS K is one more MMA into TMEM columns [384, 448)
 // and the separate dq kernel (which recomputes S and dP) is not launched.
 template <int DH, bool FUSE_DQ>
-__global__ void __launch_bounds__(kBwdThreads, 1)
+__global__ void __launch_bounds__(kBwdThreads, FUSE_DQ ? 2 : 1)
 attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
                     const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                     const AttnBwdParams p) {
-  using Cfg = DkvCfg<DH>;
+  using Cfg = DkvCfg<DH, FUSE_DQ>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kOffBar);
@@ -334,8 +353,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // setup above overlapped the previous kernel; global memory (TMA loads, lse/delta, stores) from here on
   pdl_launch();
-  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + DH;
-  const uint32_t tDQ = tmem_base + 256 + 2 * DH;  // FUSE_DQ only (DH = 64: columns [384, 448))
+  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + Cfg::kColDV, tDK = tmem_base + Cfg::kColDK;
+  const uint32_t tDQ = tmem_base + Cfg::kColDQ;  // FUSE_DQ only
 
   if (warp == 0) {
     if (lane == 0 && n_q > 0) {
@@ -484,7 +503,7 @@ static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmDO, cons
     if (e != cudaSuccess) return static_cast<int>(e);
     if (kCanFuse) {
       e = cudaFuncSetAttribute(attn_bwd_dkv_kernel<DH, kCanFuse>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               DkvCfg<DH>::kSmemBytes);
+                               DkvCfg<DH, kCanFuse>::kSmemBytes);
       if (e != cudaSuccess) return static_cast<int>(e);
     }
     configured = true;
@@ -493,7 +512,7 @@ static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmDO, cons
   const long long gk = static_cast<long long>(p.B) * p.H * p.n_ktiles;
   if (kCanFuse && p.n_qtiles == 1 && p.n_ktiles == 1) {  // single tile: dq rides on the dkv kernel
     (void)launch_k(attn_bwd_dkv_kernel<DH, kCanFuse>, dim3(static_cast<unsigned>(gk)), dim3(kBwdThreads),
-                   DkvCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
+                   DkvCfg<DH, kCanFuse>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
     return launch_status();
   }
   (void)launch_k(attn_bwd_dq_kernel<DH>, dim3(static_cast<unsigned>(gq)), dim3(kBwdThreads), DqCfg<DH>::kSmemBytes, s, tmQ, tmDO, tmK, tmV, p);
