@@ -45,6 +45,9 @@ uint64_t owl_launch_count(void);
  * NCCL CTAs when gradients are exchanged concurrently with backward (DDP overlap, rft_trainer.py:96): a persistent
  * grid sized to ALL SMs would queue one CTA behind the communication kernel and stretch that GEMM to two waves. */
 int owl_set_reserved_sms(int n);
+/* Debug aid: enqueue a one-thread kernel that stores the GPU's %globaltimer (ns) to *dst.  Used by
+ * tools/step_trace.py to time phases INSIDE a replayed CUDA graph; never called on the product path. */
+int owl_debug_timestamp(uint64_t* dst, owl_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * GEMM  (tcgen05.mma, TMEM accumulators, TMA-fed, persistent, warp-specialised)

@@ -90,6 +90,13 @@ __global__ void dsilu_mul_bf16_kernel(const bf16* __restrict__ dy, const bf16* _
   }
 }
 
+// one-thread kernel that stores the GPU's global nanosecond timer: in-graph timeline probe (tools/step_trace.py)
+__global__ void timestamp_kernel(unsigned long long* dst) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  *dst = t;
+}
+
 static inline int grid_for(int64_t work_items, int threads) {
   int64_t blocks = (work_items + threads - 1) / threads;
   const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
@@ -603,6 +610,13 @@ int owl_layer_norm_fwd(const void* x, void* y, int64_t M, int64_t d, float eps, 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   OWL_DISPATCH_NV(d, ((void)launch_k(layer_norm_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<bf16*>(y), M, static_cast<int>(d), eps)));
   return launch_status();
+}
+
+int owl_debug_timestamp(uint64_t* dst, owl_stream_t stream) {
+  OWL_REQUIRE(dst != nullptr, OWL_ERR_BAD_ARG);
+  timestamp_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(dst));
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? OWL_OK : static_cast<int>(e);
 }
 
 }  // extern "C"

@@ -721,6 +721,7 @@ class DiTBlockFn(torch.autograd.Function):
         T = M // R
         need_grad = any(ctx.needs_input_grad)
         W = stage_block_weights(stage, P, with_cond=bank is None)
+        ops.stamp("f0 cast")
         x16 = _as_bf16(x).view(M, d)
         cond16 = _as_bf16(cond).view(R, d)
         if bank is not None:
@@ -735,22 +736,30 @@ class DiTBlockFn(torch.autograd.Function):
         a2, b2, c2 = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], mod[:, 5 * d:6 * d]
 
         h1, rstd1 = ops.adaln_modulate_fwd(x16, a1, b1, T, RMS_EPS, want_rstd=need_grad)
+        ops.stamp("f1 adaln1")
         qkv = torch.empty(B, L, 3 * d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, h1, W["wqkv"], M, 3 * d, d, mode=OWL_EPI_STORE, bias=W["bqkv"], out0=qkv)
+        ops.stamp("f2 qkv")
         o, asaved = _attn_core_fwd(qkv, plan, need_grad)
+        ops.stamp("f3 rope+attn")
         del qkv
         o2 = o.view(M, d)
 
         # out projection (store-only epilogue); its gate and residual ride on the next norm's single pass
         y1 = torch.empty(M, d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, o2, W["wout"], M, d, d, mode=OWL_EPI_STORE, bias=W["bout"], out0=y1)
+        ops.stamp("f4 out")
         x1, h2, rstd2 = ops.residual_adaln_fwd(x16, y1, c1, a2, b2, T, RMS_EPS, want_rstd=need_grad)
+        ops.stamp("f5 res+adaln2")
         z = torch.empty(M, 4 * d, device=x16.device, dtype=bf16)
         s = torch.empty(M, 4 * d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=z, out1=s)
+        ops.stamp("f6 fc1")
         y2 = torch.empty(M, d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, s, W["w2"], M, d, 4 * d, mode=OWL_EPI_STORE, bias=W["b2"], out0=y2)
+        ops.stamp("f7 fc2")
         x2 = ops.gate_fwd(y2, c2, x1, T)
+        ops.stamp("f8 gate2")
 
         if need_grad:
             q, k_all, v_all, lse, rq, rk, offset, mask = asaved
@@ -780,39 +789,49 @@ class DiTBlockFn(torch.autograd.Function):
         dx2 = _as_bf16(dx2).view(M, d)
         c1, a2, c2, a1 = mod[:, 2 * d:3 * d], mod[:, 3 * d:4 * d], mod[:, 5 * d:6 * d], mod[:, 0:d]
         dmod = bank.dmod(ctx.layer) if bank is not None else torch.empty(R, 6 * d, device=dev, dtype=bf16)
+        ops.stamp("b0 start")
 
         # ---- MLP branch: x2 = x1 + c2 * (s W2^T + b2)
         g_b2 = _fresh_or_sink(b2, need[np0 + 7])
         dy2 = ops.gate_bwd(dx2, y2, c2, dmod[:, 5 * d:6 * d], g_b2[0], T, dbias_accumulate=g_b2[1])
+        ops.stamp("b1 gate2")
         g_b2 = None if (g_b2[0] is None or g_b2[2]) else _grad_like(g_b2[0], b2)
         dz = torch.empty(M, 4 * d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dy2, w216, M, 4 * d, d, mode=OWL_EPI_DSILU, aux0=z, out0=dz)
+        ops.stamp("b2 dz")
         g_w2 = _wgrad(dy2, s, w2, M) if need[np0 + 6] else None
         del dy2
         g_b1 = _bgrad(dz, b1) if need[np0 + 5] else None
         dh2 = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dz, w116, M, d, 4 * d, mode=OWL_EPI_STORE, out0=dh2)
+        ops.stamp("b3 dh2")
         g_w1 = _wgrad(dz, h2, w1, M) if need[np0 + 4] else None
         del dz
         dx1 = ops.adaln_modulate_bwd(dh2, x1, a2, rstd2, dx2, dmod[:, 3 * d:4 * d], dmod[:, 4 * d:5 * d], T)
+        ops.stamp("b4 adaln2")
         del dh2
 
         # ---- attention branch: x1 = x + c1 * (o Wout^T + bout)
         g_bout = _fresh_or_sink(bout, need[np0 + 3])
         dy1 = ops.gate_bwd(dx1, y1, c1, dmod[:, 2 * d:3 * d], g_bout[0], T, dbias_accumulate=g_bout[1])
+        ops.stamp("b5 gate1")
         g_bout = None if (g_bout[0] is None or g_bout[2]) else _grad_like(g_bout[0], bout)
         do = torch.empty(B, L, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dy1, wout16, M, d, d, mode=OWL_EPI_STORE, out0=do)
+        ops.stamp("b6 do")
         g_wout = _wgrad(dy1, o2, wout, M) if need[np0 + 2] else None
         del dy1
         dqkv = _attn_core_bwd(do, o2.view(B, L, d), (q, k_all, v_all, lse, rq, rk, offset, mask), cos, sin, L)
+        ops.stamp("b7 attn+rope")
         dqkv2 = dqkv.view(M, 3 * d)
         g_bqkv = _bgrad(dqkv2, bqkv) if need[np0 + 1] else None
         dh1 = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dqkv2, wqkv16, M, d, 3 * d, mode=OWL_EPI_STORE, out0=dh1)
+        ops.stamp("b8 dh1")
         g_wqkv = _wgrad(dqkv2, h1, wqkv, M) if need[np0 + 0] else None
         del dqkv, dqkv2
         dx = ops.adaln_modulate_bwd(dh1, x16, a1, rstd1, dx1, dmod[:, 0:d], dmod[:, d:2 * d], T)
+        ops.stamp("b9 adaln1")
 
         # ---- conditioning projections: mod = silu(cond) Wc^T + bc
         g_wa1 = g_wg1 = g_wa2 = g_wg2 = g_ba1 = g_bg1 = g_ba2 = g_bg2 = None

@@ -45,6 +45,21 @@ def _rows(t: torch.Tensor):
     return t.shape[0], t.shape[1], t.stride(0)
 
 
+# in-graph timeline probe (tools/step_trace.py): TRACE = (uint64 device buffer, [labels]) or None
+TRACE = None
+
+
+def stamp(label: str) -> None:
+    if TRACE is None:
+        return
+    buf, labels = TRACE
+    i = len(labels)
+    if i >= buf.numel():
+        return
+    labels.append(label)
+    _lib.check(_lib.load().owl_debug_timestamp(buf.data_ptr() + 8 * i, _stream()), "owl_debug_timestamp")
+
+
 def launch_count() -> int:
     return int(_lib.load().owl_launch_count())
 
