@@ -326,6 +326,55 @@ __global__ void gate_bwd_kernel(const bf16* __restrict__ dx, const bf16* __restr
   }
 }
 
+// gate backward with the bias gradient of the producing Linear folded in (one pass over dx instead of two kernels):
+//   dy = dx * c[frame];  dbias[n] += sum_m dy[m, n];  if T == 1 also dc = dx * y.
+// Same block shape as colsum_kernel: 32 column groups (256 columns) x 8 row lanes, grid = (ceil(d/256), row_splits).
+__global__ void __launch_bounds__(256)
+gate_bwd_colsum_kernel(const bf16* __restrict__ dx, const bf16* __restrict__ y, const bf16* __restrict__ c,
+                       int64_t ld_c, bf16* __restrict__ dy, bf16* __restrict__ dc, int64_t ld_dc,
+                       float* __restrict__ dbias, int64_t M, int d, int T) {
+  pdl_prologue();
+  __shared__ float part[8][256 + 8];
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cg) * 8;
+  const bool write_dc = (T == 1) && (dc != nullptr);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (col < d) {
+#pragma unroll 4
+    for (int64_t r = static_cast<int64_t>(blockIdx.y) * 8 + rl; r < M; r += static_cast<int64_t>(gridDim.y) * 8) {
+      float fd[8], fc[8], o[8];
+      unpack8(ldg16(dx + r * d + col), fd);
+      unpack8(ldg16(c + (r / T) * ld_c + col), fc);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fd[j] * fc[j];
+      const uint4 packed = pack8(o);
+      stg16(dy + r * d + col, packed);
+      unpack8(packed, o);  // the column sum is taken over the bf16 values the next GEMM will read
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += o[j];
+      if (write_dc) {
+        float fy[8];
+        unpack8(ldg16(y + r * d + col), fy);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = fd[j] * fy[j];
+        stg16(dc + r * ld_dc + col, pack8(o));
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[rl][cg * 8 + j] = acc[j];
+  __syncthreads();
+  const int cc = threadIdx.x;
+  if (blockIdx.x * 256 + cc < d) {
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) sum += part[i][cc];
+    atomicAdd(dbias + blockIdx.x * 256 + cc, sum);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // column sum: out[n] (+)= sum_m x[m, n].  Block = 32 column groups (256 columns) x 8 row lanes;
 // grid = (ceil(N/256), row_splits).  Partial sums meet in shared memory, then one fp32 atomic per
@@ -575,9 +624,28 @@ int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, voi
                   (dc == nullptr || ld_dc % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  (void)launch_k(gate_bwd_kernel, dim3(grid_for(M * (d / 8), 256)), dim3(256), 0, s, static_cast<const bf16*>(dx), static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c,
-      static_cast<bf16*>(dy), static_cast<bf16*>(dc), ld_dc, M, static_cast<int>(d), static_cast<int>(T));
-  int rc = launch_status();
+  int rc;
+  if (dbias != nullptr) {
+    LaunchOpts o;
+    if (!dbias_accumulate) {
+      cudaError_t e = cudaMemsetAsync(dbias, 0, static_cast<size_t>(d) * sizeof(float), s);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      o.pdl = false;  // follows a memset node
+    }
+    const unsigned gx = static_cast<unsigned>((d + 255) / 256);
+    int64_t splits = (M + 31) / 32;
+    const int64_t cap = (static_cast<int64_t>(sm_count()) * 8 + gx - 1) / gx;
+    if (splits > cap) splits = cap;
+    (void)launch_kx(o, gate_bwd_colsum_kernel, dim3(gx, static_cast<unsigned>(splits)), dim3(256), 0, s,
+                    static_cast<const bf16*>(dx), static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c,
+                    static_cast<bf16*>(dy), static_cast<bf16*>(dc), ld_dc, dbias, M, static_cast<int>(d),
+                    static_cast<int>(T));
+  } else {
+    (void)launch_k(gate_bwd_kernel, dim3(grid_for(M * (d / 8), 256)), dim3(256), 0, s, static_cast<const bf16*>(dx),
+                   static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c, static_cast<bf16*>(dy),
+                   static_cast<bf16*>(dc), ld_dc, M, static_cast<int>(d), static_cast<int>(T));
+  }
+  rc = launch_status();
   if (rc != OWL_OK) return rc;
   if (T > 1 && dc != nullptr) {
     dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
@@ -587,7 +655,6 @@ int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, voi
     rc = launch_status();
     if (rc != OWL_OK) return rc;
   }
-  if (dbias != nullptr) rc = owl_colsum_bf16(dy, d, dbias, dbias_accumulate, M, d, stream);
   return rc;
 }
 

@@ -28,14 +28,16 @@ f32 = torch.float32
 class GradSink:
     """What functional._sink returns: the fp32 bucket view of one parameter + whether to add to it."""
 
-    __slots__ = ("view", "owner")
+    __slots__ = ("view", "owner", "pre_zeroed")
 
-    def __init__(self, view: torch.Tensor, owner: "GradBuckets"):
-        self.view, self.owner = view, owner
+    def __init__(self, view: torch.Tensor, owner: "GradBuckets", pre_zeroed: bool = False):
+        self.view, self.owner, self.pre_zeroed = view, owner, pre_zeroed
 
     @property
     def accumulate(self) -> bool:
-        return self.owner.accumulate
+        # bias gradients are column sums built with atomics: the engine zeroes all of them with ONE multi-tensor
+        # kernel at begin_step, so the kernels always add (no memset node in front of every column sum)
+        return self.pre_zeroed or self.owner.accumulate
 
 
 class CondSink:
@@ -43,10 +45,11 @@ class CondSink:
     conditioning projections as one [n_layers*6d, d] matrix (+ [n_layers*6d] biases) inside one flat bucket,
     so a group of layers' weight gradients is ONE GEMM written in place."""
 
-    __slots__ = ("gw", "gb", "owner", "index")
+    __slots__ = ("gw", "gb", "owner", "index", "gb_pre_zeroed")
 
     def __init__(self, gw, gb, owner: "GradBuckets", index: int):
         self.gw, self.gb, self.owner, self.index = gw, gb, owner, index
+        self.gb_pre_zeroed = True   # GradBuckets.begin_step zeroes every bias sink (incl. gb) in one kernel
 
     @property
     def accumulate(self) -> bool:
@@ -103,6 +106,7 @@ class GradBuckets:
         self.rest_index = len(groups)
         groups.append(rest)
         self.flats: List[torch.Tensor] = []
+        self._bias_views: List[torch.Tensor] = []
         dev = next(model.parameters()).device
         for gi, ps in enumerate(groups):
             n = sum(_align(p.numel()) for p in ps)
@@ -114,7 +118,9 @@ class GradBuckets:
                 view = flat[off:off + p.numel()].view_as(p)
                 p.grad = view
                 if gi != self.rest_index:
-                    p._owl_grad_sink = GradSink(view, self)
+                    p._owl_grad_sink = GradSink(view, self, pre_zeroed=p.dim() == 1)
+                    if p.dim() == 1:
+                        self._bias_views.append(view)
                 off += _align(p.numel())
             self.flats.append(flat)
         self.is_cuda = dev.type == "cuda"
@@ -145,6 +151,8 @@ class GradBuckets:
         """Call before the first micro-batch's forward."""
         self.accumulate = False
         self.flats[self.rest_index].zero_()   # these grads arrive through autograd's accumulate-in-place
+        if self._bias_views:
+            torch._foreach_zero_(self._bias_views)
         self._pending.clear()
         self._reset_cond()
 

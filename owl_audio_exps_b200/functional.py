@@ -531,6 +531,7 @@ class CondBank:
         self.scond16 = None
         self.gw = self.gb = None  # fp32 [n_layers*6d, d] / [n_layers*6d]: bucket sink views or private buffers
         self.accumulate = False
+        self.gb_pre_zeroed = False   # engine zeroes the bias-gradient sinks at begin_step: column sums always add
         self.after_group = None  # engine hook: (row_lo, row_hi) of gw finished
         self.want_wgrad = False
         self.sunk = False        # gw/gb are engine bucket views (then the group wgrads may run on the side stream)
@@ -583,7 +584,7 @@ class CondBank:
         def run():
             ops.gemm(OWL_GEMM_TN, dm, self.scond16, r1 - r0, self.d, R, mode=OWL_EPI_F32, outf=self.gw[r0:r1],
                      accumulate=self.accumulate)
-            ops.colsum(dm, self.gb[r0:r1], accumulate=self.accumulate)
+            ops.colsum(dm, self.gb[r0:r1], accumulate=self.accumulate or self.gb_pre_zeroed)
         if self.sunk:
             _on_side(run, self.dmod_all, self.scond16)
         else:
@@ -616,6 +617,7 @@ class CondBankFn(torch.autograd.Function):
                 if sink is not None:
                     bank.gw, bank.gb, bank.accumulate, bank.after_group = sink.gw, sink.gb, sink.accumulate, sink.after_group
                     bank.sunk = True
+                    bank.gb_pre_zeroed = getattr(sink, "gb_pre_zeroed", False)
                 else:
                     bank.gw = torch.empty(N, d, device=scond16.device, dtype=f32)
                     bank.gb = torch.empty(N, device=scond16.device, dtype=f32)
