@@ -472,12 +472,13 @@ static int stages_for(int bn, int n_slots, int ctas = 1) {
 static GemmPlan plan_gemm(long long M, long long N, int kb_total, bool can_split, int n_slots, int sms, int force_ctas) {
   GemmPlan best{64, 1, 2, n_slots, 1};
   double best_cost = 1e300;
-  // {tile width, CTAs per tile, relative time per k-block of one tile (measured on B200)}: a CTA pair runs a
-  // 256x256 tile (twice the flops) in ~1.35x the time of a single CTA's 128x256 tile because each SM pulls
-  // only half of B through L2; 128-/64-wide single-CTA tiles are operand-bandwidth bound.
+  // {tile width, CTAs per tile, relative time per k-block of one tile (measured on B200, tools/gemm_one.py and
+  // tools/gemm_sweep.py)}: a CTA pair finishes its 256x256 tile in ~0.95x the time one CTA needs for 128x256 (each SM
+  // pulls only half of B through L2 and shared memory: -5..9 % on the conditioning-bank GEMMs, equal on the K = 1024
+  // block shapes); 128-/64-wide single-CTA tiles are operand-bandwidth bound.
   const int cand_bn[4] = {256, 256, 128, 64};
   const int cand_ctas[4] = {2, 1, 1, 1};
-  const double eff[4] = {1.35, 1.0, 1.6, 2.8};
+  const double eff[4] = {0.95, 1.0, 1.6, 2.8};
   for (int i = 0; i < 4; ++i) {
     const int bn = cand_bn[i], ctas = cand_ctas[i];
     if (force_ctas && ctas != force_ctas) continue;
