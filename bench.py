@@ -6,8 +6,9 @@
 One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for what every field means.
   value      whole-job tokens/s, inputs resident in HBM when the timed region starts (CUDA-graph replay)
   e2e        same metric through the public call (DiT forward/backward via engine.TrainStep) with the
-             step's inputs in PINNED HOST memory: H2D copy of x/cond/target and D2H read of the loss
-             are inside the timed region, every step
+             step's inputs in PINNED HOST memory: H2D copy of x/cond/target (double-buffered on a copy stream:
+             step i+1's copy overlaps step i's compute, TrainStep.prefetch) and D2H read of the loss are inside
+             the timed region, every step
   roofline   the dominant kernel (tcgen05 GEMM for audio/av, tcgen05 attention for dit_v4) against the
              measured bf16 peak: algorithmic FLOPs / CUDA-event time of its launches inside a step
   cpu_baseline   the oracle port (oracle/dit_oracle.py, plain torch CPU) on the host cores, bounded sample
@@ -222,9 +223,13 @@ def run_owl(args):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record()
-        for _ in range(n):
+        if from_host:
+            step.prefetch(*host)                     # H2D of the first step's inputs (inside the timed region)
+        for i in range(n):
             if from_host:
-                loss = step(*host)
+                loss = step()                        # consumes the staged inputs, runs the step
+                if i + 1 < n:
+                    step.prefetch(*host)             # H2D of the next step's inputs overlaps this step's compute
                 _ = loss.item()                      # D2H read of the step's result, every step
             else:
                 step(*step.static_in)
@@ -242,7 +247,8 @@ def run_owl(args):
     with ClockSampler(local) as clk:
         ms = timed(args.steps, False)
     for _ in range(2):
-        step(*host)
+        step.prefetch(*host)
+        step()
     ms_e2e = timed(args.steps, True)
     tokens = B * L * world
     value = tokens * args.steps / (ms * 1e-3)
@@ -253,6 +259,8 @@ def run_owl(args):
         # ---- roofline of the dominant kernel: CUDA events around every launch of one eager step
         fl = step_flops(B, L, d, T, cfg.n_layers, cfg.local_window, cfg.global_window)
         buckets.sync_grads = False   # rank 0 only from here on: no collectives (the other ranks are at the barrier)
+        from owl_audio_exps_b200 import functional as OF
+        OF.set_side_stream(None)     # per-launch event timing needs every kernel serialised on one stream
         eager = engine.TrainStep(model, loss_fn, host, buckets=buckets, use_graph=False)
         eager(*step.static_in)
         prof = None

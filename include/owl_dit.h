@@ -115,6 +115,9 @@ int owl_gemm_bf16_check(int layout, int64_t M, int64_t N, int64_t K, const void*
 /* dst[i] = bf16(src[i])  -- fp32 master weights -> bf16 operands (what autocast does per forward,
  * rft_trainer.py:146).  n elements, n % 8 == 0 not required. */
 int owl_cast_f32_bf16(const float* src, void* dst, int64_t n, owl_stream_t stream);
+/* `count` casts in one launch per 8 tensors (every ns[i] a multiple of 8): a block's weight matrices staged together. */
+int owl_cast_f32_bf16_multi(const float* const* srcs, void* const* dsts, const int64_t* ns, int count,
+                            owl_stream_t stream);
 
 /* y = silu(x), bf16, n elements                                    (modulation.py:17,38)         */
 int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream);

@@ -46,6 +46,7 @@ SIGNATURES = {
     "owl_error_string": ([C.c_int], C.c_char_p),
     "owl_launch_count": ([], C.c_uint64),
     "owl_set_reserved_sms": ([C.c_int], C.c_int),
+    "owl_cast_f32_bf16_multi": ([vp, vp, vp, C.c_int, vp], C.c_int),
     "owl_debug_timestamp": ([vp, vp], C.c_int),
     "owl_gemm_bf16": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp], C.c_int),
     "owl_gemm_bf16_check": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, vp, i64, vp], C.c_int),

@@ -90,6 +90,33 @@ __global__ void dsilu_mul_bf16_kernel(const bf16* __restrict__ dy, const bf16* _
   }
 }
 
+// Several fp32 -> bf16 casts in ONE launch (a block's weight matrices are separate nn.Parameters; eight launches of
+// 1-4 us each per layer were mostly launch gaps).  Segment i owns blocks [blk0[i], blk0[i+1]).
+struct CastSegs {
+  const float* src[8];
+  bf16* dst[8];
+  long long n8[8];   // elements / 8
+  int blk0[9];
+  int count;
+};
+__global__ void __launch_bounds__(256) cast_multi_kernel(const CastSegs s) {
+  pdl_prologue();
+  int i = 0;
+  while (i + 1 < s.count && static_cast<int>(blockIdx.x) >= s.blk0[i + 1]) ++i;
+  const int local = static_cast<int>(blockIdx.x) - s.blk0[i];
+  const long long stride = static_cast<long long>(s.blk0[i + 1] - s.blk0[i]) * blockDim.x;
+  const float4* src = reinterpret_cast<const float4*>(s.src[i]);
+  bf16* dst = s.dst[i];
+#pragma unroll 2
+  for (long long j = static_cast<long long>(local) * blockDim.x + threadIdx.x; j < s.n8[i]; j += stride) {
+    const float4 a = __ldg(src + 2 * j);
+    const float4 b = __ldg(src + 2 * j + 1);
+    uint4 o;
+    o.x = pack_bf16(a.x, a.y); o.y = pack_bf16(a.z, a.w); o.z = pack_bf16(b.x, b.y); o.w = pack_bf16(b.z, b.w);
+    stg16(dst + 8 * j, o);
+  }
+}
+
 // one-thread kernel that stores the GPU's global nanosecond timer: in-graph timeline probe (tools/step_trace.py)
 __global__ void timestamp_kernel(unsigned long long* dst) {
   unsigned long long t;
@@ -684,6 +711,43 @@ int owl_debug_timestamp(uint64_t* dst, owl_stream_t stream) {
   timestamp_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(dst));
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? OWL_OK : static_cast<int>(e);
+}
+
+int owl_cast_f32_bf16_multi(const float* const* srcs, void* const* dsts, const int64_t* ns, int count,
+                            owl_stream_t stream) {
+  OWL_REQUIRE(srcs && dsts && ns && count > 0, OWL_ERR_BAD_ARG);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long cap_total = static_cast<long long>(sm_count()) * 16;
+  for (int base = 0; base < count; base += 8) {
+    const int c = count - base < 8 ? count - base : 8;
+    CastSegs s{};
+    long long total8 = 0;
+    for (int i = 0; i < c; ++i) {
+      OWL_REQUIRE(srcs[base + i] && dsts[base + i] && ns[base + i] > 0, OWL_ERR_BAD_ARG);
+      OWL_REQUIRE(ns[base + i] % 8 == 0, OWL_ERR_UNSUPPORTED);
+      OWL_REQUIRE(aligned16(srcs[base + i]) && aligned16(dsts[base + i]), OWL_ERR_ALIGN);
+      total8 += ns[base + i] / 8;
+    }
+    long long want = (total8 + 256 * 4 - 1) / (256 * 4);  // ~4 chunks of 16 bytes out per thread
+    if (want > cap_total) want = cap_total;
+    if (want < c) want = c;
+    int blk = 0;
+    for (int i = 0; i < c; ++i) {
+      s.src[i] = srcs[base + i];
+      s.dst[i] = static_cast<bf16*>(dsts[base + i]);
+      s.n8[i] = ns[base + i] / 8;
+      s.blk0[i] = blk;
+      long long b = (want * s.n8[i] + total8 - 1) / total8;
+      if (b < 1) b = 1;
+      blk += static_cast<int>(b);
+    }
+    s.blk0[c] = blk;
+    s.count = c;
+    (void)launch_k(cast_multi_kernel, dim3(static_cast<unsigned>(blk)), dim3(256), 0, st, s);
+    int rc = launch_status();
+    if (rc != OWL_OK) return rc;
+  }
+  return OWL_OK;
 }
 
 }  // extern "C"

@@ -235,6 +235,8 @@ class TrainStep:
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.loss: Optional[torch.Tensor] = None
         self.launches_per_step = 0
+        self._copy_stream = None
+        self._have_staged = False
         if use_graph:
             self._capture(warmup)
 
@@ -266,7 +268,32 @@ class TrainStep:
         with torch.cuda.graph(self.graph):
             self.loss = self._eager()
 
+    def prefetch(self, *inputs: torch.Tensor) -> None:
+        """Start the host->device copy of the NEXT step's inputs (pinned host tensors) on a copy stream, into staging
+        buffers, while the current step is still running; the next __call__ without arguments consumes them with a
+        device-to-device copy.  This is the data-loader side of the step (DataLoader(pin_memory=True) +
+        `.to(device, non_blocking=True)` in rft_trainer.py:176-180), double-buffered."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream()
+            self._staging = [torch.empty_like(s) for s in self.static_in]
+            self._staged = torch.cuda.Event()
+            self._consumed = torch.cuda.Event()
+            self._consumed.record()
+        self._copy_stream.wait_event(self._consumed)        # the previous staging contents have been read
+        with torch.cuda.stream(self._copy_stream):
+            for s, t in zip(self._staging, inputs):
+                s.copy_(t, non_blocking=True)
+            self._staged.record()
+        self._have_staged = True
+
     def __call__(self, *inputs: torch.Tensor) -> torch.Tensor:
+        if not inputs and self._have_staged:
+            cur = torch.cuda.current_stream()
+            cur.wait_event(self._staged)
+            for s, t in zip(self.static_in, self._staging):
+                s.copy_(t, non_blocking=True)
+            self._consumed.record()
+            self._have_staged = False
         for s, t in zip(self.static_in, inputs):
             if t is not s:
                 s.copy_(t, non_blocking=True)

@@ -93,33 +93,48 @@ class WeightStage:
 
     def get(self, key: str, params, rows=None) -> torch.Tensor:
         """bf16 [sum(rows), K] concatenation of 2-D `params` (or fp32 concatenation of 1-D biases)."""
-        vers = tuple((p.data_ptr(), p._version, p.dtype) for p in params)
-        hit = self._slots.get(key)
-        if hit is not None and hit[0] == vers and not _capturing():
-            return hit[1]
-        p0 = params[0]
-        if p0.dim() == 1:
-            out = params[0].detach().float() if len(params) == 1 else torch.cat([p.detach().float() for p in params])
-            out = out.contiguous()
-        elif len(params) == 1 and p0.dtype == bf16 and p0.is_contiguous():
-            out = p0.detach()
-        else:
-            n = sum(p.shape[0] for p in params)
-            out = self._bufs.get(key)
-            if out is None or out.shape != (n, p0.shape[1]) or out.device != p0.device:
-                out = torch.empty(n, p0.shape[1], device=p0.device, dtype=bf16)
-                self._bufs[key] = out
-            r = 0
-            for p in params:
-                dst = out[r:r + p.shape[0]]
-                if p.dtype == f32:
-                    ops.cast_f32_bf16(p.detach().contiguous(), dst)
-                else:
-                    dst.copy_(p.detach())
-                r += p.shape[0]
-        if not _capturing():
-            self._slots[key] = (vers, out)
-        return out
+        return self.get_many([(key, params)])[0]
+
+    def get_many(self, items):
+        """[(key, params), ...] -> staged operands; every fp32 -> bf16 cast that is due goes into ONE multi-tensor
+        launch per 8 matrices (ops.cast_f32_bf16_multi) instead of one launch per parameter."""
+        outs, pairs = [], []
+        for key, params in items:
+            vers = tuple((p.data_ptr(), p._version, p.dtype) for p in params)
+            hit = self._slots.get(key)
+            if hit is not None and hit[0] == vers and not _capturing():
+                outs.append(hit[1])
+                continue
+            p0 = params[0]
+            if p0.dim() == 1:
+                out = params[0].detach().float() if len(params) == 1 else torch.cat([p.detach().float() for p in params])
+                out = out.contiguous()
+            elif len(params) == 1 and p0.dtype == bf16 and p0.is_contiguous():
+                out = p0.detach()
+            else:
+                n = sum(p.shape[0] for p in params)
+                out = self._bufs.get(key)
+                if out is None or out.shape != (n, p0.shape[1]) or out.device != p0.device:
+                    out = torch.empty(n, p0.shape[1], device=p0.device, dtype=bf16)
+                    self._bufs[key] = out
+                r = 0
+                for p in params:
+                    dst = out[r:r + p.shape[0]]
+                    if p.dtype == f32:
+                        pairs.append((p.detach().contiguous(), dst))
+                    else:
+                        dst.copy_(p.detach())
+                    r += p.shape[0]
+            if not _capturing():
+                self._slots[key] = (vers, out)
+            outs.append(out)
+        if pairs:
+            if all(s_.numel() % 8 == 0 for s_, _ in pairs):
+                ops.cast_f32_bf16_multi(pairs)
+            else:
+                for s_, d_ in pairs:
+                    ops.cast_f32_bf16(s_, d_)
+        return outs
 
     def clear(self):
         self._slots.clear()
@@ -681,15 +696,11 @@ def stage_block_weights(stage: WeightStage, P, with_cond: bool = True):
     gate1.fc_c, adaln2.fc, gate2.fc_c; modulation.py:10,31) share their input silu(cond), so they are
     staged as ONE [6d, d] operand: columns [a1 | b1 | c1 | a2 | b2 | c2] of a single GEMM."""
     (wqkv, bqkv, wout, bout, w1, b1, w2, b2, wa1, ba1, wg1, bg1, wa2, ba2, wg2, bg2) = P
-    W = dict(
-        wqkv=stage.get("wqkv", [wqkv]), bqkv=stage.get("bqkv", [bqkv]),
-        wout=stage.get("wout", [wout]), bout=stage.get("bout", [bout]),
-        w1=stage.get("w1", [w1]), b1=stage.get("b1", [b1]),
-        w2=stage.get("w2", [w2]), b2=stage.get("b2", [b2]),
-    )
+    items = [("wqkv", [wqkv]), ("bqkv", [bqkv]), ("wout", [wout]), ("bout", [bout]),
+             ("w1", [w1]), ("b1", [b1]), ("w2", [w2]), ("b2", [b2])]
     if with_cond:  # not needed when the stack's CondBank already projected the conditioning
-        W["wc"] = stage.get("wc", [wa1, wg1, wa2, wg2])
-        W["bc"] = stage.get("bc", [ba1, bg1, ba2, bg2])
+        items += [("wc", [wa1, wg1, wa2, wg2]), ("bc", [ba1, bg1, ba2, bg2])]
+    W = dict(zip([k for k, _ in items], stage.get_many(items)))
     return W
 
 

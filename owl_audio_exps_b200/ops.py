@@ -165,6 +165,16 @@ def cast_f32_bf16(src: torch.Tensor, dst: Optional[torch.Tensor] = None) -> torc
     return dst
 
 
+@_prof("cast_f32_bf16")
+def cast_f32_bf16_multi(pairs) -> None:
+    """[(src fp32, dst bf16), ...] contiguous tensors of equal numel per pair, numel % 8 == 0: one launch per 8."""
+    n = len(pairs)
+    srcs = (C.c_void_p * n)(*[s.data_ptr() for s, _ in pairs])
+    dsts = (C.c_void_p * n)(*[d.data_ptr() for _, d in pairs])
+    ns = (C.c_int64 * n)(*[s.numel() for s, _ in pairs])
+    _lib.check(_lib.load().owl_cast_f32_bf16_multi(srcs, dsts, ns, n, _stream()), "owl_cast_f32_bf16_multi")
+
+
 @_prof("silu")
 def silu(x: torch.Tensor) -> torch.Tensor:
     _req(x)

@@ -35,6 +35,10 @@ def case(tag):
         dy, x = g(M, 3 * d), g(M, d)
         o = torch.zeros(3 * d, d, device=dev)
         return lambda: ops.gemm(2, dy, x, 3 * d, d, M, mode=ops.OWL_EPI_F32, outf=o)
+    if tag == "wouttn":
+        dy, x = g(M, d), g(M, d)
+        o = torch.zeros(d, d, device=dev)
+        return lambda: ops.gemm(2, dy, x, d, d, M, mode=ops.OWL_EPI_F32, outf=o)
     if tag == "w1tn":
         dy, x = g(M, 4 * d), g(M, d)
         o = torch.zeros(4 * d, d, device=dev)
