@@ -333,13 +333,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (p.mode == OWL_EPI_STORE) {
               *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(a);
             } else if (p.mode == OWL_EPI_BIAS_SILU) {
+              // the reference's Linear output is bf16 before F.silu (mlp.py:34-35): pack once (F2FP, full rate) and
+              // read the rounded values back with shifts instead of a per-element F2F round trip (quarter rate)
+              const uint4 zp = pack8u(a);
+              unpack8u(zp, a);
               float sv[8];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                a[j] = round_bf16(a[j]);  // the reference's Linear output is bf16 before F.silu (mlp.py:34-35)
-                sv[j] = silu_f(a[j]);
-              }
-              *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(a);
+              for (int j = 0; j < 8; ++j) sv[j] = silu_f(a[j]);
+              *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = zp;
               *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = pack8u(sv);
             } else if (p.mode == OWL_EPI_GATE_RESIDUAL) {
               float res[8], gt[8];
@@ -352,9 +353,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < 8; ++j) gt[j] = 0.f;
               }
-#pragma unroll
-              for (int j = 0; j < 8; ++j) a[j] = round_bf16(a[j]);
-              if (p.has_out1) *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = pack8u(a);
+              const uint4 yp = pack8u(a);
+              unpack8u(yp, a);  // bf16-rounded branch output
+              if (p.has_out1) *reinterpret_cast<uint4*>(s_out1 + panel_off(r, c)) = yp;
 #pragma unroll
               for (int j = 0; j < 8; ++j) res[j] += gt[j] * a[j];
               *reinterpret_cast<uint4*>(s_out0 + panel_off(r, c)) = pack8u(res);
