@@ -54,3 +54,43 @@ def test_bucket_grads_match_autograd(use_graph):
         for k, p in model.named_parameters():
             assert relerr(p.grad, 2 * ref[k]) <= 1e-3, k
     buckets.detach()
+
+
+def test_prefetch_matches_direct_call():
+    """TrainStep.prefetch (H2D of the next batch on a copy stream into staging buffers) + TrainStep() == TrainStep(*batch)."""
+    from owl_audio_exps_b200 import engine
+    fx = load_golden("audio_T1")
+    model = _model(fx)
+    dev_in = [fx["x"].to(DEV), fx["cond"].to(DEV), fx["dy"].to(DEV)]
+    host_a = [t.cpu().pin_memory() for t in dev_in]
+    host_b = [(t * 0.5).cpu().pin_memory() for t in dev_in]
+    buckets = engine.GradBuckets(model)
+    step = engine.TrainStep(model, _loss, dev_in, buckets=buckets, use_graph=True, warmup=2)
+    ref = {}
+    for name, host in (("a", host_a), ("b", host_b)):
+        loss = step(*host).clone()
+        torch.cuda.synchronize()
+        ref[name] = (loss, {k: p.grad.clone() for k, p in model.named_parameters()})
+    step.prefetch(*host_a)
+    la = step().clone()
+    step.prefetch(*host_b)            # overlaps the step above
+    ga = {k: p.grad.clone() for k, p in model.named_parameters()}
+    lb = step().clone()
+    torch.cuda.synchronize()
+    gb = {k: p.grad.clone() for k, p in model.named_parameters()}
+    assert torch.equal(la, ref["a"][0]) and torch.equal(lb, ref["b"][0])
+    for k in ga:
+        assert relerr(ga[k], ref["a"][1][k]) <= 1e-3, k
+        assert relerr(gb[k], ref["b"][1][k]) <= 1e-3, k
+    buckets.detach()
+
+
+def test_cast_multi_matches_single():
+    from owl_audio_exps_b200 import ops
+    g = torch.Generator(device=DEV).manual_seed(0)
+    srcs = [torch.randn(n, device=DEV, generator=g) for n in (1024 * 1024, 8, 3072 * 1024, 64, 1024, 4096 * 1024, 512, 2048,
+                                                              1024 * 16, 40)]
+    dsts = [torch.empty(s.numel(), device=DEV, dtype=torch.bfloat16) for s in srcs]
+    ops.cast_f32_bf16_multi(list(zip(srcs, dsts)))
+    for s, d in zip(srcs, dsts):
+        assert torch.equal(d, s.to(torch.bfloat16))

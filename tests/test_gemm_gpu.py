@@ -127,3 +127,23 @@ def test_gemm_rejects_bad_args():
         ops.gemm(0, a, b, 128, 128, 64, mode=ops.OWL_EPI_STORE)  # no output
     with pytest.raises(RuntimeError):
         ops.gemm(0, a[:, 1:], b, 128, 128, 56, mode=ops.OWL_EPI_STORE, out0=torch.empty(128, 128, device=dev, dtype=bf16))
+
+
+@pytest.mark.parametrize("ctas", ["1", "2"])
+@pytest.mark.parametrize("layout", [0, 1, 2])
+@pytest.mark.parametrize("M,N,K", [(384, 320, 200), (3840, 1024, 1024), (1000, 2048, 520)])
+def test_gemm_single_cta_and_cta_pair(monkeypatch, ctas, layout, M, N, K):
+    """Both tile schedules (one CTA per 128x256 tile; cta_group::2 pair per 256x256 tile) on the same operands,
+    incl. ragged M / N / K: the planner normally picks one per shape, OWL_GEMM_CTAS forces it."""
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    monkeypatch.setenv("OWL_GEMM_CTAS", ctas)
+    a, b, ref = _operands(layout, M, N, K, dev)
+    out = torch.empty(M, N, device=dev, dtype=bf16)
+    bias = torch.randn(N, device=dev)
+    ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_STORE, bias=bias, out0=out)
+    outf = torch.zeros(M, N, device=dev)
+    ops.gemm(layout, a, b, M, N, K, mode=ops.OWL_EPI_F32, outf=outf)
+    torch.cuda.synchronize()
+    assert relerr(out, ref + bias) <= 1e-2
+    assert relerr(outf, ref) <= 1e-4
