@@ -86,12 +86,15 @@ __device__ __forceinline__ uint32_t panel_off(int r, int c) { return r * 128 + (
 // (the tcgen05.ld 32x32b layout); results are packed into a 128B-swizzled shared-memory panel and leave the
 // SM as ONE TMA store per 128x64 (bf16) / 128x32 (fp32) panel, so global writes are full 128-byte lines.
 // Residual / pre-activation / gate operands arrive the same way (TMA load, prefetched one panel ahead).
-template <int BN, bool A_MN, bool B_MN, int CTAS>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
-                 const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
-                 const GemmParams p) {
+// F32ONLY = the fp32-output epilogue (weight gradients) compiled on its own: without the bf16 epilogues' live ranges
+// it fits kF32Regs registers per thread, so 384 threads leave a third of the register file to a co-resident CTA
+// of a memory-bound kernel from another stream (weight gradients run on the side stream, see functional._Side).
+static constexpr int kF32Regs = 104;
+
+template <int BN, bool A_MN, bool B_MN, int CTAS, bool F32ONLY>
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO0,
+                                          const CUtensorMap& tmO1, const CUtensorMap& tmX0, const CUtensorMap& tmX1,
+                                          const GemmParams& p) {
   using Cfg = GemmCfg<BN, CTAS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -234,8 +237,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int r = q * 32 + lane;      // row inside the tile
     const bool leader = (threadIdx.x & 127) == 0;
     const int bar_id = 1 + grp;
-    const bool f32out = p.mode == OWL_EPI_F32;
-    const bool has_aux = (p.aux0_tma | p.aux1_tma) != 0;
+    const bool f32out = F32ONLY || p.mode == OWL_EPI_F32;
+    const bool has_aux = !F32ONLY && (p.aux0_tma | p.aux1_tma) != 0;
     const int P = f32out ? BN / 32 : BN / 64;  // panels per tile
     const int pcols = f32out ? 32 : 64;
     const int n_out = 1 + p.has_out1;
@@ -398,6 +401,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 }
 
+template <int BN, bool A_MN, bool B_MN, int CTAS>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
+                 const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+                 const GemmParams p) {
+  gemm_body<BN, A_MN, B_MN, CTAS, false>(tmA, tmB, tmO0, tmO1, tmX0, tmX1, p);
+}
+
+template <int BN, bool A_MN, bool B_MN, int CTAS>
+__global__ void __maxnreg__(kF32Regs)
+gemm_f32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmO0, const __grid_constant__ CUtensorMap tmO1,
+                const __grid_constant__ CUtensorMap tmX0, const __grid_constant__ CUtensorMap tmX1,
+                const GemmParams p) {
+  gemm_body<BN, A_MN, B_MN, CTAS, true>(tmA, tmB, tmO0, tmO1, tmX0, tmX1, p);
+}
+
 // ------------------------------------------------------------------------------------------------
 // CUDA-core check GEMM (verification aid only)
 // ------------------------------------------------------------------------------------------------
@@ -425,9 +446,13 @@ struct GemmMaps {
 template <int BN, bool A_MN, bool B_MN, int CTAS>
 static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, bool pdl, cudaStream_t stream) {
   static bool configured = false;  // idempotent attribute; a benign race at worst sets it twice
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>;
+  auto kern = p.mode == OWL_EPI_F32 ? gemm_f32_kernel<BN, A_MN, B_MN, CTAS> : gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    e = cudaFuncSetAttribute(gemm_f32_kernel<BN, A_MN, B_MN, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             kSmemLimit);
     if (e != cudaSuccess) return static_cast<int>(e);
     configured = true;
   }
