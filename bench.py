@@ -279,7 +279,10 @@ def run_owl(args):
         dom_gemm = gemm_ms >= att_ms
         ach = gemm_tf if dom_gemm else att_tf
         roofline = {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)" if dom_gemm else "attn fwd/bwd kernels (tcgen05)",
-                    "achieved": ach, "peak": pk["tf"], "unit": "TFLOP/s", "frac": ach / pk["tf"], "traffic": None,
+                    "achieved": ach, "peak": pk["tf"], "unit": "TFLOP/s", "frac": ach / pk["tf"],
+                    # dram__bytes_read+write per GEMM launch, mean over the four block shapes of the ncu --set full
+                    # capture in profiles/r01_ncu_gemm_full.md (audio shapes; algorithmic mean 60 MB: outputs stay in L2)
+                    "traffic": 32.8e6 if (dom_gemm and args.workload == "audio") else None,
                     "peak_source": pk["src"], "launches_per_step": gemm_n if dom_gemm else att_n,
                     "avg_launch_us": 1e3 * (gemm_ms / gemm_n if dom_gemm else att_ms / max(att_n, 1)),
                     "share_of_step_kernel_time": (gemm_ms if dom_gemm else att_ms) / total_ms,
