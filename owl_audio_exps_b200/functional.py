@@ -656,9 +656,11 @@ class CondBankFn(torch.autograd.Function):
             R = bank.mod_all.shape[0]
             if bank.dmod_all is None:
                 bank.dmod_all = torch.zeros_like(bank.mod_all)
-            dscond = torch.empty(R, d, device=wc.device, dtype=bf16)
-            ops.gemm(OWL_GEMM_NN, bank.dmod_all, wc, R, d, N, mode=OWL_EPI_STORE, out0=dscond)
-            dscond = dscond.view(shape).to(dtype)
+            # [R, d] output = few tiles, K = 6d*n_layers = many k-blocks: fp32 output so the planner may split K over
+            # all SMs (TMA reduce-add), then one small cast
+            acc = torch.empty(R, d, device=wc.device, dtype=f32)
+            ops.gemm(OWL_GEMM_NN, bank.dmod_all, wc, R, d, N, mode=OWL_EPI_F32, outf=acc)
+            dscond = ops.cast_f32_bf16(acc).view(shape).to(dtype)
         grads = [None] * len(P)
         if bank.want_wgrad and not ctx.sunk:
             r = 0
