@@ -270,31 +270,55 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
 //   out_p [f, c] = sum_{r in frame f} p[r, c]                       (optional)
 // grid = (frames, ceil(d / 512)); 64 threads x 8 columns.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64)
+static constexpr int kFrLanes = 8;  // row lanes per CTA: the T rows of a frame are split 8 ways, then summed in smem
+
+__global__ void __launch_bounds__(64 * kFrLanes)
 frame_reduce_kernel(const bf16* __restrict__ p, const bf16* __restrict__ q, const float* __restrict__ scale,
                     bf16* __restrict__ out_pq, bf16* __restrict__ out_p, int64_t ld_out, int d, int T) {
   pdl_prologue();
-  const int c = (blockIdx.y * 64 + threadIdx.x) * 8;
-  if (c >= d) return;
+  __shared__ float red[kFrLanes - 1][64][17];
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int c = (blockIdx.y * 64 + tx) * 8;
+  const bool act = c < d;
   const int64_t f = blockIdx.x;
   float apq[8], ap[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) apq[j] = ap[j] = 0.f;
   const int64_t r0 = f * T;
+  if (act) {
 #pragma unroll 4
-  for (int r = 0; r < T; ++r) {
-    float fp[8], fq[8];
-    unpack8(ldg16(p + (r0 + r) * d + c), fp);
-    unpack8(ldg16(q + (r0 + r) * d + c), fq);
-    const float s = scale != nullptr ? __ldg(scale + r0 + r) : 1.f;
+    for (int r = ty; r < T; r += kFrLanes) {
+      float fp[8], fq[8];
+      unpack8(ldg16(p + (r0 + r) * d + c), fp);
+      unpack8(ldg16(q + (r0 + r) * d + c), fq);
+      const float s = scale != nullptr ? __ldg(scale + r0 + r) : 1.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      apq[j] += fp[j] * fq[j] * s;
-      ap[j] += fp[j];
+      for (int j = 0; j < 8; ++j) {
+        apq[j] += fp[j] * fq[j] * s;
+        ap[j] += fp[j];
+      }
     }
   }
-  stg16(out_pq + f * ld_out + c, pack8(apq));
-  if (out_p != nullptr) stg16(out_p + f * ld_out + c, pack8(ap));
+  if (ty > 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      red[ty - 1][tx][j] = apq[j];
+      red[ty - 1][tx][8 + j] = ap[j];
+    }
+  }
+  __syncthreads();
+  if (ty == 0 && act) {
+#pragma unroll
+    for (int l = 0; l < kFrLanes - 1; ++l) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        apq[j] += red[l][tx][j];
+        ap[j] += red[l][tx][8 + j];
+      }
+    }
+    stg16(out_pq + f * ld_out + c, pack8(apq));
+    if (out_p != nullptr) stg16(out_p + f * ld_out + c, pack8(ap));
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -602,7 +626,7 @@ int owl_adaln_modulate_bwd(const void* dh, const void* x, const void* a, int64_t
   if (rc != OWL_OK) return rc;
   if (T > 1 && da != nullptr) {
     dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
-    (void)launch_k(frame_reduce_kernel, dim3(grid), dim3(64), 0, s, static_cast<const bf16*>(dh), static_cast<const bf16*>(x), rstd,
+    (void)launch_k(frame_reduce_kernel, dim3(grid), dim3(64 * kFrLanes), 0, s, static_cast<const bf16*>(dh), static_cast<const bf16*>(x), rstd,
                                             static_cast<bf16*>(da), static_cast<bf16*>(db), ld_dab,
                                             static_cast<int>(d), static_cast<int>(T));
     rc = launch_status();
@@ -676,7 +700,7 @@ int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, voi
   if (rc != OWL_OK) return rc;
   if (T > 1 && dc != nullptr) {
     dim3 grid(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
-    (void)launch_k(frame_reduce_kernel, dim3(grid), dim3(64), 0, s, static_cast<const bf16*>(dx), static_cast<const bf16*>(y), nullptr,
+    (void)launch_k(frame_reduce_kernel, dim3(grid), dim3(64 * kFrLanes), 0, s, static_cast<const bf16*>(dx), static_cast<const bf16*>(y), nullptr,
                                             static_cast<bf16*>(dc), nullptr, ld_dc, static_cast<int>(d),
                                             static_cast<int>(T));
     rc = launch_status();
