@@ -163,17 +163,24 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_wait(s_full, it & 1);
       tc_fence_after();
       const bool full = doc_row == nullptr && lo <= j0 && j0 + kTile <= hi;
+      // One pass over TMEM: the whole score row (128 fp32) is pulled into registers with a single wait, and the S
+      // buffer is handed back to the MMA warp at once, so QK^T of the next KV tile runs under this tile's softmax.
       uint32_t valid[4];
+      uint32_t r[4][32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld_x32(tS + lane_addr + c * 32, r[c]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        valid[c] = full ? 0xffffffffu : chunk_valid_bits(j0 + c * 32, lo, hi, doc_row, dq, p.m.T);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(s_free);
       float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(tS + lane_addr + c * 32, r);
-        valid[c] = full ? 0xffffffffu : chunk_valid_bits(j0 + c * 32, lo, hi, doc_row, dq, p.m.T);
-        tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; ++e)
-          if ((valid[c] >> e) & 1u) mx = fmaxf(mx, __uint_as_float(r[e]));
+          if ((valid[c] >> e) & 1u) mx = fmaxf(mx, __uint_as_float(r[c][e]));
       }
       const float m_new = fmaxf(m_run, mx * p.scale_log2);
       const float m_use = m_new == -INFINITY ? 0.f : m_new;
@@ -185,14 +192,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float rs = 0.f;
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_x32(tS + lane_addr + c * 32, r);
-        tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
-          const float p0 = ((valid[c] >> e) & 1u) ? exp2f(__uint_as_float(r[e]) * p.scale_log2 - m_use) : 0.f;
-          const float p1 = ((valid[c] >> (e + 1)) & 1u) ? exp2f(__uint_as_float(r[e + 1]) * p.scale_log2 - m_use) : 0.f;
+          const float p0 = ((valid[c] >> e) & 1u) ? exp2f(__uint_as_float(r[c][e]) * p.scale_log2 - m_use) : 0.f;
+          const float p1 = ((valid[c] >> (e + 1)) & 1u) ? exp2f(__uint_as_float(r[c][e + 1]) * p.scale_log2 - m_use) : 0.f;
           rs += p0 + p1;
           pk[e >> 1] = pack_bf16(p0, p1);
         }
@@ -201,8 +205,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           *reinterpret_cast<uint4*>(sP + tile_chunk_offset(row, c * 4 + g)) =
               make_uint4(pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
       }
-      tc_fence_before();
-      mbar_arrive(s_free);
       if (it > 0 && !__all_sync(0xffffffffu, alpha == 1.f)) {
 #pragma unroll
         for (int c = 0; c < DH / 16; ++c) {
