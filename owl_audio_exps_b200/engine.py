@@ -143,13 +143,14 @@ class GradBuckets:
         if self.is_cuda and self.world > 1:
             import os
             from . import _lib
-            self.comm_ctas = int(os.environ.get("OWL_COMM_CTAS", "16"))  # measured at N=2: 0 -> 11.90, 16 -> 11.54, 24 -> 11.91 ms
-            _lib.check(_lib.load().owl_set_reserved_sms(min(self.comm_ctas, 64)), "owl_set_reserved_sms")
+            self.comm_ctas = min(int(os.environ.get("OWL_COMM_CTAS", "16")), 64)  # measured at N=2: 0 -> 11.90, 16 -> 11.54, 24 -> 11.91 ms
+        self._reserved = 0
 
     # ---- step protocol -------------------------------------------------------------------------
     def begin_step(self):
         """Call before the first micro-batch's forward."""
         self.accumulate = False
+        self._reserve_sms(0)                  # no exchange in flight during forward: GEMMs use every SM
         self.flats[self.rest_index].zero_()   # these grads arrive through autograd's accumulate-in-place
         if self._bias_views:
             torch._foreach_zero_(self._bias_views)
@@ -171,9 +172,19 @@ class GradBuckets:
             self._reduce(self.flats[gi][r0 * d:r1 * d])
             self._cond_low[ci] = r0
 
+    def _reserve_sms(self, n: int):
+        """SMs the persistent GEMM grids leave free from now on (host-side launch state, so it is also what a graph
+        capture bakes into the kernels launched after this point): 0 during forward, comm_ctas once the first
+        bucket of the step is in flight."""
+        if n != self._reserved and self.is_cuda and self.world > 1:
+            from . import _lib
+            _lib.check(_lib.load().owl_set_reserved_sms(n), "owl_set_reserved_sms")
+            self._reserved = n
+
     def _reduce(self, flat: torch.Tensor):
         if self.world == 1:
             return
+        self._reserve_sms(self.comm_ctas)
         if self.is_cuda:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
             if self.side_stream is not None:
@@ -203,6 +214,7 @@ class GradBuckets:
             self._reduce(self.flats[self.rest_index])
         if self.is_cuda and self.world > 1:
             torch.cuda.current_stream().wait_stream(self.comm_stream)
+            self._reserve_sms(0)
 
     def grad_bytes(self) -> int:
         return sum(f.numel() * 4 for f in self.flats)
