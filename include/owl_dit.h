@@ -122,6 +122,11 @@ int owl_cast_f32_bf16_multi(const float* const* srcs, void* const* dsts, const i
 /* y = silu(x), bf16, n elements                                    (modulation.py:17,38)         */
 int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream);
 
+/* SinCosEmbed (embeddings.py:30-72): out[r] = [sin(t[r]*mult*freqs[i]) | cos(...)], i < half; t fp32 [n_rows],
+ * freqs fp32 [half] (the caller builds exp(-i*log(theta)/(half-1)) as the reference does), out bf16 [n_rows, 2*half]. */
+int owl_sincos_embed(const float* t, const float* freqs, void* out, int64_t n_rows, int half, float mult,
+                     owl_stream_t stream);
+
 /* dz = dy * silu'(z), bf16, n elements: autograd of F.silu where it is not fused into a GEMM
  * epilogue (attn.py:274 FinalLayer.act; standalone MLP)                                           */
 int owl_dsilu_mul_bf16(const void* dy, const void* z, void* dz, int64_t n, owl_stream_t stream);

@@ -203,6 +203,29 @@ def final_layer(x: Tensor, cond: Tensor, W: Dict[str, Tensor], prefix: str) -> T
     return _lin(F.silu(adaln(x, cond, W, prefix + "norm")), W, prefix + "proj")
 
 
+def sincos_embed(t: Tensor, dim: int, theta: float = 300, mult: float = 1000) -> Tensor:
+    """embeddings.py:30-72 (SinCosEmbed): [..] -> [.., dim] = cat(sin, cos) of t*mult*exp(-i*log(theta)/(dim/2-1))."""
+    half = dim // 2
+    step = torch.log(torch.tensor(float(theta))) / (half - 1)
+    freqs = torch.exp(torch.arange(half) * -step).to(t.dtype)
+    arg = (t * mult).unsqueeze(-1) * freqs
+    return torch.cat((torch.sin(arg), torch.cos(arg)), dim=-1)
+
+
+def timestep_embedding(t: Tensor, W: Dict[str, Tensor], prefix: str) -> Tensor:
+    """embeddings.py:74-84 (TimestepEmbedding): SinCosEmbed(512, 300, 1000) -> MLPCustom."""
+    return mlp(sincos_embed(t, 512), W, prefix + "mlp")
+
+
+def audio_rft_core(x: Tensor, t: Tensor, W: Dict[str, Tensor], cfg, rope_tables: List[Tuple[Tensor, Tensor]],
+                   doc_id: Optional[Tensor] = None) -> Tensor:
+    """models/audiorft.py:34-57 (AudioRFTCore.forward): t_embed -> proj_in -> DiT -> FinalLayer."""
+    cond = timestep_embedding(t, W, "t_embed.")
+    h = _lin(x, W, "proj_in")
+    h = dit_forward(h, cond, W, cfg, rope_tables, doc_id=doc_id, prefix="transformer.")
+    return final_layer(h, cond, W, "proj_out.")
+
+
 # ---------------------------------------------------------------------------------------------
 # algorithmic work (SURVEY.md section 8d / BASELINE.md section 3) -- used by bench.py for the roofline basis
 # ---------------------------------------------------------------------------------------------

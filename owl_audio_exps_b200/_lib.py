@@ -52,6 +52,7 @@ SIGNATURES = {
     "owl_gemm_bf16_check": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, vp, i64, vp], C.c_int),
     "owl_cast_f32_bf16": ([vp, vp, i64, vp], C.c_int),
     "owl_silu_bf16": ([vp, vp, i64, vp], C.c_int),
+    "owl_sincos_embed": ([vp, vp, vp, i64, C.c_int, f32, vp], C.c_int),
     "owl_dsilu_mul_bf16": ([vp, vp, vp, i64, vp], C.c_int),
     "owl_adaln_modulate_fwd": ([vp, vp, vp, i64, vp, vp, i64, i64, i64, f32, vp], C.c_int),
     "owl_residual_adaln_fwd": ([vp, vp, vp, i64, vp, vp, i64, vp, vp, vp, i64, i64, i64, f32, vp], C.c_int),

@@ -540,6 +540,25 @@ layer_norm_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int64_t 
     else { constexpr int NV = 16; __VA_ARGS__; }                \
   } while (0)
 
+// Sin/cos feature row of one scalar per row (embeddings.py:30-72 SinCosEmbed): out[r] = [sin(t_r*mult*f_i) | cos(t_r*mult*f_i)],
+// i < half.  The argument is formed in fp32 with the reference's two roundings (t*mult, then *f_i); the file is built with fast
+// math, so sin/cos go through the double-precision routines (arguments reach ~1e3 rad, far outside __sinf's accurate range).
+__global__ void __launch_bounds__(256) sincos_embed_kernel(const float* __restrict__ t, const float* __restrict__ freqs,
+                                                          bf16* __restrict__ out, int64_t n_rows, int half, float mult) {
+  pdl_prologue();
+  const int64_t total = n_rows * half;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / half;
+    const int c = static_cast<int>(i - r * half);
+    const float arg = __fmul_rn(__fmul_rn(t[r], mult), freqs[c]);
+    double sn, cs;
+    sincos(static_cast<double>(arg), &sn, &cs);
+    out[r * (2 * half) + c] = __float2bfloat16(static_cast<float>(sn));
+    out[r * (2 * half) + half + c] = __float2bfloat16(static_cast<float>(cs));
+  }
+}
+
 static inline int row_grid(int64_t M) {
   int64_t blocks = (M + (kRowThreads / 32) - 1) / (kRowThreads / 32);
   const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
@@ -569,6 +588,14 @@ int owl_silu_bf16(const void* x, void* y, int64_t n, owl_stream_t stream) {
   OWL_REQUIRE(x && y && n > 0, OWL_ERR_BAD_ARG);
   OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
   (void)launch_k(silu_bf16_kernel, dim3(grid_for((n + 7) / 8, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), static_cast<bf16*>(y), n);
+  return launch_status();
+}
+
+int owl_sincos_embed(const float* t, const float* freqs, void* out, int64_t n_rows, int half, float mult,
+                     owl_stream_t stream) {
+  OWL_REQUIRE(t && freqs && out && n_rows > 0 && half > 0, OWL_ERR_BAD_ARG);
+  (void)launch_k(sincos_embed_kernel, dim3(grid_for(n_rows * half, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream), t, freqs,
+                 static_cast<bf16*>(out), n_rows, half, mult);
   return launch_status();
 }
 

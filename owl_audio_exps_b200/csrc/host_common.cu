@@ -1,5 +1,6 @@
 // Host-side helpers shared by the C-ABI launchers (see host_common.h).
 #include "host_common.h"
+#include <cstdio>
 
 #include <stdlib.h>
 
@@ -14,17 +15,32 @@ typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static encode_tiled_fn g_encode_raw = nullptr;
+
+// The driver call needs a current context.  A thread that has not made a runtime call yet has none -- autograd's backward
+// thread when a GEMM is the very first op of the backward pass -- and the encode answers CUDA_ERROR_INVALID_CONTEXT:
+// bind the device's primary context (cudaFree(0)) and encode again.
+static CUresult encode_bound(CUtensorMap* m, CUtensorMapDataType dt, cuuint32_t rank, void* base, const cuuint64_t* dims,
+                             const cuuint64_t* strides, const cuuint32_t* box, const cuuint32_t* estr, CUtensorMapInterleave il,
+                             CUtensorMapSwizzle sw, CUtensorMapL2promotion l2, CUtensorMapFloatOOBfill oob) {
+  CUresult r = g_encode_raw(m, dt, rank, base, dims, strides, box, estr, il, sw, l2, oob);
+  if (r == CUDA_ERROR_INVALID_CONTEXT || r == CUDA_ERROR_NOT_INITIALIZED) {
+    (void)cudaFree(nullptr);
+    r = g_encode_raw(m, dt, rank, base, dims, strides, box, estr, il, sw, l2, oob);
+  }
+  return r;
+}
+
 static encode_tiled_fn get_encode() {
-  static encode_tiled_fn fn = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult qres;
     cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres);
-    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) fn = reinterpret_cast<encode_tiled_fn>(p);
+    if (e == cudaSuccess && qres == cudaDriverEntryPointSuccess) g_encode_raw = reinterpret_cast<encode_tiled_fn>(p);
     (void)cudaGetLastError();
   });
-  return fn;
+  return g_encode_raw ? &encode_bound : nullptr;
 }
 
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
@@ -39,6 +55,10 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    fprintf(stderr, "owl: cuTensorMapEncodeTiled(bf16 2d) -> %d: base %p dims (%llu,%llu) ld %llu box (%u,%u)\n", static_cast<int>(r),
+            base, static_cast<unsigned long long>(cols), static_cast<unsigned long long>(rows),
+            static_cast<unsigned long long>(ld_elems), box_cols, box_rows);
   return r == CUDA_SUCCESS ? OWL_OK : OWL_ERR_DRIVER;
 }
 

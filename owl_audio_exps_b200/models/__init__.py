@@ -1,0 +1,2 @@
+"""The callers either side of the DiT stack, mirroring owl_wms/models."""
+from .audiorft import AudioRFT, AudioRFTCore  # noqa: F401

@@ -183,6 +183,18 @@ def silu(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+@_prof("sincos_embed")
+def sincos_embed(t: torch.Tensor, freqs: torch.Tensor, mult: float) -> torch.Tensor:
+    """t fp32 [n] contiguous, freqs fp32 [half] -> bf16 [n, 2*half] = [sin | cos] (embeddings.py:30-72)."""
+    _req(t, torch.float32)
+    _req(freqs, torch.float32)
+    n, half = t.numel(), freqs.numel()
+    out = torch.empty(n, 2 * half, device=t.device, dtype=torch.bfloat16)
+    _lib.check(_lib.load().owl_sincos_embed(t.data_ptr(), freqs.data_ptr(), out.data_ptr(), n, half, float(mult), _stream()),
+               "owl_sincos_embed")
+    return out
+
+
 @_prof("dsilu_mul")
 def dsilu_mul(dy: torch.Tensor, z: torch.Tensor, dz: torch.Tensor) -> torch.Tensor:
     _req(dy), _req(z), _req(dz)

@@ -1,0 +1,90 @@
+"""Parity of the callers either side of the DiT stack (SinCosEmbed / TimestepEmbedding,
+proj_in, FinalLayer, assembled as AudioRFTCore) against the reference model's golden fixture and the CPU oracle.
+Bar: tensor-normalised max relative error <= 2e-2 (bf16), the same as the block stack."""
+import pytest
+import torch
+
+from helpers import audio_cfg, cfg_of, load_golden, relerr
+from oracle import dit_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-2
+DEV = "cuda:0"
+
+
+def _core(cfg, state, rope, dtype=torch.float32):
+    from owl_audio_exps_b200.models import AudioRFTCore
+    model = AudioRFTCore(cfg)
+    model.load_state_dict({k: v.float() for k, v in state.items()}, strict=True)   # the reference's own key names
+    model = model.to(DEV).to(dtype)
+    for blk, (cos, sin) in zip(model.transformer.blocks, rope):
+        blk.attn.rope.cos = cos.to(DEV).float().contiguous()
+        blk.attn.rope.sin = sin.to(DEV).float().contiguous()
+    return model
+
+
+def test_sincos_embed_matches_reference_and_oracle():
+    import owl_audio_exps_b200.nn as N
+    fx = load_golden("audiorft_core")
+    emb = N.SinCosEmbed(512, theta=300, mult=1000)
+    got = emb(fx["t"].to(DEV))
+    assert got.shape == (*fx["t"].shape, 512) and got.dtype == torch.bfloat16
+    # bf16 output of an fp32 argument: one bf16 ulp of a value in [-1, 1] is 2^-8
+    assert (got.float().cpu() - fx["sincos"]).abs().max() <= 2 ** -8
+    # scalars, [b], large arguments (t*mult up to 1e3 rad: needs real range reduction, not the fast-math intrinsic)
+    t = torch.tensor([0.0, 1e-4, 0.5, 0.999, 1.0], device=DEV)
+    assert (emb(t).float().cpu() - O.sincos_embed(t.cpu(), 512)).abs().max() <= 2 ** -8
+    assert emb(0.25, device=DEV).shape == (1, 512)
+    step = N.StepEmbedding(128).to(DEV)
+    assert step(torch.tensor([1.0, 4.0, 128.0], device=DEV)).shape == (3, 128)
+
+
+@pytest.mark.parametrize("regime", ["fp32_params", "bf16_params"])
+def test_audiorft_core_golden(regime):
+    fx = load_golden("audiorft_core")
+    cfg = cfg_of(fx)
+    model = _core(cfg, fx["state"], fx["rope"], torch.float32 if regime == "fp32_params" else torch.bfloat16)
+    x = fx["x"].to(DEV).float().requires_grad_(True)
+    t = fx["t"].to(DEV)
+    assert relerr(model.t_embed(t), fx["cond"]) <= TOL
+    y = model(x, t)
+    assert y.shape == fx["y"].shape
+    assert relerr(y, fx["y"]) <= TOL
+    y.backward(fx["dy"].to(DEV).to(y.dtype))
+    assert relerr(x.grad, fx["dx"]) <= TOL
+    worst = max((relerr(p.grad, fx["grads"][k]), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+
+
+def test_audiorft_core_audio_yml_shape_vs_oracle():
+    """configs/audio.yml width (d=1024, 16 heads, 64 channels, L=120) on 2 layers, against the fp32 CPU oracle."""
+    cfg = audio_cfg(n_layers=2)
+    torch.manual_seed(5)
+    from owl_audio_exps_b200.models import AudioRFT, AudioRFTCore
+    model = AudioRFTCore(cfg).to(DEV)
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() == 1:
+                p.copy_(0.1 * torch.randn_like(p))
+            p.copy_(p.to(torch.bfloat16).float())
+    B, L = 2, 120
+    x = torch.randn(B, L, cfg.channels, device=DEV).to(torch.bfloat16).float().requires_grad_(True)
+    t = torch.rand(B, L, device=DEV)
+    dy = torch.randn(B, L, cfg.channels, device=DEV).to(torch.bfloat16)
+    y = model(x, t)
+    y.backward(dy)
+    W = {k: v.detach().float().cpu().requires_grad_(True) for k, v in model.state_dict().items()}
+    rope = [(b.attn.rope.cos.cpu(), b.attn.rope.sin.cpu()) for b in model.transformer.blocks]
+    xo = x.detach().cpu().requires_grad_(True)
+    yo = O.audio_rft_core(xo, t.cpu(), W, cfg, rope)
+    (yo * dy.float().cpu()).sum().backward()
+    assert relerr(y, yo) <= TOL
+    assert relerr(x.grad, xo.grad) <= TOL
+    worst = max((relerr(p.grad, W[k].grad), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+    # the training wrapper (audiorft.py:60-97): scalar loss, gradients reach every parameter
+    rft = AudioRFT(cfg).to(DEV)
+    loss = rft(torch.randn(B, L, cfg.channels, device=DEV))
+    loss.backward()
+    assert loss.dim() == 0 and torch.isfinite(loss)
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in rft.parameters())

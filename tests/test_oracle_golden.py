@@ -85,3 +85,22 @@ def test_frame_mask_matches_package_descriptor():
         dense = fm.mask_mod(torch.tensor(0), torch.tensor(0), torch.arange(nq)[:, None], torch.arange(nq + off)[None, :])
         ref = O.frame_mask(nq, nq + off, T, win, doc, off, causal)[0, 0]
         assert torch.equal(dense, ref), (T, nq, off, win, causal)
+
+
+def test_audiorft_core_matches_reference():
+    """Oracle restatement of SinCosEmbed / TimestepEmbedding / AudioRFTCore vs the reference model's own outputs
+    (tests/golden/make_golden_audiorft.py): forward, input gradient and every parameter gradient."""
+    fx = load_golden("audiorft_core")
+    cfg = cfg_of(fx)
+    assert fx["flex_vs_dense_fwd_maxabs"] < 5e-6
+    t = fx["t"]
+    assert relerr(O.sincos_embed(t, 512), fx["sincos"]) < TOL
+    W = {k: v.requires_grad_(True) for k, v in _weights(fx).items()}
+    assert relerr(O.timestep_embedding(t, W, "t_embed."), fx["cond"]) < TOL
+    x = fx["x"].float().requires_grad_(True)
+    y = O.audio_rft_core(x, t, W, cfg, fx["rope"])
+    assert relerr(y, fx["y"]) < TOL
+    (y * fx["dy"].float()).sum().backward()
+    assert relerr(x.grad, fx["dx"]) < TOL
+    for k, g in fx["grads"].items():
+        assert relerr(W[k].grad, g) < 5 * TOL, k
