@@ -226,6 +226,37 @@ def audio_rft_core(x: Tensor, t: Tensor, W: Dict[str, Tensor], cfg, rope_tables:
     return final_layer(h, cond, W, "proj_out.")
 
 
+def mouse_embedding(m: Tensor, W: Dict[str, Tensor], prefix: str, dim: int = 512) -> Tensor:
+    """embeddings.py:119-156 (MouseEmbedding): symlog, polar split, angle Linear(2, dim/2) | SinCosEmbed(dim/2) -> MLP."""
+    m = torch.sign(m) * torch.log1p(torch.abs(m))
+    ang = torch.atan2(m[..., 1], m[..., 0])
+    mag = torch.norm(m, dim=-1)
+    ang_emb = _lin(torch.stack([torch.cos(ang), torch.sin(ang)], dim=-1), W, prefix + "angle_proj")
+    return mlp(torch.cat([ang_emb, sincos_embed(mag, dim // 2)], dim=-1), W, prefix + "mlp")
+
+
+def control_embedding(mouse: Tensor, btn: Tensor, W: Dict[str, Tensor], prefix: str) -> Tensor:
+    """embeddings.py:158-184 (ButtonEmbeddding + ControlEmbedding)."""
+    return mouse_embedding(mouse, W, prefix + "mouse.") + mlp(btn * 2 - 1, W, prefix + "button.proj")
+
+
+def game_rft_core(x: Tensor, t: Tensor, mouse: Tensor, btn: Tensor, W: Dict[str, Tensor], cfg,
+                  rope_tables: List[Tuple[Tensor, Tensor]], doc_id: Optional[Tensor] = None,
+                  has_controls: Optional[Tensor] = None) -> Tensor:
+    """models/gamerft.py:33-60 (GameRFTCore.forward)."""
+    b, n, c, h, w = x.shape
+    cond = timestep_embedding(t, W, "t_embed.")
+    if not cfg.uncond:
+        ctrl = control_embedding(mouse, btn, W, "control_embed.")
+        if has_controls is not None:
+            ctrl = torch.where(has_controls[:, None, None], ctrl, torch.zeros_like(ctrl))
+        cond = cond + ctrl
+    tok = x.permute(0, 1, 3, 4, 2).reshape(b, n * h * w, c)
+    tok = dit_forward(_lin(tok, W, "proj_in"), cond, W, cfg, rope_tables, doc_id=doc_id, prefix="transformer.")
+    tok = final_layer(tok, cond, W, "proj_out.")
+    return tok.view(b, n, h, w, c).permute(0, 1, 4, 2, 3)
+
+
 # ---------------------------------------------------------------------------------------------
 # algorithmic work (SURVEY.md section 8d / BASELINE.md section 3) -- used by bench.py for the roofline basis
 # ---------------------------------------------------------------------------------------------

@@ -300,6 +300,15 @@ class _Linear(torch.autograd.Function):
 
 
 def linear(x, weight, bias, stage: WeightStage, key: str, silu_in=False, silu_out=False):
+    K = weight.shape[1]
+    if K % 8:
+        # TMA rows are 16-byte multiples: a narrow input (ButtonEmbeddding's n_buttons, MouseEmbedding's 2 angle features)
+        # is zero-padded to the next multiple of 8; the pad's own autograd slices dW back to [N, K].
+        pad = 8 - K % 8
+        x = torch.nn.functional.pad(x if x.requires_grad else _as_bf16(x), (0, pad))
+        weight = torch.nn.functional.pad(weight, (0, pad))
+        b32 = stage.get(key + ".b", [bias]) if bias is not None else None
+        return _Linear.apply(x, weight, bias, weight.detach().to(bf16), b32, silu_in, silu_out)
     w16 = stage.get(key + ".w", [weight])
     b32 = stage.get(key + ".b", [bias]) if bias is not None else None
     return _Linear.apply(x, weight, bias, w16, b32, silu_in, silu_out)

@@ -2,12 +2,13 @@
 (SURVEY.md section 8f rank 2): SinCosEmbed (:30-72), TimestepEmbedding (:74-84), StepEmbedding (:86-104),
 ConditionEmbedding (:106-117), LearnedPosEnc (:14-28).  The sin/cos features are one kernel writing bf16
 (`owl_sincos_embed`), the MLPs are the tcgen05 GEMMs of nn/mlp.py.  Parameter names and shapes are the
-reference's.  Mouse/Button/ControlEmbedding (:119-184) are not built yet (DESIGN.md "out of scope / next")."""
+reference's; Mouse/Button/ControlEmbedding (:119-184) build the game models' control half of `cond`."""
 import math
 
 import torch
 from torch import nn
 
+from .. import functional as OF
 from .. import ops
 from .mlp import MLPCustom
 
@@ -94,3 +95,48 @@ class ConditionEmbedding(nn.Module):
 
     def forward(self, x):
         return self.mlp(self.embedding(x))
+
+
+class MouseEmbedding(nn.Module):
+    """embeddings.py:119-156: symlog -> polar; angle (cos, sin) through Linear(2, dim/2), magnitude through
+    SinCosEmbed(dim/2); concatenated into the MLP."""
+
+    def __init__(self, dim_out, dim=512):
+        super().__init__()
+        self.angle_proj = nn.Linear(2, dim // 2, bias=False)
+        self.magnitude_embed = SinCosEmbed(dim // 2)
+        self.mlp = MLPCustom(dim, dim * 4, dim_out)
+        self._stage = OF.WeightStage()
+
+    def forward(self, x):
+        with torch.no_grad():
+            x = torch.sign(x) * torch.log1p(torch.abs(x))
+            angles = torch.atan2(x[..., 1], x[..., 0])
+            magnitudes = torch.norm(x, dim=-1)
+            angle_emb = torch.stack([torch.cos(angles), torch.sin(angles)], dim=-1).to(x.dtype)
+            magnitude_emb = self.magnitude_embed(magnitudes)
+        angle_emb = OF.linear(angle_emb, self.angle_proj.weight, None, self._stage, "angle_proj")
+        return self.mlp(torch.cat([angle_emb, magnitude_emb], dim=-1))
+
+
+class ButtonEmbeddding(nn.Module):
+    """embeddings.py:158-168 (the reference's spelling): {0,1} -> {-1,+1} -> MLP."""
+
+    def __init__(self, n_buttons, dim_out, dim=512):
+        super().__init__()
+        self.proj = MLPCustom(n_buttons, dim * 4, dim_out)
+
+    def forward(self, x):
+        return self.proj((x * 2) - 1)
+
+
+class ControlEmbedding(nn.Module):
+    """embeddings.py:170-184: mouse [b,n,2] + button [b,n,n_buttons] -> [b,n,d]."""
+
+    def __init__(self, n_buttons, dim_out, dim=512):
+        super().__init__()
+        self.mouse = MouseEmbedding(dim_out, dim)
+        self.button = ButtonEmbeddding(n_buttons, dim_out, dim)
+
+    def forward(self, mouse, button, has_controls=None):
+        return self.mouse(mouse) + self.button(button)

@@ -1,0 +1,105 @@
+"""Generate tests/golden/audiorft_core.pt and gamerft_core.pt by running the UNMODIFIED reference models
+`owl_wms.models.audiorft.AudioRFTCore` (t_embed -> proj_in -> DiT -> FinalLayer) and `owl_wms.models.gamerft.GameRFTCore`
+(+ ControlEmbedding, patchify) on CPU in fp32, forward + backward.  Build container only (needs
+/root/reference):   python tests/golden/make_golden_models.py
+Same recipe and the same SDPA-for-flex backward substitution as make_golden.py (whose helpers are reused)."""
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import make_golden as G  # noqa: E402  (sets TORCHDYNAMO_DISABLE before torch is imported)
+import torch  # noqa: E402
+
+
+def audiorft(A, flex_real):
+    from owl_wms.models.audiorft import AudioRFTCore
+    cfg = G.make_cfg(d_model=128, n_heads=2, n_layers=2, tokens_per_frame=1, n_frames=64, sample_size=24,
+                     has_audio=True, rope_impl="audio1d", local_window=4, channels=64)
+    torch.manual_seed(321)
+    model = AudioRFTCore(cfg)
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() == 1:
+                p.copy_(0.1 * torch.randn_like(p))
+            p.copy_(G.bf16r(p))
+    B, L = 2, 24
+    g = torch.Generator().manual_seed(4321)
+    x = G.bf16r(torch.randn(B, L, cfg.channels, generator=g)).requires_grad_(True)
+    t = torch.randn(B, L, generator=g).sigmoid()
+    dy = G.bf16r(torch.randn(B, L, cfg.channels, generator=g))
+    A.flex_attention = flex_real
+    with torch.no_grad():
+        y_flex = model(x, t)
+    A.flex_attention = G.dense_flex
+    y = model(x, t)
+    sub_diff = (y - y_flex).abs().max().item()
+    (y * dy).sum().backward()
+    with torch.no_grad():
+        emb = model.t_embed.sincos(t)
+        cond = model.t_embed(t)
+    fx = dict(
+        name="audiorft_core", cfg=dict(vars(cfg)), B=B, L=L, flex_vs_dense_fwd_maxabs=sub_diff,
+        state=dict((k, v.detach().to(torch.bfloat16)) for k, v in model.state_dict().items()),
+        rope=[(blk.attn.rope.cos.clone(), blk.attn.rope.sin.clone()) for blk in model.transformer.blocks],
+        x=x.detach().to(torch.bfloat16), t=t, dy=dy.to(torch.bfloat16), sincos=emb, cond=cond,
+        y=y.detach(), dx=x.grad.clone(), grads=dict((k, p.grad.clone()) for k, p in model.named_parameters()),
+    )
+    torch.save(fx, os.path.join(HERE, "audiorft_core.pt"))
+    print(f"audiorft_core: y absmax {y.abs().max():.3f}  flex-vs-dense fwd diff {sub_diff:.2e}")
+
+
+def gamerft(A, flex_real):
+    from owl_wms.models.gamerft import GameRFTCore
+    cfg = G.make_cfg(d_model=128, n_heads=2, n_layers=2, tokens_per_frame=4, n_frames=8, sample_size=2,
+                     has_audio=False, rope_impl="motion", local_window=2, channels=16, n_buttons=11, uncond=False)
+    torch.manual_seed(654)
+    model = GameRFTCore(cfg)
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() == 1:
+                p.copy_(0.1 * torch.randn_like(p))
+            p.copy_(G.bf16r(p))
+    B, n, c, h = 2, 6, cfg.channels, cfg.sample_size
+    g = torch.Generator().manual_seed(8765)
+    x = G.bf16r(torch.randn(B, n, c, h, h, generator=g)).requires_grad_(True)
+    t = torch.randn(B, n, generator=g).sigmoid()
+    mouse = 3.0 * torch.randn(B, n, 2, generator=g)
+    btn = (torch.rand(B, n, cfg.n_buttons, generator=g) < 0.3).float()
+    has_controls = torch.tensor([True, False])
+    dy = G.bf16r(torch.randn(B, n, c, h, h, generator=g))
+    A.flex_attention = flex_real
+    with torch.no_grad():
+        y_flex = model(x, t, mouse, btn, None, has_controls)
+    A.flex_attention = G.dense_flex
+    y = model(x, t, mouse, btn, None, has_controls)
+    sub_diff = (y - y_flex).abs().max().item()
+    (y * dy).sum().backward()
+    with torch.no_grad():
+        ctrl = model.control_embed(mouse, btn)
+    fx = dict(
+        name="gamerft_core", cfg=dict(vars(cfg)), B=B, flex_vs_dense_fwd_maxabs=sub_diff,
+        state=dict((k, v.detach().to(torch.bfloat16)) for k, v in model.state_dict().items()),
+        rope=[(blk.attn.rope.cos.clone(), blk.attn.rope.sin.clone()) for blk in model.transformer.blocks],
+        x=x.detach().to(torch.bfloat16), t=t, mouse=mouse, btn=btn, has_controls=has_controls, dy=dy.to(torch.bfloat16),
+        ctrl=ctrl, y=y.detach(), dx=x.grad.clone(),
+        # fixture size: gradients of the wide embedding matrices are kept in bf16 (checked to 4e-3), the rest in fp32
+        grads=dict((k, p.grad.to(torch.bfloat16) if p.numel() > 100_000 else p.grad.clone())
+                   for k, p in model.named_parameters()),
+    )
+    torch.save(fx, os.path.join(HERE, "gamerft_core.pt"))
+    print(f"gamerft_core: y absmax {y.abs().max():.3f}  flex-vs-dense fwd diff {sub_diff:.2e}")
+
+
+def main():
+    G.install_stubs()
+    sys.modules["rotary_embedding_torch"].apply_rotary_emb = None   # imported by embeddings.py:9-12, never called on this path
+    import owl_wms.nn.attn as A
+    flex_real = A.flex_attention
+    if "--only-game" not in sys.argv:
+        audiorft(A, flex_real)
+    gamerft(A, flex_real)
+
+
+if __name__ == "__main__":
+    main()

@@ -88,3 +88,52 @@ def test_audiorft_core_audio_yml_shape_vs_oracle():
     loss.backward()
     assert loss.dim() == 0 and torch.isfinite(loss)
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in rft.parameters())
+
+
+def _game(cfg, state, rope, dtype=torch.float32):
+    from owl_audio_exps_b200.models import GameRFTCore
+    model = GameRFTCore(cfg)
+    model.load_state_dict({k: v.float() for k, v in state.items()}, strict=True)
+    model = model.to(DEV).to(dtype)
+    for blk, (cos, sin) in zip(model.transformer.blocks, rope):
+        blk.attn.rope.cos = cos.to(DEV).float().contiguous()
+        blk.attn.rope.sin = sin.to(DEV).float().contiguous()
+    return model
+
+
+@pytest.mark.parametrize("regime", ["fp32_params", "bf16_params"])
+def test_gamerft_core_golden(regime):
+    """GameRFTCore (gamerft.py:13-60): ControlEmbedding with its narrow inputs (2 angle features, 11 buttons: K padded to 8s),
+    has_controls masking, patchify / unpatchify, against the reference model's fixture."""
+    fx = load_golden("gamerft_core")
+    cfg = cfg_of(fx)
+    model = _game(cfg, fx["state"], fx["rope"], torch.float32 if regime == "fp32_params" else torch.bfloat16)
+    mouse, btn, t = fx["mouse"].to(DEV), fx["btn"].to(DEV), fx["t"].to(DEV)
+    assert relerr(model.control_embed(mouse, btn), fx["ctrl"]) <= TOL
+    x = fx["x"].to(DEV).float().requires_grad_(True)
+    y = model(x, t, mouse, btn, None, fx["has_controls"].to(DEV))
+    assert y.shape == fx["y"].shape
+    assert relerr(y, fx["y"]) <= TOL
+    y.backward(fx["dy"].to(DEV).to(y.dtype))
+    assert relerr(x.grad, fx["dx"]) <= TOL
+    worst = max((relerr(p.grad, fx["grads"][k]), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+    assert all(p.grad.shape == p.shape for p in model.parameters())
+
+
+def test_gamerft_training_wrapper():
+    """gamerft.py:63-125: CFG control dropout + noise + MSE; gradients reach every parameter."""
+    from owl_audio_exps_b200.models import GameRFT
+    fx = load_golden("gamerft_core")
+    cfg = cfg_of(fx)
+    cfg.cfg_prob = 0.5
+    torch.manual_seed(3)
+    rft = GameRFT(cfg).to(DEV)
+    B, n = 4, 6
+    x = torch.randn(B, n, cfg.channels, cfg.sample_size, cfg.sample_size, device=DEV)
+    out = rft(x, torch.randn(B, n, 2, device=DEV), (torch.rand(B, n, cfg.n_buttons, device=DEV) < 0.3).float(),
+              return_dict=True)
+    out["diffusion_loss"].backward()
+    assert torch.isfinite(out["diffusion_loss"]) and out["pred_video"].shape == x.shape
+    assert out["cfg_mask"].dtype == torch.bool and out["cfg_mask"].shape == (B,)
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in rft.parameters())

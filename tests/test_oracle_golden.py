@@ -104,3 +104,19 @@ def test_audiorft_core_matches_reference():
     assert relerr(x.grad, fx["dx"]) < TOL
     for k, g in fx["grads"].items():
         assert relerr(W[k].grad, g) < 5 * TOL, k
+
+
+def test_gamerft_core_matches_reference():
+    """Mouse/Button/ControlEmbedding, patchify and GameRFTCore of the oracle vs the reference model's own outputs."""
+    fx = load_golden("gamerft_core")
+    cfg = cfg_of(fx)
+    assert fx["flex_vs_dense_fwd_maxabs"] < 5e-6
+    W = {k: v.requires_grad_(True) for k, v in _weights(fx).items()}
+    assert relerr(O.control_embedding(fx["mouse"], fx["btn"], W, "control_embed."), fx["ctrl"]) < TOL
+    x = fx["x"].float().requires_grad_(True)
+    y = O.game_rft_core(x, fx["t"], fx["mouse"], fx["btn"], W, cfg, fx["rope"], has_controls=fx["has_controls"])
+    assert relerr(y, fx["y"]) < TOL
+    (y * fx["dy"].float()).sum().backward()
+    assert relerr(x.grad, fx["dx"]) < TOL
+    for k, g in fx["grads"].items():
+        assert relerr(W[k].grad, g) < (5 * TOL if g.dtype == torch.float32 else 4e-3), k
