@@ -218,12 +218,42 @@ def timestep_embedding(t: Tensor, W: Dict[str, Tensor], prefix: str) -> Tensor:
 
 
 def audio_rft_core(x: Tensor, t: Tensor, W: Dict[str, Tensor], cfg, rope_tables: List[Tuple[Tensor, Tensor]],
-                   doc_id: Optional[Tensor] = None) -> Tensor:
+                   doc_id: Optional[Tensor] = None, kv_cache: Optional[OracleKVCache] = None,
+                   decoding: bool = False) -> Tensor:
     """models/audiorft.py:34-57 (AudioRFTCore.forward): t_embed -> proj_in -> DiT -> FinalLayer."""
     cond = timestep_embedding(t, W, "t_embed.")
     h = _lin(x, W, "proj_in")
-    h = dit_forward(h, cond, W, cfg, rope_tables, doc_id=doc_id, prefix="transformer.")
+    h = dit_forward(h, cond, W, cfg, rope_tables, doc_id=doc_id, kv_cache=kv_cache, decoding=decoding,
+                    prefix="transformer.")
     return final_layer(h, cond, W, "proj_out.")
+
+
+def audio_cached_rollout(x: Tensor, W: Dict[str, Tensor], cfg, rope_tables: List[Tuple[Tensor, Tensor]], dt: List[float],
+                         num_tokens: int, noise_prev: float, max_window: Optional[int], noise) -> Tensor:
+    """sampling/audio_caching.py:55-151 (AudioCachingSampler.__call__): `noise(shape)` supplies every N(0,1) draw in
+    the reference's order (context re-noise, then per token: start latent, committed-latent re-noise)."""
+    b, _, ch = x.shape
+    cache = OracleKVCache(cfg.n_layers, cfg.tokens_per_frame)
+    latents = [x.clone()]
+
+    def commit(tok):
+        noisy = tok * (1.0 - noise_prev) + noise(tuple(tok.shape)) * noise_prev
+        cache.should_update = True
+        audio_rft_core(noisy, torch.full((b, tok.shape[1]), noise_prev), W, cfg, rope_tables, kv_cache=cache,
+                       decoding=len(latents) > 1)
+        cache.should_update = False
+
+    commit(x)
+    for _ in range(num_tokens):
+        cur, t = noise((b, 1, ch)), torch.ones(b, 1)
+        for d in dt:
+            cur = cur - d * audio_rft_core(cur, t, W, cfg, rope_tables, kv_cache=cache, decoding=True)
+            t = t - d
+        latents.append(cur)
+        commit(cur)
+        if max_window is not None and len(latents) > max_window:
+            cache.truncate(1, front=False)
+    return torch.cat(latents, dim=1)
 
 
 def mouse_embedding(m: Tensor, W: Dict[str, Tensor], prefix: str, dim: int = 512) -> Tensor:

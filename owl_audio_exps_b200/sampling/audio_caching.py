@@ -1,0 +1,77 @@
+"""Drop-in for owl_wms/sampling/audio_caching.py:22-160: one audio latent at a time through the KV-cached decode path.
+
+Prefill the noised context with cache updates on, then for every new latent run `n_steps` Euler steps against the cache
+(decode mode: no mask), re-noise the result to `noise_prev`, append it to the cache and drop the oldest latent once the
+window is full.  Differences from the reference loop: dt lives on the host (no per-step device read), there is no
+per-token `empty_cache()`, and the noise source is injectable (`noise_fn`) so a rollout is reproducible across devices."""
+import torch
+
+from ..nn.kv_cache import KVCache
+from .schedulers import get_sd3_euler
+
+
+def get_deltas(custom_schedule):
+    """audio_caching.py:9-19: |difference| of consecutive schedule points, a final 0.0 appended when missing."""
+    pts = list(custom_schedule)
+    if pts[-1] != 0.0:
+        pts.append(0.0)
+    return [abs(b - a) for a, b in zip(pts[:-1], pts[1:])]
+
+
+class AudioCachingSampler:
+    def __init__(self, n_steps: int = 16, num_tokens: int = 120, noise_prev: float = 0.2, custom_schedule=None,
+                 max_window=None, noise_fn=None) -> None:
+        self.n_steps = n_steps
+        self.num_tokens = num_tokens
+        self.noise_prev = noise_prev
+        self.custom_schedule = custom_schedule
+        self.max_window = max_window
+        self.noise_fn = noise_fn        # (shape, like) -> N(0,1) tensor; default torch.randn on like's device / dtype
+
+    def _randn(self, shape, like):
+        if self.noise_fn is not None:
+            return self.noise_fn(tuple(shape), like)
+        return torch.randn(*shape, device=like.device, dtype=like.dtype)
+
+    def zlerp(self, x, alpha):
+        return x * (1.0 - alpha) + self._randn(x.shape, x) * alpha
+
+    @torch.no_grad()
+    def __call__(self, model, x, decode_fn=None, vae_scale=1.0, compile_on_decode=False):
+        """model: AudioRFTCore; x [b, init_len, channels] -> [b, init_len + num_tokens, channels] (and waveforms when
+        decode_fn is given).  `compile_on_decode` is accepted and ignored: the decode step already is hand-written kernels."""
+        b, _, channels = x.shape
+        if self.custom_schedule is None:
+            dt = get_sd3_euler(self.n_steps).tolist()
+        else:
+            dt = get_deltas(self.custom_schedule)
+        cache = KVCache(model.config)
+        cache.reset(b)
+        latents = [x.clone()]
+
+        def commit(tokens):     # noise to `noise_prev`, run once with cache updates on
+            t = tokens.new_full((b, tokens.size(1)), self.noise_prev)
+            cache.enable_cache_updates()
+            model(self.zlerp(tokens, self.noise_prev), t, doc_id=None, kv_cache=cache)
+            cache.disable_cache_updates()
+
+        commit(x)
+        model.transformer.enable_decoding()
+        try:
+            for _ in range(self.num_tokens):
+                cur = self._randn((b, 1, channels), x)
+                t = x.new_ones(b, 1)
+                for step in range(self.n_steps):
+                    v = model(cur, t, doc_id=None, kv_cache=cache)
+                    cur = cur - dt[step] * v.to(cur.dtype)
+                    t = t - dt[step]
+                latents.append(cur)
+                commit(cur)
+                if self.max_window is not None and len(latents) > self.max_window:
+                    cache.truncate(1, front=False)
+        finally:
+            model.transformer.disable_decoding()
+        full = torch.cat(latents, dim=1)
+        if decode_fn is not None:
+            return full, decode_fn(full * vae_scale)
+        return full

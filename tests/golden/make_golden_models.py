@@ -91,14 +91,55 @@ def gamerft(A, flex_real):
     print(f"gamerft_core: y absmax {y.abs().max():.3f}  flex-vs-dense fwd diff {sub_diff:.2e}")
 
 
+def audio_rollout(A):
+    """The reference's own AudioCachingSampler (sampling/audio_caching.py) on the reference AudioRFTCore carrying the
+    audiorft_core.pt weights: real CPU flex forward, every torch.randn / randn_like draw served from a recorded queue,
+    a custom schedule (the default one needs diffusers), the KV cache moved to CPU fp32."""
+    from owl_wms.models.audiorft import AudioRFTCore
+    import owl_wms.nn.kv_cache as K
+    import owl_wms.sampling.audio_caching as S
+    core = torch.load(os.path.join(HERE, "audiorft_core.pt"), weights_only=False)
+    cfg = G.make_cfg(**core["cfg"])
+    model = AudioRFTCore(cfg).eval()
+    model.load_state_dict({k: v.float() for k, v in core["state"].items()})
+    S.KVCache = lambda config: K.KVCache(config).to("cpu", torch.float32)
+    g = torch.Generator().manual_seed(2468)
+    B, init_len, num_tokens, schedule = 2, 6, 4, [1.0, 0.75, 0.4]
+    x = G.bf16r(torch.randn(B, init_len, cfg.channels, generator=g))
+    draws = []
+
+    def draw(shape):
+        z = torch.randn(*shape, generator=g)
+        draws.append(z)
+        return z
+    real_randn, real_like = torch.randn, torch.randn_like
+    torch.randn_like = lambda t, **kw: draw(tuple(t.shape))
+    torch.randn = lambda *shape, generator=None, **kw: real_randn(*shape, generator=generator) if generator is not None \
+        else draw(tuple(shape[0]) if isinstance(shape[0], (tuple, list)) else shape)
+    try:
+        sampler = S.AudioCachingSampler(n_steps=len(schedule), num_tokens=num_tokens, noise_prev=0.2,
+                                        custom_schedule=list(schedule), max_window=4)
+        out = sampler(model, x)
+    finally:
+        torch.randn, torch.randn_like = real_randn, real_like
+    fx = dict(name="audio_rollout", weights_from="audiorft_core", x=x, schedule=schedule, num_tokens=num_tokens,
+              noise_prev=0.2, max_window=4, draws=draws, out=out)
+    torch.save(fx, os.path.join(HERE, "audio_rollout.pt"))
+    print(f"audio_rollout: {len(draws)} noise draws, out {tuple(out.shape)} absmax {out.abs().max():.3f}")
+
+
 def main():
     G.install_stubs()
     sys.modules["rotary_embedding_torch"].apply_rotary_emb = None   # imported by embeddings.py:9-12, never called on this path
     import owl_wms.nn.attn as A
     flex_real = A.flex_attention
+    if "--only-rollout" in sys.argv:
+        return audio_rollout(A)
     if "--only-game" not in sys.argv:
         audiorft(A, flex_real)
     gamerft(A, flex_real)
+    A.flex_attention = flex_real
+    audio_rollout(A)
 
 
 if __name__ == "__main__":

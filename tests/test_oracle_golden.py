@@ -120,3 +120,24 @@ def test_gamerft_core_matches_reference():
     assert relerr(x.grad, fx["dx"]) < TOL
     for k, g in fx["grads"].items():
         assert relerr(W[k].grad, g) < (5 * TOL if g.dtype == torch.float32 else 4e-3), k
+
+
+def test_audio_cached_rollout_matches_reference_sampler():
+    """Oracle rollout vs the reference's own AudioCachingSampler run (tests/golden/make_golden_models.py audio_rollout)."""
+    fx = load_golden("audio_rollout")
+    core = load_golden(fx["weights_from"])
+    cfg = cfg_of(core)
+    W = _weights(core)
+    draws = iter(fx["draws"])
+
+    def noise(shape):
+        z = next(draws)
+        assert tuple(z.shape) == tuple(shape)
+        return z
+    sched = list(fx["schedule"]) + [0.0]
+    dt = [abs(b - a) for a, b in zip(sched[:-1], sched[1:])]
+    with torch.no_grad():
+        out = O.audio_cached_rollout(fx["x"], W, cfg, core["rope"], dt, fx["num_tokens"], fx["noise_prev"],
+                                     fx["max_window"], noise)
+    assert next(draws, None) is None
+    assert relerr(out, fx["out"]) < 5 * TOL
