@@ -19,6 +19,7 @@ regime, causvid_pipeline.py:36); activations on the path are always bf16.
 from __future__ import annotations
 
 from dataclasses import dataclass
+import contextlib
 from typing import Optional
 
 import torch
@@ -79,6 +80,21 @@ def _capturing() -> bool:
     return torch.cuda.is_current_stream_capturing()
 
 
+_FROZEN = False
+
+
+@contextlib.contextmanager
+def frozen_weights():
+    """Inside this context a CUDA-graph capture may reuse operands staged before it (inference: the parameters do not
+    change between replays), instead of recording the fp32 -> bf16 casts into the graph."""
+    global _FROZEN
+    prev, _FROZEN = _FROZEN, True
+    try:
+        yield
+    finally:
+        _FROZEN = prev
+
+
 class WeightStage:
     """bf16 operand copies of a module's parameters, re-staged when a parameter's version changes.
 
@@ -102,7 +118,7 @@ class WeightStage:
         for key, params in items:
             vers = tuple((p.data_ptr(), p._version, p.dtype) for p in params)
             hit = self._slots.get(key)
-            if hit is not None and hit[0] == vers and not _capturing():
+            if hit is not None and hit[0] == vers and (_FROZEN or not _capturing()):
                 outs.append(hit[1])
                 continue
             p0 = params[0]

@@ -58,6 +58,14 @@ class SingleKVCache:
         self._reserve = int(n_tokens)
         return self
 
+    def make_room(self, n_new: int):
+        """Do now any compaction / growth the next `n_new`-row call would trigger, so that call finds its rows in place
+        (a CUDA-graph capture of the decode step must not record buffer management).  Extension, not in the reference."""
+        self._check()
+        for i in range(self.config.n_layers):
+            self._ensure_room(i, n_new)
+        return self
+
     @property
     def _head_dim(self):
         return self.config.d_model // self.config.n_heads

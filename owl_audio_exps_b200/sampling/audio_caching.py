@@ -3,9 +3,13 @@
 Prefill the noised context with cache updates on, then for every new latent run `n_steps` Euler steps against the cache
 (decode mode: no mask), re-noise the result to `noise_prev`, append it to the cache and drop the oldest latent once the
 window is full.  Differences from the reference loop: dt lives on the host (no per-step device read), there is no
-per-token `empty_cache()`, and the noise source is injectable (`noise_fn`) so a rollout is reproducible across devices."""
+per-token `empty_cache()`, the noise source is injectable (`noise_fn`) so a rollout is reproducible across devices, and
+the Euler steps of one latent replay a CUDA graph: within a latent the cache, its length and the RoPE offset are fixed, so
+step 0 runs eagerly (and stages the weights), the same call is captured once and steps 1..n-1 are replays (B=1 decode is
+launch-bound: ~200 kernels per call)."""
 import torch
 
+from .. import functional as OF
 from ..nn.kv_cache import KVCache
 from .schedulers import get_sd3_euler
 
@@ -20,13 +24,43 @@ def get_deltas(custom_schedule):
 
 class AudioCachingSampler:
     def __init__(self, n_steps: int = 16, num_tokens: int = 120, noise_prev: float = 0.2, custom_schedule=None,
-                 max_window=None, noise_fn=None) -> None:
+                 max_window=None, noise_fn=None, graph_decode: bool = True) -> None:
         self.n_steps = n_steps
         self.num_tokens = num_tokens
         self.noise_prev = noise_prev
         self.custom_schedule = custom_schedule
         self.max_window = max_window
         self.noise_fn = noise_fn        # (shape, like) -> N(0,1) tensor; default torch.randn on like's device / dtype
+        self.graph_decode = graph_decode
+        self._pool = None
+
+    def _denoise(self, model, cache, cur, t, dt):
+        """n_steps Euler steps of one latent against a fixed cache: cur <- cur - dt*v(cur, t), t <- t - dt."""
+        n = self.n_steps
+        if not (self.graph_decode and cur.is_cuda and n >= 3):
+            for step in range(n):
+                v = model(cur, t, doc_id=None, kv_cache=cache)
+                cur = cur - dt[step] * v.to(cur.dtype)
+                t = t - dt[step]
+            return cur
+        cache.make_room(cur.size(1))                      # buffer management happens here, not inside the capture
+        cur, t = cur.clone(), t.clone()                   # the graph's input buffers
+        def euler(step, v):                               # same arithmetic as the eager loop, written into the graph's inputs
+            cur.copy_(cur - dt[step] * v.to(cur.dtype))
+            t.copy_(t - dt[step])
+
+        euler(0, model(cur, t, doc_id=None, kv_cache=cache))   # step 0, eager
+        graph = torch.cuda.CUDAGraph()
+        if self._pool is None:
+            self._pool = torch.cuda.graph_pool_handle()
+        with OF.frozen_weights(), torch.cuda.graph(graph, pool=self._pool):
+            v = model(cur, t, doc_id=None, kv_cache=cache)
+        for step in range(1, n):
+            graph.replay()
+            euler(step, v)
+        out = cur.clone()
+        del graph, v
+        return out
 
     def _randn(self, shape, like):
         if self.noise_fn is not None:
@@ -61,10 +95,7 @@ class AudioCachingSampler:
             for _ in range(self.num_tokens):
                 cur = self._randn((b, 1, channels), x)
                 t = x.new_ones(b, 1)
-                for step in range(self.n_steps):
-                    v = model(cur, t, doc_id=None, kv_cache=cache)
-                    cur = cur - dt[step] * v.to(cur.dtype)
-                    t = t - dt[step]
+                cur = self._denoise(model, cache, cur, t, dt)
                 latents.append(cur)
                 commit(cur)
                 if self.max_window is not None and len(latents) > self.max_window:

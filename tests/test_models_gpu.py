@@ -163,3 +163,18 @@ def test_audio_caching_sampler_matches_reference_rollout():
     # default schedule + default noise source run end to end
     out = AudioCachingSampler(n_steps=2, num_tokens=2)(model, fx["x"].to(DEV))
     assert out.shape == (2, 8, 64) and torch.isfinite(out).all()
+
+
+def test_sampler_graph_replay_equals_eager_steps():
+    """The per-latent CUDA graph of the decode step launches the same kernels as the eager loop: identical latents."""
+    from owl_audio_exps_b200.sampling import AudioCachingSampler
+    core = load_golden("audiorft_core")
+    model = _core(cfg_of(core), core["state"], core["rope"]).eval()
+    x = torch.randn(2, 5, 64, device=DEV)
+    outs = []
+    for graph in (False, True):
+        g = torch.Generator(device=DEV).manual_seed(11)
+        noise_fn = lambda shape, like: torch.randn(*shape, device=like.device, dtype=like.dtype, generator=g)  # noqa: E731
+        outs.append(AudioCachingSampler(n_steps=5, num_tokens=4, max_window=6, noise_fn=noise_fn,
+                                        graph_decode=graph)(model, x))
+    assert torch.equal(outs[0], outs[1])
