@@ -2,17 +2,17 @@
 
 Layout: csrc/ (CUDA kernels + C ABI, built into libowl_dit.so), _lib.py (ctypes binding), ops.py
 (tensor-level wrappers), functional.py (autograd schedule of the block), nn/ (drop-in mirror of
-owl_wms/nn), engine.py (data-parallel step: flat gradient buckets, overlapped NCCL all-reduce, CUDA graphs).
+owl_wms/nn), models/ + sampling/ (the callers either side of the stack: AudioRFT, GameRFT, AudioCachingSampler), engine.py (data-parallel step: flat gradient buckets, overlapped NCCL all-reduce, CUDA graphs).
 """
 import sys
 
 __version__ = "0.1.0"
 
-_NN_MODULES = ("attn", "kv_cache", "mlp", "modulation", "normalization", "rope")
+_NN_MODULES = ("attn", "embeddings", "kv_cache", "mlp", "modulation", "normalization", "rope")
 
 
 def install(package: str = "owl_wms"):
-    """Make `<package>.nn.{attn,kv_cache,mlp,modulation,normalization,rope}` resolve to this
+    """Make `<package>.nn.{attn,embeddings,kv_cache,mlp,modulation,normalization,rope}` resolve to this
     implementation, so the reference's models / samplers / trainers / inference pipeline (which do
     `from ..nn.attn import DiT, FinalLayer`, `from ..nn.kv_cache import KVCache`, ...) pick up the
     sm_100a path without any edit.  Call before importing `<package>.models`.  See INTEGRATION.md."""
