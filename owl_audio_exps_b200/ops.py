@@ -23,7 +23,15 @@ def _p(t: Optional[torch.Tensor]):
     return None if t is None else t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_raw_device = getattr(torch._C, "_cuda_getDevice", None)
+
+
 def _stream():
+    """cudaStream_t of torch's current stream.  The raw accessors skip building a torch.cuda.Stream object per launch
+    (a quarter of the host time of a launch-bound decode step)."""
+    if _raw_stream is not None and _raw_device is not None:
+        return _raw_stream(_raw_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -43,6 +51,23 @@ def _rows(t: torch.Tensor):
     if t.dim() > 2:
         t = t.reshape(-1, t.shape[-1]) if t.is_contiguous() else t.flatten(0, -2)
     return t.shape[0], t.shape[1], t.stride(0)
+
+
+def _ld(t: torch.Tensor) -> int:
+    """Leading dimension of a 2-D operand (fast path of _rows)."""
+    if t.dim() == 2 and t.stride(1) == 1:
+        return t.stride(0)
+    return _rows(t)[2]
+
+
+_GEMM_FN = None
+
+
+def _gemm_fn():
+    global _GEMM_FN
+    if _GEMM_FN is None:
+        _GEMM_FN = _lib.load().owl_gemm_bf16
+    return _GEMM_FN
 
 
 # in-graph timeline probe (tools/step_trace.py): TRACE = (uint64 device buffer, [labels]) or None
@@ -117,22 +142,31 @@ def gemm(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, 
          aux0: Optional[torch.Tensor] = None, aux1: Optional[torch.Tensor] = None, rows_per_frame: int = 1,
          accumulate: bool = False) -> None:
     """C[M,N] = opA . opB with a fused epilogue; a/b are 2-D bf16 (row stride = leading dimension)."""
-    lib = _lib.load()
     _req(a), _req(b)
     e = GemmEpilogue()
     e.mode, e.accumulate, e.rows_per_frame = mode, int(accumulate), rows_per_frame
     if bias is not None:
         _req(bias, torch.float32)
         e.bias = bias.data_ptr()
-    for name, ldname, t, dt in (("out0", "ld0", out0, bf16), ("out1", "ld1", out1, bf16),
-                                ("outf", "ldf", outf, torch.float32), ("aux0", "lda0", aux0, bf16),
-                                ("aux1", "lda1", aux1, bf16)):
-        if t is not None:
-            _req(t, dt)
-            setattr(e, name, t.data_ptr())
-            setattr(e, ldname, _rows(t)[2])
-    rc = lib.owl_gemm_bf16(layout, M, N, K, a.data_ptr(), _rows(a)[2], b.data_ptr(), _rows(b)[2], C.byref(e), _stream())
-    _lib.check(rc, "owl_gemm_bf16")
+    # spelled out (no loop / setattr): this wrapper runs ~70 times per decode call, where host time is the bound
+    if out0 is not None:
+        _req(out0)
+        e.out0, e.ld0 = out0.data_ptr(), _ld(out0)
+    if out1 is not None:
+        _req(out1)
+        e.out1, e.ld1 = out1.data_ptr(), _ld(out1)
+    if outf is not None:
+        _req(outf, torch.float32)
+        e.outf, e.ldf = outf.data_ptr(), _ld(outf)
+    if aux0 is not None:
+        _req(aux0)
+        e.aux0, e.lda0 = aux0.data_ptr(), _ld(aux0)
+    if aux1 is not None:
+        _req(aux1)
+        e.aux1, e.lda1 = aux1.data_ptr(), _ld(aux1)
+    rc = _gemm_fn()(layout, M, N, K, a.data_ptr(), _ld(a), b.data_ptr(), _ld(b), C.byref(e), _stream())
+    if rc != 0:
+        _lib.check(rc, "owl_gemm_bf16")
 
 
 def gemm_check(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int) -> torch.Tensor:
