@@ -41,6 +41,15 @@ def train():
 ms = timed(train, 10)
 print(f"AudioRFT train step eager B=32 L=120: {ms:.2f} ms  ({32 * 120 / ms * 1e3:.0f} tokens/s)")
 
+from owl_audio_exps_b200 import engine
+buckets = engine.GradBuckets(rft)
+step = engine.TrainStep(rft, lambda m, x: m(x), [x], buckets=buckets, use_graph=True, warmup=3)
+ms = timed(lambda: step(x), 20)
+print(f"AudioRFT train step CUDA graph (engine.TrainStep, noise + loss inside) B=32 L=120: {ms:.2f} ms  "
+      f"({32 * 120 / ms * 1e3:.0f} tokens/s), {step.launches_per_step} launches")
+buckets.detach()
+del step
+
 core = rft.core.eval()
 calls = [0]
 fwd = core.forward
