@@ -287,6 +287,22 @@ def game_rft_core(x: Tensor, t: Tensor, mouse: Tensor, btn: Tensor, W: Dict[str,
     return tok.view(b, n, h, w, c).permute(0, 1, 4, 2, 3)
 
 
+def game_rft_audio_core(x: Tensor, audio: Tensor, t: Tensor, W: Dict[str, Tensor], cfg,
+                        rope_tables: List[Tuple[Tensor, Tensor]]) -> Tuple[Tensor, Tensor]:
+    """models/gamerft_audio.py:47-98 (GameRFTAudioCore.forward, `dit` backbone, uncond): per frame h*w video tokens then
+    the audio token; video head sees layer_norm(video), layer_norm(cond).  Keys are spelled `transformer.*` as in the
+    fixture (made with dynamo disabled; a compiled reference checkpoint spells them `transformer._orig_mod.*`)."""
+    b, n, c, h, w = x.shape
+    cond = timestep_embedding(t, W, "t_embed.")
+    vid = _lin(x.permute(0, 1, 3, 4, 2).reshape(b, n * h * w, c), W, "proj_in")
+    aud = _lin(audio, W, "audio_proj_in")
+    d = vid.shape[-1]
+    tok = torch.cat([vid.view(b, n, h * w, d), aud.view(b, n, 1, d)], dim=2).reshape(b, n * (h * w + 1), d)
+    tok = dit_forward(tok, cond, W, cfg, rope_tables, prefix="transformer.").view(b, n, h * w + 1, d)
+    vid = final_layer(layer_norm(tok[:, :, :-1].reshape(b, n * h * w, d)), layer_norm(cond), W, "proj_out.")
+    return vid.reshape(b, n, h, w, c).permute(0, 1, 4, 2, 3), final_layer(tok[:, :, -1], cond, W, "audio_proj_out.")
+
+
 # ---------------------------------------------------------------------------------------------
 # algorithmic work (SURVEY.md section 8d / BASELINE.md section 3) -- used by bench.py for the roofline basis
 # ---------------------------------------------------------------------------------------------

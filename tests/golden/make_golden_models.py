@@ -91,6 +91,53 @@ def gamerft(A, flex_real):
     print(f"gamerft_core: y absmax {y.abs().max():.3f}  flex-vs-dense fwd diff {sub_diff:.2e}")
 
 
+def gamerft_audio(A, flex_real):
+    """GameRFTAudioCore (video patches + one audio token per frame, T = h*w + 1).  The reference wraps its backbone in
+    torch.compile(dynamic=True); with TORCHDYNAMO_DISABLE=1 that wrapper runs the module eagerly, and its state-dict keys
+    keep the `transformer._orig_mod.` spelling."""
+    import types
+    mm = types.ModuleType("owl_wms.nn.mmattn")   # the reference's mmattn.py:12 imports a name attn.py no longer has, so
+    mm.MMDIT = object                            # gamerft_audio.py cannot be imported as shipped; only its `dit` branch
+    sys.modules["owl_wms.nn.mmattn"] = mm        # is exercised here and that branch never touches MMDIT
+    from owl_wms.models.gamerft_audio import GameRFTAudioCore
+    cfg = G.make_cfg(d_model=128, n_heads=2, n_layers=2, tokens_per_frame=5, n_frames=6, sample_size=2,
+                     has_audio=True, rope_impl="ortho", local_window=3, channels=16, audio_channels=8, n_buttons=11,
+                     uncond=True)
+    torch.manual_seed(987)
+    model = GameRFTAudioCore(cfg)
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() == 1:
+                p.copy_(0.1 * torch.randn_like(p))
+            p.copy_(G.bf16r(p))
+    B, n, c, h = 2, 6, cfg.channels, cfg.sample_size
+    g = torch.Generator().manual_seed(1357)
+    x = G.bf16r(torch.randn(B, n, c, h, h, generator=g)).requires_grad_(True)
+    audio = G.bf16r(torch.randn(B, n, cfg.audio_channels, generator=g)).requires_grad_(True)
+    t = torch.randn(B, n, generator=g).sigmoid()
+    dyv = G.bf16r(torch.randn(B, n, c, h, h, generator=g))
+    dya = G.bf16r(torch.randn(B, n, cfg.audio_channels, generator=g))
+    A.flex_attention = flex_real
+    with torch.no_grad():
+        yv_flex, _ = model(x, audio, t, None, None)
+    A.flex_attention = G.dense_flex
+    yv, ya = model(x, audio, t, None, None)
+    sub_diff = (yv - yv_flex).abs().max().item()
+    ((yv * dyv).sum() + (ya * dya).sum()).backward()
+    blocks = model.transformer._orig_mod.blocks if hasattr(model.transformer, "_orig_mod") else model.transformer.blocks
+    fx = dict(
+        name="gamerft_audio_core", cfg=dict(vars(cfg)), B=B, flex_vs_dense_fwd_maxabs=sub_diff,
+        state=dict((k, v.detach().to(torch.bfloat16)) for k, v in model.state_dict().items()),
+        rope=[(blk.attn.rope.cos.clone(), blk.attn.rope.sin.clone()) for blk in blocks],
+        x=x.detach().to(torch.bfloat16), audio=audio.detach().to(torch.bfloat16), t=t, dyv=dyv.to(torch.bfloat16),
+        dya=dya.to(torch.bfloat16), yv=yv.detach(), ya=ya.detach(), dx=x.grad.clone(), daudio=audio.grad.clone(),
+        grads=dict((k, p.grad.to(torch.bfloat16) if p.numel() > 100_000 else p.grad.clone())
+                   for k, p in model.named_parameters()),
+    )
+    torch.save(fx, os.path.join(HERE, "gamerft_audio_core.pt"))
+    print(f"gamerft_audio_core: yv absmax {yv.abs().max():.3f} ya absmax {ya.abs().max():.3f}  flex-vs-dense {sub_diff:.2e}")
+
+
 def audio_rollout(A):
     """The reference's own AudioCachingSampler (sampling/audio_caching.py) on the reference AudioRFTCore carrying the
     audiorft_core.pt weights: real CPU flex forward, every torch.randn / randn_like draw served from a recorded queue,
@@ -133,11 +180,14 @@ def main():
     sys.modules["rotary_embedding_torch"].apply_rotary_emb = None   # imported by embeddings.py:9-12, never called on this path
     import owl_wms.nn.attn as A
     flex_real = A.flex_attention
+    if "--only-av" in sys.argv:
+        return gamerft_audio(A, flex_real)
     if "--only-rollout" in sys.argv:
         return audio_rollout(A)
     if "--only-game" not in sys.argv:
         audiorft(A, flex_real)
     gamerft(A, flex_real)
+    gamerft_audio(A, flex_real)
     A.flex_attention = flex_real
     audio_rollout(A)
 

@@ -178,3 +178,37 @@ def test_sampler_graph_replay_equals_eager_steps():
         outs.append(AudioCachingSampler(n_steps=5, num_tokens=4, max_window=6, noise_fn=noise_fn,
                                         graph_decode=graph)(model, x))
     assert torch.equal(outs[0], outs[1])
+
+
+def test_gamerft_audio_core_golden():
+    """GameRFTAudioCore (gamerft_audio.py:19-98) vs the reference model's fixture; state_dict() spells the backbone keys
+    `transformer._orig_mod.*` like a compiled reference checkpoint, and both spellings load."""
+    from owl_audio_exps_b200.models import GameRFTAudio, GameRFTAudioCore
+    fx = load_golden("gamerft_audio_core")
+    cfg = cfg_of(fx)
+    model = GameRFTAudioCore(cfg)
+    model.load_state_dict({k: v.float() for k, v in fx["state"].items()}, strict=True)   # fixture: dynamo off, plain keys
+    assert list(model.state_dict().keys()) == [k.replace("transformer.", "transformer._orig_mod.") for k in fx["state"]]
+    model.load_state_dict(model.state_dict(), strict=True)                             # compiled-checkpoint spelling
+    model = model.to(DEV)
+    for blk, (cos, sin) in zip(model.transformer.blocks, fx["rope"]):
+        blk.attn.rope.cos = cos.to(DEV).float().contiguous()
+        blk.attn.rope.sin = sin.to(DEV).float().contiguous()
+    x = fx["x"].to(DEV).float().requires_grad_(True)
+    audio = fx["audio"].to(DEV).float().requires_grad_(True)
+    yv, ya = model(x, audio, fx["t"].to(DEV), None, None)
+    assert relerr(yv, fx["yv"]) <= TOL and relerr(ya, fx["ya"]) <= TOL
+    torch.autograd.backward([yv, ya], [fx["dyv"].to(DEV).to(yv.dtype), fx["dya"].to(DEV).to(ya.dtype)])
+    assert relerr(x.grad, fx["dx"]) <= TOL and relerr(audio.grad, fx["daudio"]) <= TOL
+    named = dict(model.named_parameters())
+    worst = max((relerr(named[k].grad, g), k) for k, g in fx["grads"].items())
+    assert worst[0] <= TOL, worst
+    # training wrapper: three losses, finite gradients everywhere
+    cfg.cfg_prob = 0.0
+    rft = GameRFTAudio(cfg).to(DEV)
+    B, n = 2, 6
+    loss, lv, la = rft(torch.randn(B, n, cfg.channels, 2, 2, device=DEV), torch.randn(B, n, cfg.audio_channels, device=DEV),
+                       None, None)
+    loss.backward()
+    assert torch.isfinite(loss) and torch.allclose(loss, lv + la)
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in rft.parameters())

@@ -141,3 +141,19 @@ def test_audio_cached_rollout_matches_reference_sampler():
                                      fx["max_window"], noise)
     assert next(draws, None) is None
     assert relerr(out, fx["out"]) < 5 * TOL
+
+
+def test_gamerft_audio_core_matches_reference():
+    """Video + audio token interleave, layer_norm'd video head and the audio head of the oracle vs the reference model."""
+    fx = load_golden("gamerft_audio_core")
+    cfg = cfg_of(fx)
+    assert fx["flex_vs_dense_fwd_maxabs"] < 5e-6
+    W = {k: v.requires_grad_(True) for k, v in _weights(fx).items()}
+    x = fx["x"].float().requires_grad_(True)
+    audio = fx["audio"].float().requires_grad_(True)
+    yv, ya = O.game_rft_audio_core(x, audio, fx["t"], W, cfg, fx["rope"])
+    assert relerr(yv, fx["yv"]) < TOL and relerr(ya, fx["ya"]) < TOL
+    ((yv * fx["dyv"].float()).sum() + (ya * fx["dya"].float()).sum()).backward()
+    assert relerr(x.grad, fx["dx"]) < TOL and relerr(audio.grad, fx["daudio"]) < TOL
+    for k, g in fx["grads"].items():
+        assert relerr(W[k].grad, g) < (5 * TOL if g.dtype == torch.float32 else 4e-3), k
