@@ -210,6 +210,9 @@ int owl_kv_append(const void* src, int64_t src_sb, int64_t src_sh, void* cache, 
 
 /* Weight-less LayerNorm over the last dim (normalization.py:6-7), bf16 [M,d].                     */
 int owl_layer_norm_fwd(const void* x, void* y, int64_t M, int64_t d, float eps, owl_stream_t stream);
+/* Its autograd: dx = rstd * (dy - mean(dy) - xhat * mean(dy * xhat)), statistics recomputed from x
+ * (gamerft_audio.py:86 puts layer_norm on the training path of the video head).                   */
+int owl_layer_norm_bwd(const void* dy, const void* x, void* dx, int64_t M, int64_t d, float eps, owl_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Attention                                                          (attn.py:24-62,102-111)

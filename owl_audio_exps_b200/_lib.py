@@ -67,6 +67,7 @@ SIGNATURES = {
     "owl_rope_apply": ([vp, vp, vp, i64, vp, i64, i64, i64, C.c_int, vp], C.c_int),
     "owl_kv_append": ([vp, i64, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp], C.c_int),
     "owl_layer_norm_fwd": ([vp, vp, i64, i64, f32, vp], C.c_int),
+    "owl_layer_norm_bwd": ([vp, vp, vp, i64, i64, f32, vp], C.c_int),
     "owl_attn_fwd": (_ATTN_FWD, C.c_int),
     "owl_attn_bwd": (_ATTN_BWD, C.c_int),
     "owl_attn_fwd_check": (_ATTN_FWD, C.c_int),

@@ -559,6 +559,62 @@ __global__ void __launch_bounds__(256) sincos_embed_kernel(const float* __restri
   }
 }
 
+// weight-less LayerNorm backward: dx = rstd * (dy - mean(dy) - xhat * mean(dy * xhat)); mean / rstd are recomputed from x
+// (one more pass over registers, no saved statistics).
+template <int NV>
+__global__ void __launch_bounds__(kRowThreads)
+layer_norm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, bf16* __restrict__ dx, int64_t M, int d, float eps) {
+  pdl_prologue();
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  const float inv_d = 1.f / static_cast<float>(d);
+  for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
+    uint4 xv[NV], gv[NV];
+    float s = 0.f, sg = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        xv[i] = ldg16(x + row * d + c);
+        gv[i] = ldg16(dy + row * d + c);
+        float f[8], g[8];
+        unpack8(xv[i], f);
+        unpack8(gv[i], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s += f[j]; sg += g[j]; }
+      }
+    }
+    const float mean = warp_sum(s) * inv_d;
+    const float gmean = warp_sum(sg) * inv_d;
+    float v = 0.f, gx = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        float f[8], g[8];
+        unpack8(xv[i], f);
+        unpack8(gv[i], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { v += (f[j] - mean) * (f[j] - mean); gx += g[j] * (f[j] - mean); }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(v) * inv_d + eps);
+    const float proj = warp_sum(gx) * inv_d * rstd * rstd;   // mean(dy * xhat) * rstd, applied to (x - mean)
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        float f[8], g[8], o[8];
+        unpack8(xv[i], f);
+        unpack8(gv[i], g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (g[j] - gmean - (f[j] - mean) * proj);
+        stg16(dx + row * d + c, pack8(o));
+      }
+    }
+  }
+}
+
 static inline int row_grid(int64_t M) {
   int64_t blocks = (M + (kRowThreads / 32) - 1) / (kRowThreads / 32);
   const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
@@ -754,6 +810,15 @@ int owl_layer_norm_fwd(const void* x, void* y, int64_t M, int64_t d, float eps, 
   OWL_REQUIRE(aligned16(x) && aligned16(y), OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   OWL_DISPATCH_NV(d, ((void)launch_k(layer_norm_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<bf16*>(y), M, static_cast<int>(d), eps)));
+  return launch_status();
+}
+
+int owl_layer_norm_bwd(const void* dy, const void* x, void* dx, int64_t M, int64_t d, float eps, owl_stream_t stream) {
+  OWL_REQUIRE(dy && x && dx && M > 0 && d > 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(dy) && aligned16(x) && aligned16(dx), OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  OWL_DISPATCH_NV(d, ((void)launch_k(layer_norm_bwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(dy), static_cast<const bf16*>(x), static_cast<bf16*>(dx), M, static_cast<int>(d), eps)));
   return launch_status();
 }
 

@@ -330,6 +330,27 @@ def linear(x, weight, bias, stage: WeightStage, key: str, silu_in=False, silu_ou
     return _Linear.apply(x, weight, bias, w16, b32, silu_in, silu_out)
 
 
+class _LayerNorm(torch.autograd.Function):
+    """Weight-less LayerNorm over the last dim (normalization.py:6-7) with its backward on the kernel path."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x16 = _as_bf16(x).view(-1, x.shape[-1])
+        ctx.save_for_backward(x16)
+        ctx.meta = (x.shape, x.dtype)
+        return ops.layer_norm(x16, LN_EPS).view(x.shape).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x16,) = ctx.saved_tensors
+        shp, dt = ctx.meta
+        return ops.layer_norm_bwd(_as_bf16(dy).view(-1, shp[-1]), x16, LN_EPS).view(shp).to(dt)
+
+
+def layer_norm(x):
+    return _LayerNorm.apply(x)
+
+
 class _Silu(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x):

@@ -14,11 +14,8 @@ from .. import ops
 
 
 def layer_norm(x: torch.Tensor) -> torch.Tensor:
-    """Weight-less LayerNorm over the last dim (forward only on the kernel path, as its one call site
-    runs on conditioning rows; with grad enabled it defers to autograd-capable torch math)."""
-    if x.requires_grad and torch.is_grad_enabled():
-        return torch.nn.functional.layer_norm(x, (x.size(-1),)).type_as(x)
-    return ops.layer_norm(OF._as_bf16(x), OF.LN_EPS).view(x.shape).type_as(x)
+    """Weight-less LayerNorm over the last dim (normalization.py:6-7), forward and backward on the kernel path."""
+    return OF.layer_norm(x)
 
 
 def rms_norm(x: torch.Tensor) -> torch.Tensor:

@@ -315,6 +315,15 @@ def layer_norm(x, eps: float = 1e-5):
     return y
 
 
+@_prof("layer_norm_bwd")
+def layer_norm_bwd(dy, x, eps: float = 1e-5):
+    M, d, _ = _rows(x)
+    dx = torch.empty_like(x)
+    _lib.check(_lib.load().owl_layer_norm_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), M, d, eps, _stream()),
+               "owl_layer_norm_bwd")
+    return dx
+
+
 @_prof("qk_norm_rope_fwd")
 def qk_norm_rope_fwd(qkv, cos, sin, pos_offset: int, H: int, eps: float, q, k, v, want_rstd: bool = True):
     """qkv [B,L,3*H*dh] -> q,k,v written into caller views [B,H,L,dh] (dh contiguous, L stride dh)."""

@@ -139,3 +139,22 @@ def test_kv_append():
     ops.kv_append(new, cache, 130)
     assert torch.equal(cache[:, :, 130:195], new)
     assert cache[:, :, :130].abs().max().item() == 0 and cache[:, :, 195:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("M,d", [(48, 128), (130, 1024), (1040, 1536)])
+def test_layer_norm_fwd_bwd_vs_torch(M, d):
+    """normalization.py:6-7 weight-less LayerNorm and its backward (gamerft_audio.py:86 trains through it)."""
+    import torch.nn.functional as F
+    from owl_audio_exps_b200 import functional as OF
+    torch.manual_seed(M + d)
+    x = (torch.randn(M, d, device="cuda:0") * 2 + 0.5).to(torch.bfloat16)
+    dy = torch.randn(M, d, device="cuda:0").to(torch.bfloat16)
+    xa = x.clone().requires_grad_(True)
+    y = OF.layer_norm(xa)
+    y.backward(dy)
+    xr = x.float().requires_grad_(True)
+    yr = F.layer_norm(xr, (d,))
+    yr.backward(dy.float())
+    assert y.dtype == torch.bfloat16
+    assert (y.float() - yr).abs().max() <= 2 ** -7 * yr.abs().max()
+    assert (xa.grad.float() - xr.grad).abs().max() <= 2 ** -7 * xr.grad.abs().max()
