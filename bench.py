@@ -97,6 +97,20 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port timed on the host cores (cpu_baseline, and --impl reference)
 # ------------------------------------------------------------------------------------------------
+def host_threads():
+    """All the host cores this process may use.  torchrun exports OMP_NUM_THREADS=1 to every rank, which would silently
+    make the CPU arm single-threaded at N > 1: set the count explicitly (physical cores, capped by the affinity mask)."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    try:
+        import psutil
+        phys = psutil.cpu_count(logical=False)
+        if phys:
+            n = min(n, phys)
+    except Exception:
+        pass
+    return max(n, 1)
+
+
 def cpu_port_step_time(workload, B, n_layers, steps, warmup, threads=None):
     """Seconds per fwd+bwd of the DiT stack on CPU (fp32) via oracle.dit_forward; returns (s/step, tokens/step, sample)."""
     from oracle import dit_oracle as O
@@ -146,7 +160,8 @@ def run_reference(args):
         return
     w = WORKLOADS[args.workload]
     n_layers, B = 2, 1    # bounded sample: each step stays in the seconds range on any host
-    dt, toks, sample, cores = cpu_port_step_time(args.workload, B, n_layers, max(args.steps, 1), max(args.warmup, 1))
+    dt, toks, sample, cores = cpu_port_step_time(args.workload, B, n_layers, max(args.steps, 1), max(args.warmup, 1),
+                                                 threads=host_threads())
     # per-layer cost is uniform: scale the measured layers to the full stack
     dt_full = dt * w["cfg"]["n_layers"] / n_layers
     val = toks / dt_full
@@ -306,7 +321,7 @@ def run_owl(args):
             "roofline": roofline, "clocks": clk.summary(),
         }
         if world == 1 and not args.no_cpu:
-            dt, toks, sample, cores = cpu_port_step_time(args.workload, 1, 2, 3, 1)
+            dt, toks, sample, cores = cpu_port_step_time(args.workload, 1, 2, 3, 1, threads=host_threads())
             dt_full = dt * cfg.n_layers / 2
             line["cpu_baseline"] = {"value": toks / dt_full, "unit": "tokens/s", "cores": cores, "kind": "port",
                                     "sample": sample + "; scaled to full depth"}

@@ -212,3 +212,33 @@ def test_gamerft_audio_core_golden():
     loss.backward()
     assert torch.isfinite(loss) and torch.allclose(loss, lv + la)
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in rft.parameters())
+
+
+def test_step_condition_posenc_embeddings_vs_oracle():
+    """StepEmbedding (embeddings.py:86-104), ConditionEmbedding (:106-117), LearnedPosEnc (:14-28) against the oracle's
+    sincos / mlp restatements on the same weights."""
+    import math
+    import owl_audio_exps_b200.nn as N
+    torch.manual_seed(9)
+    step = N.StepEmbedding(128, d_in=512, max_steps=128).to(DEV)
+    steps = torch.tensor([1.0, 2.0, 16.0, 128.0], device=DEV)
+    W = {k: v.detach().float().cpu() for k, v in step.state_dict().items()}
+    t = math.log2(128) - torch.log2(steps.cpu())
+    ref = O.mlp(O.sincos_embed(t, 512, theta=300, mult=1000 / math.log2(128)), W, "mlp")
+    assert relerr(step(steps), ref) <= TOL
+    assert step(4).shape == (1, 128)                                   # python scalar, as the reference accepts
+
+    cond = N.ConditionEmbedding(10, 128).to(DEV)
+    idx = torch.tensor([0, 3, 9], device=DEV)
+    W = {k: v.detach().float().cpu() for k, v in cond.state_dict().items()}
+    ref = O.mlp(W["embedding.weight"][idx.cpu()], W, "mlp")
+    out = cond(idx)
+    assert relerr(out, ref) <= TOL
+    out.float().sum().backward()
+    assert cond.embedding.weight.grad is not None and cond.mlp.fc1.weight.grad is not None
+
+    pe = N.LearnedPosEnc(8, 16).to(DEV)
+    x = torch.randn(2, 5, 16, device=DEV)
+    assert torch.equal(pe(x), x + pe.p[-5:].unsqueeze(0))              # shorter than n_seq: the LAST n rows
+    x = torch.randn(2, 8, 16, device=DEV)
+    assert torch.equal(pe(x), x + pe.p.unsqueeze(0))
