@@ -272,7 +272,8 @@ def control_embedding(mouse: Tensor, btn: Tensor, W: Dict[str, Tensor], prefix: 
 
 def game_rft_core(x: Tensor, t: Tensor, mouse: Tensor, btn: Tensor, W: Dict[str, Tensor], cfg,
                   rope_tables: List[Tuple[Tensor, Tensor]], doc_id: Optional[Tensor] = None,
-                  has_controls: Optional[Tensor] = None) -> Tensor:
+                  has_controls: Optional[Tensor] = None, kv_cache: Optional[OracleKVCache] = None,
+                  decoding: bool = False) -> Tensor:
     """models/gamerft.py:33-60 (GameRFTCore.forward)."""
     b, n, c, h, w = x.shape
     cond = timestep_embedding(t, W, "t_embed.")
@@ -282,9 +283,46 @@ def game_rft_core(x: Tensor, t: Tensor, mouse: Tensor, btn: Tensor, W: Dict[str,
             ctrl = torch.where(has_controls[:, None, None], ctrl, torch.zeros_like(ctrl))
         cond = cond + ctrl
     tok = x.permute(0, 1, 3, 4, 2).reshape(b, n * h * w, c)
-    tok = dit_forward(_lin(tok, W, "proj_in"), cond, W, cfg, rope_tables, doc_id=doc_id, prefix="transformer.")
+    tok = dit_forward(_lin(tok, W, "proj_in"), cond, W, cfg, rope_tables, doc_id=doc_id, kv_cache=kv_cache,
+                      decoding=decoding, prefix="transformer.")
     tok = final_layer(tok, cond, W, "proj_out.")
     return tok.view(b, n, h, w, c).permute(0, 1, 4, 2, 3)
+
+
+def av_cached_rollout(x: Tensor, mouse: Tensor, btn: Tensor, W: Dict[str, Tensor], cfg,
+                      rope_tables: List[Tuple[Tensor, Tensor]], dt: List[float], num_frames: int, cfg_scale: float,
+                      noise_prev: float, max_window: Optional[int], noise) -> Tensor:
+    """sampling/av_caching_v2.py:46-144 (AVCachingSamplerV2.__call__): per-frame rollout with classifier-free guidance
+    on the controls; `noise(shape)` supplies the N(0,1) draws in the reference's order."""
+    b, init_len = x.shape[0], x.shape[1]
+    cache = OracleKVCache(cfg.n_layers, cfg.tokens_per_frame)
+    latents = [x.clone()]
+
+    def run(frames, t, m, bt, decoding):
+        return game_rft_core(frames, t, m, bt, W, cfg, rope_tables, kv_cache=cache, decoding=decoding)
+
+    def commit(frames, m, bt):
+        noisy = frames * (1.0 - noise_prev) + noise(tuple(frames.shape)) * noise_prev
+        cache.should_update = True
+        run(noisy, torch.full((b, frames.shape[1]), noise_prev), m, bt, len(latents) > 1)
+        cache.should_update = False
+
+    commit(x, mouse[:, :init_len], btn[:, :init_len])
+    for idx in range(min(num_frames, mouse.shape[1] - init_len)):
+        cur, t = noise(tuple(x[:, :1].shape)), torch.ones(b, 1)
+        at = init_len + idx
+        m, bt = mouse[:, at:at + 1], btn[:, at:at + 1]
+        for d in dt:
+            v = run(cur, t, m, bt, True)
+            if cfg_scale != 1.0:
+                v0 = run(cur, t, torch.zeros_like(m), torch.zeros_like(bt), True)
+                v = v0 + cfg_scale * (v - v0)
+            cur, t = cur - d * v, t - d
+        latents.append(cur)
+        commit(cur, m, bt)
+        if max_window is not None and len(latents) > max_window:
+            cache.truncate(1, front=False)
+    return torch.cat(latents, dim=1)
 
 
 def game_rft_audio_core(x: Tensor, audio: Tensor, t: Tensor, W: Dict[str, Tensor], cfg,

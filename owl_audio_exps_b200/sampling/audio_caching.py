@@ -34,27 +34,28 @@ class AudioCachingSampler:
         self.graph_decode = graph_decode
         self._pool = None
 
-    def _denoise(self, model, cache, cur, t, dt):
-        """n_steps Euler steps of one latent against a fixed cache: cur <- cur - dt*v(cur, t), t <- t - dt."""
+    def _denoise(self, velocity, cache, new_rows, cur, t, dt):
+        """n_steps Euler steps of one latent / frame against a fixed cache: cur <- cur - dt*v(cur, t), t <- t - dt.
+        `velocity(cur, t)` is the model evaluation (two of them under classifier-free guidance)."""
         n = self.n_steps
         if not (self.graph_decode and cur.is_cuda and n >= 3):
             for step in range(n):
-                v = model(cur, t, doc_id=None, kv_cache=cache)
-                cur = cur - dt[step] * v.to(cur.dtype)
+                cur = cur - dt[step] * velocity(cur, t).to(cur.dtype)
                 t = t - dt[step]
             return cur
-        cache.make_room(cur.size(1))                      # buffer management happens here, not inside the capture
+        cache.make_room(new_rows)                         # buffer management happens here, not inside the capture
         cur, t = cur.clone(), t.clone()                   # the graph's input buffers
+
         def euler(step, v):                               # same arithmetic as the eager loop, written into the graph's inputs
             cur.copy_(cur - dt[step] * v.to(cur.dtype))
             t.copy_(t - dt[step])
 
-        euler(0, model(cur, t, doc_id=None, kv_cache=cache))   # step 0, eager
+        euler(0, velocity(cur, t))                        # step 0, eager
         graph = torch.cuda.CUDAGraph()
         if self._pool is None:
             self._pool = torch.cuda.graph_pool_handle()
         with OF.frozen_weights(), torch.cuda.graph(graph, pool=self._pool):
-            v = model(cur, t, doc_id=None, kv_cache=cache)
+            v = velocity(cur, t)
         for step in range(1, n):
             graph.replay()
             euler(step, v)
@@ -95,7 +96,7 @@ class AudioCachingSampler:
             for _ in range(self.num_tokens):
                 cur = self._randn((b, 1, channels), x)
                 t = x.new_ones(b, 1)
-                cur = self._denoise(model, cache, cur, t, dt)
+                cur = self._denoise(lambda c, tt: model(c, tt, doc_id=None, kv_cache=cache), cache, 1, cur, t, dt)
                 latents.append(cur)
                 commit(cur)
                 if self.max_window is not None and len(latents) > self.max_window:

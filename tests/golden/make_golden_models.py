@@ -175,6 +175,42 @@ def audio_rollout(A):
     print(f"audio_rollout: {len(draws)} noise draws, out {tuple(out.shape)} absmax {out.abs().max():.3f}")
 
 
+def av_rollout(A):
+    """The reference's own AVCachingSamplerV2 (sampling/av_caching_v2.py) on the reference GameRFTCore carrying the
+    gamerft_core.pt weights, cfg_scale 1.3 (two evaluations per step), same recording harness as audio_rollout."""
+    from owl_wms.models.gamerft import GameRFTCore
+    import owl_wms.nn.kv_cache as K
+    import owl_wms.sampling.av_caching_v2 as S
+    core = torch.load(os.path.join(HERE, "gamerft_core.pt"), weights_only=False)
+    cfg = G.make_cfg(**core["cfg"])
+    model = GameRFTCore(cfg).eval()
+    model.load_state_dict({k: v.float() for k, v in core["state"].items()})
+    S.KVCache = lambda config: K.KVCache(config).to("cpu", torch.float32)
+    g = torch.Generator().manual_seed(97531)
+    B, init_len, n_total, schedule = 2, 3, 6, [1.0, 0.7, 0.3]
+    x = G.bf16r(torch.randn(B, init_len, cfg.channels, cfg.sample_size, cfg.sample_size, generator=g))
+    mouse = 2.0 * torch.randn(B, n_total, 2, generator=g)
+    btn = (torch.rand(B, n_total, cfg.n_buttons, generator=g) < 0.3).float()
+    draws = []
+
+    def draw(shape):
+        z = torch.randn(*shape, generator=g)
+        draws.append(z)
+        return z
+    real_randn, real_like = torch.randn, torch.randn_like
+    torch.randn_like = lambda t, **kw: draw(tuple(t.shape))
+    try:
+        sampler = S.AVCachingSamplerV2(n_steps=len(schedule), cfg_scale=1.3, num_frames=8, noise_prev=0.2, max_window=4,
+                                       custom_schedule=list(schedule))
+        out = sampler(model, x, mouse, btn)
+    finally:
+        torch.randn, torch.randn_like = real_randn, real_like
+    fx = dict(name="av_rollout", weights_from="gamerft_core", x=x, mouse=mouse, btn=btn, schedule=schedule, cfg_scale=1.3,
+              num_frames=8, noise_prev=0.2, max_window=4, draws=draws, out=out)
+    torch.save(fx, os.path.join(HERE, "av_rollout.pt"))
+    print(f"av_rollout: {len(draws)} noise draws, out {tuple(out.shape)} absmax {out.abs().max():.3f}")
+
+
 def main():
     G.install_stubs()
     sys.modules["rotary_embedding_torch"].apply_rotary_emb = None   # imported by embeddings.py:9-12, never called on this path
@@ -182,6 +218,8 @@ def main():
     flex_real = A.flex_attention
     if "--only-av" in sys.argv:
         return gamerft_audio(A, flex_real)
+    if "--only-av-rollout" in sys.argv:
+        return av_rollout(A)
     if "--only-rollout" in sys.argv:
         return audio_rollout(A)
     if "--only-game" not in sys.argv:
@@ -190,6 +228,7 @@ def main():
     gamerft_audio(A, flex_real)
     A.flex_attention = flex_real
     audio_rollout(A)
+    av_rollout(A)
 
 
 if __name__ == "__main__":

@@ -242,3 +242,29 @@ def test_step_condition_posenc_embeddings_vs_oracle():
     assert torch.equal(pe(x), x + pe.p[-5:].unsqueeze(0))              # shorter than n_seq: the LAST n rows
     x = torch.randn(2, 8, 16, device=DEV)
     assert torch.equal(pe(x), x + pe.p.unsqueeze(0))
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_av_caching_sampler_matches_reference_rollout(graph):
+    """AVCachingSamplerV2 on the decode path (T=4 tokens per frame, CFG on the controls, window truncation) vs the reference
+    sampler's recorded rollout; eager and with the per-frame CUDA graph (two model evaluations inside it).  3 frames x 3
+    guided steps compound the per-call bf16 error (guidance extrapolates by 1.3): 4e-2."""
+    from owl_audio_exps_b200.sampling import AVCachingSamplerV2, get_sampler_cls
+    assert get_sampler_cls("av_caching") is AVCachingSamplerV2
+    fx = load_golden("av_rollout")
+    core = load_golden(fx["weights_from"])
+    model = _game(cfg_of(core), core["state"], core["rope"]).eval()
+    draws = iter(fx["draws"])
+
+    def noise_fn(shape, like):
+        z = next(draws)
+        assert tuple(z.shape) == tuple(shape)
+        return z.to(device=like.device, dtype=like.dtype)
+    sampler = AVCachingSamplerV2(n_steps=len(fx["schedule"]), cfg_scale=fx["cfg_scale"], num_frames=fx["num_frames"],
+                                 noise_prev=fx["noise_prev"], max_window=fx["max_window"],
+                                 custom_schedule=list(fx["schedule"]), noise_fn=noise_fn, graph_decode=graph)
+    out = sampler(model, fx["x"].to(DEV), fx["mouse"].to(DEV), fx["btn"].to(DEV))
+    assert next(draws, None) is None
+    assert out.shape == fx["out"].shape
+    assert relerr(out, fx["out"]) <= 4e-2
+    assert not model.transformer.decoding

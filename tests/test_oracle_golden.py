@@ -157,3 +157,24 @@ def test_gamerft_audio_core_matches_reference():
     assert relerr(x.grad, fx["dx"]) < TOL and relerr(audio.grad, fx["daudio"]) < TOL
     for k, g in fx["grads"].items():
         assert relerr(W[k].grad, g) < (5 * TOL if g.dtype == torch.float32 else 4e-3), k
+
+
+def test_av_cached_rollout_matches_reference_sampler():
+    """Oracle rollout vs the reference's own AVCachingSamplerV2 run (cfg_scale 1.3: two model evaluations per step)."""
+    fx = load_golden("av_rollout")
+    core = load_golden(fx["weights_from"])
+    cfg = cfg_of(core)
+    W = _weights(core)
+    draws = iter(fx["draws"])
+
+    def noise(shape):
+        z = next(draws)
+        assert tuple(z.shape) == tuple(shape)
+        return z
+    sched = list(fx["schedule"]) + [0.0]
+    dt = [abs(b - a) for a, b in zip(sched[:-1], sched[1:])]
+    with torch.no_grad():
+        out = O.av_cached_rollout(fx["x"], fx["mouse"], fx["btn"], W, cfg, core["rope"], dt, fx["num_frames"],
+                                  fx["cfg_scale"], fx["noise_prev"], fx["max_window"], noise)
+    assert next(draws, None) is None
+    assert relerr(out, fx["out"]) < 5 * TOL
