@@ -10,6 +10,17 @@ from ..nn.attn import DiT, FinalLayer
 from ..nn.embeddings import ControlEmbedding, TimestepEmbedding
 
 
+def cfg_dropout(has_controls, cfg_prob: float):
+    """gamerft.py:69-91: drop controls from enough samples that at least `cfg_prob` of the batch is control-free.  Written
+    without the reference's data-dependent Python branch (a device sync that cannot sit inside a CUDA-graph capture): when
+    the batch already has enough control-free samples `need` is 0 and nothing is dropped."""
+    have = has_controls.float().mean()
+    need = (cfg_prob - (1.0 - have)).clamp_min(0.0)
+    frac = need / have.clamp_min(1e-12)
+    drop = (torch.rand(has_controls.shape[0], device=has_controls.device) <= frac) & has_controls & (need > 0)
+    return has_controls & (~drop)
+
+
 class GameRFTCore(nn.Module):
     """gamerft.py:13-60."""
 
@@ -57,12 +68,7 @@ class GameRFT(nn.Module):
             cfg_prob = self.config.cfg_prob
         if cfg_prob <= 0.0 or has_controls is None:
             return has_controls
-        have = has_controls.float().mean()
-        if 1.0 - have < cfg_prob:                                              # need more control-free samples
-            frac = (cfg_prob - (1.0 - have)) / have
-            drop = (torch.rand(has_controls.shape[0], device=has_controls.device) <= frac) & has_controls
-            has_controls = has_controls & (~drop)
-        return has_controls
+        return cfg_dropout(has_controls, cfg_prob)
 
     def noise(self, tensor, ts):
         z = torch.randn_like(tensor)

@@ -13,6 +13,7 @@ from .. import functional as OF
 from ..nn.attn import DiT, FinalLayer, UViT
 from ..nn.embeddings import ControlEmbedding, TimestepEmbedding
 from ..nn.normalization import layer_norm
+from .gamerft import cfg_dropout
 
 _COMPILED = "transformer._orig_mod."
 
@@ -99,12 +100,7 @@ class GameRFTAudio(nn.Module):
             cfg_prob = self.cfg_prob
         if cfg_prob <= 0.0 or has_controls is None:
             return has_controls
-        have = has_controls.float().mean()
-        if 1.0 - have < cfg_prob:
-            frac = (cfg_prob - (1.0 - have)) / have
-            drop = (torch.rand(has_controls.shape[0], device=has_controls.device) <= frac) & has_controls
-            has_controls = has_controls & (~drop)
-        return has_controls
+        return cfg_dropout(has_controls, cfg_prob)
 
     def forward(self, x, audio, mouse, btn, return_dict=False, cfg_prob=None, has_controls=None):
         b, n = x.shape[:2]

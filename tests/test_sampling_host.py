@@ -23,3 +23,21 @@ def test_sd3_euler_closed_form_properties():
 
 def test_sampler_registry():
     assert get_sampler_cls("audio_caching") is AudioCachingSampler
+
+
+def test_cfg_dropout_is_branch_free_and_matches_reference_semantics():
+    """gamerft.py:69-91 without the data-dependent branch: enough control-free samples -> untouched; otherwise controls
+    are dropped only where present, bringing the control-free share to ~cfg_prob."""
+    from owl_audio_exps_b200.models.gamerft import cfg_dropout
+    torch.manual_seed(0)
+    full = torch.ones(2000, dtype=torch.bool)
+    out = cfg_dropout(full, 0.3)
+    assert abs((1 - out.float().mean().item()) - 0.3) < 0.04
+    half = full.clone()
+    half[:1000] = False
+    assert torch.equal(cfg_dropout(half, 0.3), half)
+    some = full.clone()
+    some[:200] = False
+    out = cfg_dropout(some, 0.3)
+    assert not (out & ~some).any() and abs((1 - out.float().mean().item()) - 0.3) < 0.04
+    assert not cfg_dropout(torch.zeros(4, dtype=torch.bool), 0.3).any()
