@@ -24,7 +24,7 @@ def get_deltas(custom_schedule):
 
 class AudioCachingSampler:
     def __init__(self, n_steps: int = 16, num_tokens: int = 120, noise_prev: float = 0.2, custom_schedule=None,
-                 max_window=None, noise_fn=None, graph_decode: bool = True) -> None:
+                 max_window=None, noise_fn=None, graph_decode: bool = True, graph_min_steps: int = 10) -> None:
         self.n_steps = n_steps
         self.num_tokens = num_tokens
         self.noise_prev = noise_prev
@@ -32,13 +32,16 @@ class AudioCachingSampler:
         self.max_window = max_window
         self.noise_fn = noise_fn        # (shape, like) -> N(0,1) tensor; default torch.randn on like's device / dtype
         self.graph_decode = graph_decode
+        # capturing + instantiating the decode call costs ~5x its eager time, a replay saves ~60 % of it (measured, audio.yml
+        # and av_v5 geometry: tools/model_step.py, tools/av_decode_ops.py): the graph pays off from ~10 steps per latent
+        self.graph_min_steps = graph_min_steps
         self._pool = None
 
     def _denoise(self, velocity, cache, new_rows, cur, t, dt):
         """n_steps Euler steps of one latent / frame against a fixed cache: cur <- cur - dt*v(cur, t), t <- t - dt.
         `velocity(cur, t)` is the model evaluation (two of them under classifier-free guidance)."""
         n = self.n_steps
-        if not (self.graph_decode and cur.is_cuda and n >= 3):
+        if not (self.graph_decode and cur.is_cuda and n >= max(self.graph_min_steps, 2)):
             for step in range(n):
                 cur = cur - dt[step] * velocity(cur, t).to(cur.dtype)
                 t = t - dt[step]

@@ -13,9 +13,11 @@ from .schedulers import get_sd3_euler
 
 class AVCachingSamplerV2(AudioCachingSampler):
     def __init__(self, n_steps: int = 16, cfg_scale: float = 1.3, num_frames: int = 60, noise_prev: float = 0.2,
-                 max_window=None, custom_schedule=None, noise_fn=None, graph_decode: bool = True) -> None:
+                 max_window=None, custom_schedule=None, noise_fn=None, graph_decode: bool = True,
+                 graph_min_steps: int = 10) -> None:
         super().__init__(n_steps=n_steps, num_tokens=num_frames, noise_prev=noise_prev, custom_schedule=custom_schedule,
-                         max_window=max_window, noise_fn=noise_fn, graph_decode=graph_decode)
+                         max_window=max_window, noise_fn=noise_fn, graph_decode=graph_decode,
+                         graph_min_steps=graph_min_steps)
         self.cfg_scale = cfg_scale
         self.num_frames = num_frames
 

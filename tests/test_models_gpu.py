@@ -176,7 +176,7 @@ def test_sampler_graph_replay_equals_eager_steps():
         g = torch.Generator(device=DEV).manual_seed(11)
         noise_fn = lambda shape, like: torch.randn(*shape, device=like.device, dtype=like.dtype, generator=g)  # noqa: E731
         outs.append(AudioCachingSampler(n_steps=5, num_tokens=4, max_window=6, noise_fn=noise_fn,
-                                        graph_decode=graph)(model, x))
+                                        graph_decode=graph, graph_min_steps=2)(model, x))
     assert torch.equal(outs[0], outs[1])
 
 
@@ -262,7 +262,8 @@ def test_av_caching_sampler_matches_reference_rollout(graph):
         return z.to(device=like.device, dtype=like.dtype)
     sampler = AVCachingSamplerV2(n_steps=len(fx["schedule"]), cfg_scale=fx["cfg_scale"], num_frames=fx["num_frames"],
                                  noise_prev=fx["noise_prev"], max_window=fx["max_window"],
-                                 custom_schedule=list(fx["schedule"]), noise_fn=noise_fn, graph_decode=graph)
+                                 custom_schedule=list(fx["schedule"]), noise_fn=noise_fn, graph_decode=graph,
+                                 graph_min_steps=2)
     out = sampler(model, fx["x"].to(DEV), fx["mouse"].to(DEV), fx["btn"].to(DEV))
     assert next(draws, None) is None
     assert out.shape == fx["out"].shape

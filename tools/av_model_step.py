@@ -63,12 +63,12 @@ ctx = torch.randn(1, 8, 128, 8, 8, device=dev)
 mouse = torch.randn(1, 16, 2, device=dev)
 btn = (torch.rand(1, 16, 11, device=dev) < 0.3).float()
 for graph in (False, True):
-    s = AVCachingSamplerV2(n_steps=8, cfg_scale=1.3, num_frames=8, max_window=16, graph_decode=graph)
+    s = AVCachingSamplerV2(n_steps=16, cfg_scale=1.3, num_frames=4, max_window=16, graph_decode=graph)
     s(core, ctx, mouse, btn)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     s(core, ctx, mouse, btn)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    print(f"AVCachingSamplerV2 B=1, 8-frame context, 8 frames x 8 guided steps, graph_decode={graph}: {dt * 1e3:.0f} ms, "
-          f"{8 / dt:.2f} frames/s, {dt * 1e3 / (8 * 17):.2f} ms per model evaluation")
+    print(f"AVCachingSamplerV2 B=1, 8-frame context, 4 frames x 16 guided steps, graph_decode={graph}: {dt * 1e3:.0f} ms, "
+          f"{4 / dt:.2f} frames/s, {dt * 1e3 / (4 * 33):.2f} ms per model evaluation")

@@ -64,7 +64,7 @@ core.forward = counted
 ctx = torch.randn(1, 104, cfg.channels, device=dev)
 for n_steps in (4, 16):
     for graph in (False, True):
-        sampler = AudioCachingSampler(n_steps=n_steps, num_tokens=16, max_window=120, graph_decode=graph)
+        sampler = AudioCachingSampler(n_steps=n_steps, num_tokens=16, max_window=120, graph_decode=graph, graph_min_steps=2)
         sampler(core, ctx)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
