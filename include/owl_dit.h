@@ -237,7 +237,19 @@ typedef struct owl_attn_mask {
   int32_t causal;        /* 0/1; decode mode (attn.py:106-107, block_mask None) = causal 0, window 0 */
   const int32_t* doc_id; /* [B, doc_ld] or NULL                                                   */
   int64_t doc_ld;
+  /* Optional (all three or none; same [B, doc_ld] indexing, filled by owl_attn_doc_extents): per-frame document
+   * extents that let the kernels skip KV / query tiles lying entirely in other documents, the way the reference's
+   * BlockMask does for packed sequences (attn.py:52-55,62; data/latent_seq_packing.py:94-126).                  */
+  const int32_t* doc_first;  /* first frame carrying the same id as frame f                        */
+  const int32_t* doc_last;   /* last  frame carrying the same id as frame f                        */
+  const int32_t* doc_breaks; /* [B] frames that re-open an id seen earlier (0: ids are contiguous runs, the
+                                extents are exact and no per-key id compare is needed)              */
 } owl_attn_mask;
+
+/* doc_id int32 [B, doc_ld] (F valid frames per row) -> first/last int32 [B, doc_ld], breaks int32 [B].
+ * Replaces the document term of create_block_mask (attn.py:52-55,62) at tile granularity.          */
+int owl_attn_doc_extents(const int32_t* doc_id, int64_t doc_ld, int64_t B, int64_t F, int32_t* first, int32_t* last,
+                         int32_t* breaks, owl_stream_t stream);
 
 int owl_attn_fwd(const void* q, int64_t q_sb, int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh,
                  const void* v, int64_t v_sb, int64_t v_sh, void* o, int64_t o_sb, int64_t o_sl, float* lse,

@@ -31,7 +31,7 @@ class AttnMask(C.Structure):
 
     _fields_ = [
         ("tokens_per_frame", i32), ("window_frames", i32), ("q_offset", i32), ("causal", i32),
-        ("doc_id", vp), ("doc_ld", i64),
+        ("doc_id", vp), ("doc_ld", i64), ("doc_first", vp), ("doc_last", vp), ("doc_breaks", vp),
     ]
 
 
@@ -68,6 +68,7 @@ SIGNATURES = {
     "owl_kv_append": ([vp, i64, i64, vp, i64, i64, i64, i64, i64, i64, i64, vp], C.c_int),
     "owl_layer_norm_fwd": ([vp, vp, i64, i64, f32, vp], C.c_int),
     "owl_layer_norm_bwd": ([vp, vp, vp, i64, i64, f32, vp], C.c_int),
+    "owl_attn_doc_extents": ([vp, i64, i64, i64, vp, vp, vp, vp], C.c_int),
     "owl_attn_fwd": (_ATTN_FWD, C.c_int),
     "owl_attn_bwd": (_ATTN_BWD, C.c_int),
     "owl_attn_fwd_check": (_ATTN_FWD, C.c_int),

@@ -12,6 +12,7 @@
 // columns, smem 2 x 112 KB) so one CTA's softmax overlaps the other's MMAs.
 #include <cuda_bf16.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "attn_common.cuh"
 #include "host_common.h"
@@ -66,7 +67,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int i0 = qt * kTile;
   const int i_last = min(i0 + kTile, p.Lq) - 1;
   int t0, t1;
-  kv_tile_range(p.m, i0, i_last, p.Lk, t0, t1);
+  kv_tile_range_doc(p.m, b, i0, i_last, p.Lk, t0, t1);
   const int n_kv = t1 - t0;
 
   if (threadIdx.x == 0) {
@@ -271,13 +272,12 @@ template <int DH>
 static int launch_attn_fwd(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                            const AttnFwdParams& p, cudaStream_t s) {
   using Cfg = FwdCfg<DH>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e =
-        cudaFuncSetAttribute(attn_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  static PerDeviceOnce once;
+  const int rc0 = once.run([] {
+    return static_cast<int>(
+        cudaFuncSetAttribute(attn_fwd_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  });
+  if (rc0 != OWL_OK) return rc0;
   const long long grid = static_cast<long long>(p.B) * p.H * p.n_qtiles;
   (void)launch_k(attn_fwd_kernel<DH>, dim3(static_cast<unsigned>(grid)), dim3(kFwdThreads), Cfg::kSmemBytes, s, tmQ, tmK, tmV, p);
   return launch_status();
@@ -291,7 +291,45 @@ int fill_mask_params(const owl_attn_mask* mask, MaskParams* m) {
   m->causal = mask->causal;
   m->doc = mask->doc_id;
   m->doc_ld = mask->doc_ld;
+  const bool ext = mask->doc_id != nullptr && mask->doc_first != nullptr && mask->doc_last != nullptr &&
+                   mask->doc_breaks != nullptr;
+  m->doc_first = ext ? mask->doc_first : nullptr;
+  m->doc_last = ext ? mask->doc_last : nullptr;
+  m->doc_breaks = ext ? mask->doc_breaks : nullptr;
   return OWL_OK;
+}
+
+int attn_fwd2_dispatch(const void* q, int64_t q_sb, int64_t q_sh, const void* k, int64_t k_sb, int64_t k_sh,
+                       const void* v, int64_t v_sb, int64_t v_sh, void* o, int64_t o_sb, int64_t o_sl, float* lse,
+                       int64_t B, int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask,
+                       cudaStream_t s);  // attn_fwd2.cu
+
+// Per-frame document extents for tile skipping (see MaskParams): one thread per frame scans its batch row, which
+// sits in shared memory when it fits (F <= 8192).
+__global__ void __launch_bounds__(256)
+attn_doc_extents_kernel(const int* __restrict__ doc, long long ld, int F, int* __restrict__ first,
+                        int* __restrict__ last, int* __restrict__ breaks) {
+  extern __shared__ int s_doc[];
+  pdl_prologue();
+  const int b = blockIdx.y;
+  const int* row = doc + b * ld;
+  const bool in_smem = F <= 8192;
+  if (in_smem) {
+    for (int g = threadIdx.x; g < F; g += blockDim.x) s_doc[g] = row[g];
+    __syncthreads();
+    row = s_doc;
+  }
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  const int id = row[f];
+  int lo = f, hi = f;
+  for (int g = 0; g < f; ++g)
+    if (row[g] == id) { lo = g; break; }
+  for (int g = F - 1; g > f; --g)
+    if (row[g] == id) { hi = g; break; }
+  first[b * ld + f] = lo;
+  last[b * ld + f] = hi;
+  if (f > 0 && row[f - 1] != id && lo != f) atomicAdd(breaks + b, 1);  // this id was open before and re-opens here
 }
 
 }  // namespace owl
@@ -308,6 +346,13 @@ int owl_attn_fwd(const void* q, int64_t q_sb, int64_t q_sh, const void* k, int64
   if (dh != 64 && dh != 128) return OWL_ERR_UNSUPPORTED;
   if (Lq > (1 << 30) || Lk > (1 << 30) || B * H * ((Lq + kTile - 1) / kTile) > INT32_MAX) return OWL_ERR_UNSUPPORTED;
   if (!aligned16(o) || o_sb % 8 || o_sl % 8) return OWL_ERR_ALIGN;
+  {
+    // Lq > 128: the two-tile persistent kernel (attn_fwd2.cu).  OWL_ATTN_FWD=1 forces the single-tile kernel (A/B aid).
+    static const int force = [] { const char* e = getenv("OWL_ATTN_FWD"); return e ? atoi(e) : 0; }();
+    if ((Lq > kTile && force != 1) || force == 2)
+      return attn_fwd2_dispatch(q, q_sb, q_sh, k, k_sb, k_sh, v, v_sb, v_sh, o, o_sb, o_sl, lse, B, H, Lq, Lk, dh, mask,
+                                static_cast<cudaStream_t>(stream));
+  }
   AttnFwdParams p{};
   int rc = fill_mask_params(mask, &p.m);
   if (rc != OWL_OK) return rc;
@@ -321,6 +366,25 @@ int owl_attn_fwd(const void* q, int64_t q_sb, int64_t q_sh, const void* k, int64
   if ((rc = make_tmap_4d_bf16(&tmV, v, dh, Lk, H, B, dh, v_sh, v_sb, 64, kTile)) != OWL_OK) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   return dh == 64 ? launch_attn_fwd<64>(tmQ, tmK, tmV, p, s) : launch_attn_fwd<128>(tmQ, tmK, tmV, p, s);
+}
+
+int owl_attn_doc_extents(const int32_t* doc_id, int64_t doc_ld, int64_t B, int64_t F, int32_t* first, int32_t* last,
+                         int32_t* breaks, owl_stream_t stream) {
+  if (!doc_id || !first || !last || !breaks || B <= 0 || F <= 0 || doc_ld < F) return OWL_ERR_BAD_ARG;
+  if (B > 65535 || F > (1 << 30)) return OWL_ERR_UNSUPPORTED;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(breaks, 0, static_cast<size_t>(B) * sizeof(int32_t), s);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  LaunchOpts lo;
+  lo.pdl = false;  // follows a memset node, not a kernel
+  const size_t smem = F <= 8192 ? static_cast<size_t>(F) * sizeof(int) : 0;
+  e = launch_kx(lo, attn_doc_extents_kernel, dim3(static_cast<unsigned>((F + 255) / 256), static_cast<unsigned>(B)),
+                dim3(256), smem, s, doc_id, static_cast<long long>(doc_ld), static_cast<int>(F), first, last, breaks);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return static_cast<int>(e);
+  }
+  return launch_status();
 }
 
 }  // extern "C"

@@ -146,7 +146,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   const int i0 = qt * kTile;
   const int i_last = min(i0 + kTile, p.Lq) - 1;
   int t0, t1;
-  kv_tile_range(p.m, i0, i_last, p.Lk, t0, t1);
+  kv_tile_range_doc(p.m, b, i0, i_last, p.Lk, t0, t1);
   const int n_kv = t1 - t0;
 
   if (threadIdx.x == 0) {
@@ -335,7 +335,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int j0 = kt * kTile;
   const int j_last = min(j0 + kTile, p.Lk) - 1;
   int t0, t1;
-  q_tile_range(p.m, j0, j_last, p.Lq, t0, t1);
+  q_tile_range(p.m, j0, j_last, p.Lq, t0, t1, b);
   const int n_q = t1 - t0;
 
   if (threadIdx.x == 0) {
@@ -492,9 +492,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 template <int DH>
 static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmDO, const CUtensorMap& tmK,
                            const CUtensorMap& tmV, const AttnBwdParams& p, cudaStream_t s) {
-  static bool configured = false;
   constexpr bool kCanFuse = DH == 64;
-  if (!configured) {
+  static PerDeviceOnce once;
+  const int rc0 = once.run([] {
     cudaError_t e = cudaFuncSetAttribute(attn_bwd_dq_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          DqCfg<DH>::kSmemBytes);
     if (e != cudaSuccess) return static_cast<int>(e);
@@ -506,8 +506,9 @@ static int launch_attn_bwd(const CUtensorMap& tmQ, const CUtensorMap& tmDO, cons
                                DkvCfg<DH, kCanFuse>::kSmemBytes);
       if (e != cudaSuccess) return static_cast<int>(e);
     }
-    configured = true;
-  }
+    return static_cast<int>(OWL_OK);
+  });
+  if (rc0 != OWL_OK) return rc0;
   const long long gq = static_cast<long long>(p.B) * p.H * p.n_qtiles;
   const long long gk = static_cast<long long>(p.B) * p.H * p.n_ktiles;
   if (kCanFuse && p.n_qtiles == 1 && p.n_ktiles == 1) {  // single tile: dq rides on the dkv kernel

@@ -64,8 +64,44 @@ __device__ __forceinline__ void kv_tile_range(const MaskParams& m, int i0, int i
   if (t1 < t0) t1 = t0;
 }
 
-// Query tile range [t0, t1) that can see keys [j0, j1] (inclusive).
-__device__ __forceinline__ void q_tile_range(const MaskParams& m, int j0, int j1, int Lq, int& t0, int& t1) {
+// The same with the document term: tiles that hold only other documents' frames are dropped as well (what the
+// reference's BlockMask does at 128x128 granularity, attn.py:52-55,62).
+__device__ __forceinline__ void kv_tile_range_doc(const MaskParams& m, int b, int i0, int i1, int Lk, int& t0, int& t1) {
+  int lo0, hi0, lo1, hi1;
+  mask_row_range(m, i0, Lk, lo0, hi0);
+  mask_row_range(m, i1, Lk, lo1, hi1);
+  int lo = lo0, hi = hi1;
+  if (m.doc_first != nullptr) {
+    int dlo, dhi;
+    doc_token_range(m, b, (i0 + m.q_offset) / m.T, (i1 + m.q_offset) / m.T, dlo, dhi);
+    lo = dlo > lo ? dlo : lo;
+    hi = dhi < hi ? dhi : hi;
+  }
+  if (hi < lo) hi = lo;
+  t0 = lo / kTile;
+  t1 = (hi + kTile - 1) / kTile;
+  if (t1 < t0) t1 = t0;
+}
+
+// One query row's key range [lo, hi) with its document extent folded in; need_doc_test = an id compare per key is
+// still required inside the range (ids present and not known to be contiguous runs).
+__device__ __forceinline__ void row_range_doc(const MaskParams& m, int b, int i, int Lk, int& lo, int& hi,
+                                              bool& need_doc_test) {
+  mask_row_range(m, i, Lk, lo, hi);
+  need_doc_test = m.doc != nullptr;
+  if (m.doc_first != nullptr) {
+    const int fq = (i + m.q_offset) / m.T;
+    const int dlo = m.doc_first[b * m.doc_ld + fq] * m.T, dhi = (m.doc_last[b * m.doc_ld + fq] + 1) * m.T;
+    lo = dlo > lo ? dlo : lo;
+    hi = dhi < hi ? dhi : hi;
+    if (hi < lo) hi = lo;
+    if (m.doc_breaks[b] == 0) need_doc_test = false;
+  }
+}
+
+// Query tile range [t0, t1) that can see keys [j0, j1] (inclusive): causal / window terms, and - when the mask carries
+// document extents and `b` >= 0 - only queries of the documents those keys belong to.
+__device__ __forceinline__ void q_tile_range(const MaskParams& m, int j0, int j1, int Lq, int& t0, int& t1, int b = -1) {
   long long ilo = 0, ihi = Lq;
   const long long fk0 = j0 / m.T, fk1 = j1 / m.T;
   if (m.causal) ilo = fk0 * m.T - m.q_offset;
@@ -73,6 +109,13 @@ __device__ __forceinline__ void q_tile_range(const MaskParams& m, int j0, int j1
     const long long h = (fk1 + m.W) * m.T - m.q_offset;
     if (h < ihi) ihi = h;
     if (!m.causal) ilo = (fk0 - m.W + 1) * m.T - m.q_offset;
+  }
+  if (b >= 0 && m.doc_first != nullptr) {
+    int dlo, dhi;  // key-frame extents are query-frame extents too (same frame axis, shifted by q_offset tokens)
+    doc_token_range(m, b, static_cast<int>(fk0), static_cast<int>(fk1), dlo, dhi);
+    const long long a = static_cast<long long>(dlo) - m.q_offset, z = static_cast<long long>(dhi) - m.q_offset;
+    if (a > ilo) ilo = a;
+    if (z < ihi) ihi = z;
   }
   if (ilo < 0) ilo = 0;
   if (ihi > Lq) ihi = Lq;

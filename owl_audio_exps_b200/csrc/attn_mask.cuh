@@ -20,7 +20,29 @@ struct MaskParams {
   int causal;
   const int* doc;  // [B, doc_ld] frame-indexed doc ids or nullptr
   long long doc_ld;
+  // Optional per-frame document extents (owl_attn_doc_extents; same [B, doc_ld] indexing), all three or none:
+  //   doc_first[b][f] / doc_last[b][f] = first / last frame whose id equals doc[b][f]  (a bounding range for ANY id
+  //   pattern); doc_breaks[b] = 0 when every id of batch b is one contiguous run (count of frames that re-open an earlier id), in which case the bounding range is
+  //   exact and no per-element id compare is needed.  They let the kernels skip tiles that lie in other documents.
+  const int* doc_first;
+  const int* doc_last;
+  const int* doc_breaks;
 };
+
+// Key-token range [lo, hi) that the rows of frames [f0, f1] (inclusive, frames of q + q_offset) may see under the
+// document term alone: the union of their documents' extents.  Only with doc_first / doc_last present.
+__device__ __forceinline__ void doc_token_range(const MaskParams& m, int b, int f0, int f1, int& lo, int& hi) {
+  const int* fr = m.doc_first + b * m.doc_ld;
+  const int* la = m.doc_last + b * m.doc_ld;
+  int a = fr[f0], z = la[f0];
+  for (int f = f0 + 1; f <= f1; ++f) {
+    const int x = fr[f], y = la[f];
+    a = x < a ? x : a;
+    z = y > z ? y : z;
+  }
+  lo = a * m.T;
+  hi = (z + 1) * m.T;
+}
 
 __host__ __device__ __forceinline__ void mask_row_range(const MaskParams& m, int i, int Lk, int& lo, int& hi) {
   const int fq = (i + m.q_offset) / m.T;

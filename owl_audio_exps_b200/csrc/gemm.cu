@@ -445,17 +445,17 @@ struct GemmMaps {
 
 template <int BN, bool A_MN, bool B_MN, int CTAS>
 static int launch_gemm(const GemmMaps& tm, const GemmParams& p, int grid, int smem_bytes, bool pdl, cudaStream_t stream) {
-  static bool configured = false;  // idempotent attribute; a benign race at worst sets it twice
   auto kern = p.mode == OWL_EPI_F32 ? gemm_f32_kernel<BN, A_MN, B_MN, CTAS> : gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>;
-  if (!configured) {
+  static PerDeviceOnce once;
+  const int rc0 = once.run([] {
     cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN, CTAS>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemLimit);
     if (e != cudaSuccess) return static_cast<int>(e);
     e = cudaFuncSetAttribute(gemm_f32_kernel<BN, A_MN, B_MN, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              kSmemLimit);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+    return static_cast<int>(e);
+  });
+  if (rc0 != OWL_OK) return rc0;
   LaunchOpts o;
   o.pdl = pdl;
   o.cluster_x = CTAS;  // the two CTAs of a pair share a TPC

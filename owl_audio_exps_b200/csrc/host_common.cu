@@ -112,15 +112,16 @@ int make_tmap_4d_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_
 }
 
 int sm_count() {
-  static int n = 0;
+  static std::atomic<int> cache[64];   // per device (zero-initialised)
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  std::atomic<int>& slot = cache[dev & 63];
+  int n = slot.load(std::memory_order_relaxed);
   if (n == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
-      n = v;
-    else
-      n = 148;
+    int v = 0;
+    n = (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) ? v : 148;
     (void)cudaGetLastError();
+    slot.store(n, std::memory_order_relaxed);
   }
   return n;
 }

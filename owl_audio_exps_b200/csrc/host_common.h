@@ -86,6 +86,25 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   return launch_kx(LaunchOpts{}, kern, grid, block, smem, stream, static_cast<Args&&>(args)...);
 }
 
+// One-time, PER-DEVICE kernel configuration (cudaFuncSetAttribute is per device: a process that drives several GPUs --
+// the per-GPU-stream rollout replicas -- must opt every device into > 48 KB of dynamic shared memory).
+class PerDeviceOnce {
+  std::atomic<uint64_t> done_{0};
+
+ public:
+  template <class F>
+  int run(F&& f) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+    const uint64_t bit = 1ull << (dev & 63);
+    if (done_.load(std::memory_order_acquire) & bit) return OWL_OK;
+    const int rc = f();   // idempotent attribute writes: a race between two threads at worst sets them twice
+    if (rc != OWL_OK) return rc;
+    done_.fetch_or(bit, std::memory_order_release);
+    return OWL_OK;
+  }
+};
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace owl

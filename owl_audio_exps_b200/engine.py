@@ -28,16 +28,22 @@ f32 = torch.float32
 class GradSink:
     """What functional._sink returns: the fp32 bucket view of one parameter + whether to add to it."""
 
-    __slots__ = ("view", "owner", "pre_zeroed")
+    __slots__ = ("view", "owner", "pre_zeroed", "written")
 
     def __init__(self, view: torch.Tensor, owner: "GradBuckets", pre_zeroed: bool = False):
         self.view, self.owner, self.pre_zeroed = view, owner, pre_zeroed
+        self.written = -1    # owner.step_id of the last step this sink was written in
 
     @property
     def accumulate(self) -> bool:
+        """Read ONCE per write by the kernel launcher (functional._wgrad / _bgrad / _fresh_or_sink): the first write of a
+        step overwrites, every later one (second micro-batch, or a second backward through the same block inside one
+        loss: self-forcing / distillation trainers call the model twice) adds."""
         # bias gradients are column sums built with atomics: the engine zeroes all of them with ONE multi-tensor
         # kernel at begin_step, so the kernels always add (no memset node in front of every column sum)
-        return self.pre_zeroed or self.owner.accumulate
+        again = self.written == self.owner.step_id
+        self.written = self.owner.step_id
+        return self.pre_zeroed or self.owner.accumulate or again
 
 
 class CondSink:
@@ -45,15 +51,23 @@ class CondSink:
     conditioning projections as one [n_layers*6d, d] matrix (+ [n_layers*6d] biases) inside one flat bucket,
     so a group of layers' weight gradients is ONE GEMM written in place."""
 
-    __slots__ = ("gw", "gb", "owner", "index", "gb_pre_zeroed")
+    __slots__ = ("gw", "gb", "owner", "index", "gb_pre_zeroed", "written")
 
     def __init__(self, gw, gb, owner: "GradBuckets", index: int):
         self.gw, self.gb, self.owner, self.index = gw, gb, owner, index
         self.gb_pre_zeroed = True   # GradBuckets.begin_step zeroes every bias sink (incl. gb) in one kernel
+        self.written = {}           # first weight row of a group -> owner.step_id of its last write
 
     @property
     def accumulate(self) -> bool:
         return self.owner.accumulate
+
+    def acc_rows(self, r0: int) -> bool:
+        """Asked by CondBank at the moment it writes the weight gradient of the row group starting at r0: the first
+        write of a step overwrites, later ones (next micro-batch, second backward of the stack in one loss) add."""
+        again = self.written.get(r0) == self.owner.step_id
+        self.written[r0] = self.owner.step_id
+        return self.owner.accumulate or again
 
     def after_group(self, r0: int, r1: int):
         self.owner._cond_rows_done(self.index, r0, r1)
@@ -72,8 +86,14 @@ def _align(n: int, a: int = 64) -> int:
 
 class GradBuckets:
     def __init__(self, model: torch.nn.Module, process_group=None, comm_stream: Optional[torch.cuda.Stream] = None,
-                 average: bool = True, wgrad_side_stream: bool = True):
+                 average: bool = True, wgrad_side_stream: bool = True, backwards_per_step: int = 1):
+        """backwards_per_step: how many times every block runs backward in one micro-batch (2 when the loss calls the
+        model twice, as the reference's self-forcing / causvid / distillation trainers do).  A block's bucket is handed
+        to NCCL after its LAST expected backward; one more than declared raises (the bucket would be reduced twice)."""
         from .nn.attn import DiT, DiTBlock
+        self.backwards_per_step = max(1, int(backwards_per_step))
+        self.step_id = 0
+        self._seen: dict = {}
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.average = average
@@ -106,6 +126,7 @@ class GradBuckets:
         self.rest_index = len(groups)
         groups.append(rest)
         self.flats: List[torch.Tensor] = []
+        self._views: List = []       # (param, its bucket view): what begin_step re-attaches as p.grad
         self._bias_views: List[torch.Tensor] = []
         dev = next(model.parameters()).device
         for gi, ps in enumerate(groups):
@@ -117,6 +138,7 @@ class GradBuckets:
                     raise RuntimeError("GradBuckets needs fp32 master parameters (the autocast training regime)")
                 view = flat[off:off + p.numel()].view_as(p)
                 p.grad = view
+                self._views.append((p, view))
                 if gi != self.rest_index:
                     p._owl_grad_sink = GradSink(view, self, pre_zeroed=p.dim() == 1)
                     if p.dim() == 1:
@@ -150,6 +172,9 @@ class GradBuckets:
     def begin_step(self):
         """Call before the first micro-batch's forward."""
         self.accumulate = False
+        self.step_id += 1
+        self._seen.clear()
+        self._reattach()
         self._reserve_sms(0)                  # no exchange in flight during forward: GEMMs use every SM
         self.flats[self.rest_index].zero_()   # these grads arrive through autograd's accumulate-in-place
         if self._bias_views:
@@ -157,17 +182,28 @@ class GradBuckets:
         self._pending.clear()
         self._reset_cond()
 
+    def _reattach(self):
+        """`optimizer.zero_grad(set_to_none=True)` (the reference trainers: rft_trainer.py:200, audio_rft_trainer.py:206)
+        drops `p.grad`; the sinks keep writing into the buckets, so the views are put back before every step.  With the
+        buckets in place zero_grad() is unnecessary: begin_step zeroes what accumulates and the rest is overwritten."""
+        for p, view in self._views:
+            if p.grad is not view:
+                p.grad = view
+
     def _reset_cond(self):
         for ci, (dit, gi, nw, d) in enumerate(self.cond_stacks):
             self._cond_low[ci] = nw // d
 
     def next_micro_batch(self):
         self.accumulate = True
+        self._seen.clear()
         self._reset_cond()
 
     def _cond_rows_done(self, ci: int, r0: int, r1: int):
         """CondBank finished the weight gradient of rows [r0, r1) (groups complete from the tail)."""
         dit, gi, nw, d = self.cond_stacks[ci]
+        if not self._last_pass(("cond", ci, r0)):
+            return
         if self.sync_grads and r1 == self._cond_low[ci]:
             self._reduce(self.flats[gi][r0 * d:r1 * d])
             self._cond_low[ci] = r0
@@ -196,8 +232,18 @@ class GradBuckets:
             if self.average:
                 flat.div_(self.world)
 
+    def _last_pass(self, key) -> bool:
+        n = self._seen.get(key, 0) + 1
+        self._seen[key] = n
+        if n > self.backwards_per_step:
+            raise RuntimeError(
+                f"GradBuckets: {key} ran backward {n} times in one micro-batch but backwards_per_step="
+                f"{self.backwards_per_step}; its bucket has already been handed to the all-reduce. Construct "
+                f"GradBuckets(model, backwards_per_step=<model calls per loss>).")
+        return n == self.backwards_per_step
+
     def _block_done(self, i: int):
-        if self.sync_grads:
+        if self._last_pass(("block", i)) and self.sync_grads:
             self._reduce(self.flats[i])
 
     def finish_step(self):
@@ -221,7 +267,8 @@ class GradBuckets:
 
     def detach(self):
         from . import functional as OF
-        OF.set_side_stream(None)
+        if OF._Side.stream is self.side_stream:   # another engine may have installed its own since
+            OF.set_side_stream(None)
         for dit, gi, nw, d in self.cond_stacks:
             dit._stage.cond_sink = None
         for blk in self.blocks:

@@ -47,10 +47,13 @@ class FrameMask:
     q_offset: int = 0
     causal: bool = True
     doc_id: Optional[torch.Tensor] = None  # int32 [B, n_frames_total] on the device, or None
+    # (first, last, breaks) from ops.attn_doc_extents(doc_id): per-frame document extents that let the kernels skip
+    # tiles of other documents (the BlockMask sparsity of attn.py:52-55,62); None = per-element id compare only
+    doc_ext: Optional[tuple] = None
 
     def kw(self):
         return dict(tokens_per_frame=self.tokens_per_frame, window_frames=self.window_frames,
-                    q_offset=self.q_offset, causal=self.causal, doc_id=self.doc_id)
+                    q_offset=self.q_offset, causal=self.causal, doc_id=self.doc_id, doc_ext=self.doc_ext)
 
     def mask_mod(self, b, h, q, kv):
         """Same predicate as the closure in attn.py:43-59 (for tests / dense rendering)."""
@@ -81,14 +84,31 @@ def _capturing() -> bool:
 
 
 _FROZEN = False
+_EPOCH = 0   # bumped whenever staged operands may have gone stale without a visible `_version` change
+
+
+def restage() -> None:
+    """Invalidate every staged bf16 operand.  Needed only inside a `frozen_weights()` region after parameters were
+    mutated through `.data` (ema_pytorch's EMA.update / copy_params_from_model_to_ema do that: in-place writes through
+    `.data` do not bump `Tensor._version`); outside such a region nothing is cached across forwards."""
+    global _EPOCH
+    _EPOCH += 1
 
 
 @contextlib.contextmanager
 def frozen_weights():
-    """Inside this context a CUDA-graph capture may reuse operands staged before it (inference: the parameters do not
-    change between replays), instead of recording the fp32 -> bf16 casts into the graph."""
-    global _FROZEN
-    prev, _FROZEN = _FROZEN, True
+    """Declares that parameters do not change inside this context (one sampling call, one CUDA-graph capture for
+    inference): staged bf16 operands are reused across forwards and a graph capture may reuse operands staged before
+    it instead of recording the fp32 -> bf16 casts.  Entering the outermost context re-stages once, so whatever
+    happened to the parameters before it (optimizer steps, EMA updates through `.data`) is picked up.
+
+    OUTSIDE this context every forward re-casts fp32 master weights / re-concatenates operand groups -- exactly what
+    autocast does per forward (its weight cache lives only inside one autocast region)."""
+    global _FROZEN, _EPOCH
+    prev = _FROZEN
+    if not prev:
+        _EPOCH += 1
+    _FROZEN = True
     try:
         yield
     finally:
@@ -96,10 +116,13 @@ def frozen_weights():
 
 
 class WeightStage:
-    """bf16 operand copies of a module's parameters, re-staged when a parameter's version changes.
+    """bf16 operand copies of a module's parameters.
 
-    Inside CUDA-graph capture nothing is cached: the casts are recorded into the graph so each replay
-    sees the current master weights."""
+    Cached across forwards ONLY inside `frozen_weights()` (keyed on data_ptr / _version / dtype / restage epoch);
+    otherwise re-staged every forward, because `_version` misses in-place updates made through `.data` (EMA).
+    A single contiguous bf16 parameter is never copied (the operand aliases it), so the pure-bf16 inference regime
+    pays nothing.  Inside CUDA-graph capture of a training step nothing is cached either: the casts are recorded
+    into the graph so each replay sees the current master weights."""
 
     def __init__(self):
         self._slots = {}
@@ -116,9 +139,9 @@ class WeightStage:
         launch per 8 matrices (ops.cast_f32_bf16_multi) instead of one launch per parameter."""
         outs, pairs = [], []
         for key, params in items:
-            vers = tuple((p.data_ptr(), p._version, p.dtype) for p in params)
+            vers = (_EPOCH,) + tuple((p.data_ptr(), p._version, p.dtype) for p in params)
             hit = self._slots.get(key)
-            if hit is not None and hit[0] == vers and (_FROZEN or not _capturing()):
+            if hit is not None and hit[0] == vers and _FROZEN:
                 outs.append(hit[1])
                 continue
             p0 = params[0]
@@ -141,7 +164,7 @@ class WeightStage:
                     else:
                         dst.copy_(p.detach())
                     r += p.shape[0]
-            if not _capturing():
+            if _FROZEN and not _capturing():
                 self._slots[key] = (vers, out)
             outs.append(out)
         if pairs:
@@ -484,7 +507,7 @@ def _attn_core_fwd(qkv: torch.Tensor, plan: AttnPlan, need_grad: bool):
         # backward will need them later (self-forcing, sf_vid_only.py:180-190) the attention operands
         # must not alias the cache (it is overwritten by later frames), so a private copy is used.
         private = need_grad and not cache.should_update
-        k_all, v_all = cache._operands(plan.layer_idx, L, use_old=offset > 0, private=private)
+        k_all, v_all = cache._operands(plan.layer_idx, L, use_old=offset > 0, private=private, batch=B, device=dev)
         k_new, v_new = k_all[:, :, n_old:], v_all[:, :, n_old:]
     else:
         k_all = torch.empty(B, H, L, dh, device=dev, dtype=bf16)
@@ -596,6 +619,7 @@ class CondBank:
         self.after_group = None  # engine hook: (row_lo, row_hi) of gw finished
         self.want_wgrad = False
         self.sunk = False        # gw/gb are engine bucket views (then the group wgrads may run on the side stream)
+        self.sink = None         # engine.CondSink (decides add-vs-overwrite per row group at write time)
         self.token_grad = None
         self._done = set()
         self._flushed = 0        # layers [_flushed_lo, n_layers) already went through the group wgrad
@@ -642,10 +666,12 @@ class CondBank:
         R = self.mod_all.shape[0]
         dm = self.dmod_all[:, r0:r1]
 
+        acc = self.sink.acc_rows(r0) if self.sink is not None else self.accumulate
+
         def run():
             ops.gemm(OWL_GEMM_TN, dm, self.scond16, r1 - r0, self.d, R, mode=OWL_EPI_F32, outf=self.gw[r0:r1],
-                     accumulate=self.accumulate)
-            ops.colsum(dm, self.gb[r0:r1], accumulate=self.accumulate or self.gb_pre_zeroed)
+                     accumulate=acc)
+            ops.colsum(dm, self.gb[r0:r1], accumulate=acc or self.gb_pre_zeroed)
         if self.sunk:
             _on_side(run, self.dmod_all, self.scond16)
         else:
@@ -678,6 +704,7 @@ class CondBankFn(torch.autograd.Function):
                 if sink is not None:
                     bank.gw, bank.gb, bank.accumulate, bank.after_group = sink.gw, sink.gb, sink.accumulate, sink.after_group
                     bank.sunk = True
+                    bank.sink = sink
                     bank.gb_pre_zeroed = getattr(sink, "gb_pre_zeroed", False)
                 else:
                     bank.gw = torch.empty(N, d, device=scond16.device, dtype=f32)

@@ -34,10 +34,29 @@ def get_block_mask(n_tokens: int, tokens_per_frame: int, window_len=None, doc_id
     if not is_causal:
         assert q_offset == 0, "kv caching not supported with bidirectional"
     window = 0 if window_len is None else int(window_len)  # None -> n_frames in the reference = never binding
+    doc_ext = None
     if doc_id is not None:
         doc_id = doc_id.to(device=device, dtype=torch.int32).contiguous()
+        if doc_id.is_cuda:
+            # document extents once per mask (tiny kernel): tiles that hold only other documents are then skipped
+            doc_ext = _doc_extents(doc_id)
     return FrameMask(tokens_per_frame=int(tokens_per_frame), window_frames=window, q_offset=int(q_offset),
-                     causal=bool(is_causal), doc_id=doc_id)
+                     causal=bool(is_causal), doc_id=doc_id, doc_ext=doc_ext)
+
+
+_DOC_EXT_CACHE = {}
+
+
+def _doc_extents(doc_id):
+    """DiT.forward builds the local and the global mask from the same doc_id (attn.py:179-182): one launch serves both."""
+    from .. import ops
+    key = (doc_id.data_ptr(), doc_id._version, tuple(doc_id.shape))
+    hit = _DOC_EXT_CACHE.get("last")
+    if hit is not None and hit[0] == key and hit[1] is doc_id:
+        return hit[2]
+    ext = ops.attn_doc_extents(doc_id)
+    _DOC_EXT_CACHE["last"] = (key, doc_id, ext)
+    return ext
 
 
 def _check_mask(block_mask):

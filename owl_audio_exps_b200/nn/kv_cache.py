@@ -107,10 +107,25 @@ class SingleKVCache:
         self._k[i], self._v[i], self._start[i] = nk, nv, 0
 
     # ---- hot-path hooks used by functional._attn_core_fwd --------------------------------------
-    def _operands(self, i: int, n_new: int, use_old: bool, private: bool):
+    def _operands(self, i: int, n_new: int, use_old: bool, private: bool, batch=None, device=None):
         """(k_all, v_all) views of [B, H, n_old + n_new, dh]: cached rows followed by n_new writable
-        rows.  `private`: return a copy that does not alias the cache buffers."""
+        rows.  `private`: return a copy that does not alias the cache buffers.  `batch` / `device`: those of the
+        incoming qkv -- the kernel sizes its writes from qkv, so a mismatch must fail here, on the host."""
         self._check()
+        if self.dtype != torch.bfloat16:
+            raise RuntimeError(f"KV cache dtype {self.dtype}: the sm_100a attention path stores K/V in bf16 "
+                               "(kv_cache.py:18 default); call cache.to(dtype=torch.bfloat16)")
+        if device is not None and torch.device(self.device).type != device.type:
+            raise RuntimeError(f"KV cache lives on {self.device}, activations on {device}")
+        if batch is not None and batch != self._batch:
+            if use_old and self._len[i] > 0:   # the reference fails in torch.cat (attn.py:94) in this case
+                raise RuntimeError(f"KV cache holds batch {self._batch}, forward has batch {batch}")
+            # empty cache: the reference accepts any batch on the first update (kv_cache.py:50-58)
+            if any(self._len):
+                raise RuntimeError(f"KV cache holds batch {self._batch} in other layers, forward has batch {batch}")
+            off = list(self.offsets)
+            self.reset(batch)
+            self.offsets = off
         n_old = self._len[i] if use_old else 0
         if not use_old and self.should_update:
             self._start[i], self._len[i] = 0, 0  # offset 0: cache restarts (attn.py:92 skips the prepend)

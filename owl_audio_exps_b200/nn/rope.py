@@ -12,8 +12,17 @@ package's published closed forms are restated in `_lang_freqs`, `_pixel_freqs`, 
   forward(t)      = outer(t, freqs) with every frequency repeated twice
   get_axial_freqs = per axis: pos = linspace(-1, 1, n) ('pixel') (+ offset), forward(pos), broadcast, concat
 PARITY UNPINNED for the 'pixel' / axial form (OrthoRoPE): the reference has no golden vector for it
-(its only checksum, sanity/rope_test.py:91, targets a deleted class).  The hot-path tests feed
-identical tables to both sides, so block parity does not depend on this restatement.
+(its only checksum, sanity/rope_test.py:91, targets a deleted class), the package is not installed in the build
+image, and its releases differ on which axes of `get_axial_freqs` use linspace(-1, 1) (all of them, or only the
+last two with arange on the leading ones).  So:
+  * when `rotary_embedding_torch` IS importable (any real deployment of the reference has it: requirements.txt:5),
+    OrthoRoPE builds its table by calling the package exactly as the reference does (rope.py:65-73) -- init-time
+    plumbing, identical tables by construction, whatever the installed release does;
+  * otherwise the restatement below is used; `config.rope_axial_variant` ("all_linspace", the default, or
+    "last_two_linspace") selects the release behaviour being restated.
+The cos/sin buffers are non-persistent (rope.py:40-41), so a checkpoint never carries them: a reference AV
+checkpoint loaded here runs with whatever table this file builds.  The hot-path tests feed identical tables to
+both sides, so block parity does not depend on this restatement.
 """
 import math
 
@@ -50,10 +59,11 @@ def _pixel_freqs(dim: int, max_freq: float) -> torch.Tensor:
     return torch.linspace(1.0, max_freq / 2, dim // 2) * math.pi
 
 
-def _axial_freqs(freqs: torch.Tensor, dims, offsets, pixel: bool) -> torch.Tensor:
+def _axial_freqs(freqs: torch.Tensor, dims, offsets, pixel: bool, variant: str = "all_linspace") -> torch.Tensor:
     parts = []
     for i, n in enumerate(dims):
-        pos = torch.linspace(-1, 1, steps=n) if pixel else torch.arange(n).float()
+        lin = pixel and (variant == "all_linspace" or i >= len(dims) - 2)
+        pos = torch.linspace(-1, 1, steps=n) if lin else torch.arange(n).float()
         pos = pos + (0 if offsets is None else offsets[i])
         ang = (pos[:, None] * freqs[None, :]).repeat_interleave(2, dim=-1)  # [n, 2*len(freqs)]
         shape = [1] * len(dims) + [ang.shape[-1]]
@@ -89,8 +99,14 @@ class OrthoRoPE(RoPE):
     def get_freqs(self, config):
         p = config.sample_size
         head_dim = config.d_model // config.n_heads
-        base = _pixel_freqs(head_dim // 4, max_freq=256)
-        freqs = _axial_freqs(base, (config.n_frames, p + 1, p + 1, 1), (0, 0, 0, 1), pixel=True)
+        try:   # the reference's own table builder, when its third-party dependency is installed (rope.py:65-73)
+            from rotary_embedding_torch import RotaryEmbedding
+            pos_emb = RotaryEmbedding(dim=head_dim // 4, freqs_for="pixel", max_freq=256)
+            freqs = pos_emb.get_axial_freqs(config.n_frames, p + 1, p + 1, 1, offsets=(0, 0, 0, 1)).detach().float()
+        except ImportError:
+            base = _pixel_freqs(head_dim // 4, max_freq=256)
+            freqs = _axial_freqs(base, (config.n_frames, p + 1, p + 1, 1), (0, 0, 0, 1), pixel=True,
+                                 variant=getattr(config, "rope_axial_variant", "all_linspace"))
         freqs = freqs.view(config.n_frames, p + 1, p + 1, -1)
         vid = freqs[:, :p, :p].reshape(config.n_frames, p ** 2, -1)
         aud = freqs[:, -1, -1].unsqueeze(1)

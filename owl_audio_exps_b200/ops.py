@@ -378,13 +378,35 @@ def kv_append(src, cache, pos: int):
 # ------------------------------------------------------------------------------------------------
 # attention
 # ------------------------------------------------------------------------------------------------
-def _mask(tokens_per_frame: int, window_frames: int, q_offset: int, causal: bool, doc_id) -> AttnMask:
+def _mask(tokens_per_frame: int, window_frames: int, q_offset: int, causal: bool, doc_id, doc_ext=None) -> AttnMask:
     m = AttnMask()
     m.tokens_per_frame, m.window_frames, m.q_offset, m.causal = tokens_per_frame, window_frames, q_offset, int(causal)
     if doc_id is not None:
         _req(doc_id, torch.int32)
         m.doc_id, m.doc_ld = doc_id.data_ptr(), doc_id.stride(0)
+        if doc_ext is not None:
+            first, last, breaks = doc_ext
+            if first.stride(0) != doc_id.stride(0) or last.stride(0) != doc_id.stride(0):
+                raise RuntimeError("document extents must share doc_id's row stride")
+            m.doc_first, m.doc_last, m.doc_breaks = first.data_ptr(), last.data_ptr(), breaks.data_ptr()
     return m
+
+
+@_prof("attn_doc_extents")
+def attn_doc_extents(doc_id: torch.Tensor):
+    """doc_id int32 [B, F] -> (first, last int32 [B, F], breaks int32 [B]); see include/owl_dit.h."""
+    _req(doc_id, torch.int32)
+    if doc_id.dim() != 2 or doc_id.stride(1) != 1:
+        raise RuntimeError("doc_id must be [B, F] with contiguous rows")
+    B, F = doc_id.shape
+    ld = doc_id.stride(0)
+    first = torch.empty_strided((B, F), (ld, 1), device=doc_id.device, dtype=torch.int32)
+    last = torch.empty_strided((B, F), (ld, 1), device=doc_id.device, dtype=torch.int32)
+    breaks = torch.empty(B, device=doc_id.device, dtype=torch.int32)
+    rc = _lib.load().owl_attn_doc_extents(doc_id.data_ptr(), ld, B, F, first.data_ptr(), last.data_ptr(),
+                                          breaks.data_ptr(), _stream())
+    _lib.check(rc, "owl_attn_doc_extents")
+    return first, last, breaks
 
 
 def _hm(t: torch.Tensor):
@@ -397,14 +419,14 @@ def _hm(t: torch.Tensor):
 
 @_prof("attn_fwd")
 def attn_fwd(q, k, v, *, tokens_per_frame: int, window_frames: int = 0, q_offset: int = 0, causal: bool = True,
-             doc_id=None, want_lse: bool = True, check: bool = False):
+             doc_id=None, doc_ext=None, want_lse: bool = True, check: bool = False):
     """q [B,H,Lq,dh], k/v [B,H,Lk,dh] -> o [B,Lq,H*dh] (token-major, ready for the out Linear), lse [B,H,Lq]."""
     lib = _lib.load()
     B, H, Lq, dh = q.shape
     Lk = k.shape[2]
     o = torch.empty(B, Lq, H * dh, device=q.device, dtype=bf16)
     lse = torch.empty(B, H, Lq, device=q.device, dtype=torch.float32) if want_lse else None
-    m = _mask(tokens_per_frame, window_frames, q_offset, causal, doc_id)
+    m = _mask(tokens_per_frame, window_frames, q_offset, causal, doc_id, doc_ext)
     fn = lib.owl_attn_fwd_check if check else lib.owl_attn_fwd
     rc = fn(*_hm(q), *_hm(k), *_hm(v), o.data_ptr(), o.stride(0), o.stride(1), _p(lse), B, H, Lq, Lk, dh, C.byref(m),
             _stream())
@@ -414,7 +436,7 @@ def attn_fwd(q, k, v, *, tokens_per_frame: int, window_frames: int = 0, q_offset
 
 @_prof("attn_bwd")
 def attn_bwd(dout, o, q, k, v, lse, *, tokens_per_frame: int, window_frames: int = 0, q_offset: int = 0,
-             causal: bool = True, doc_id=None, check: bool = False, dq=None, dk=None, dv=None):
+             causal: bool = True, doc_id=None, doc_ext=None, check: bool = False, dq=None, dk=None, dv=None):
     """Returns (dq, dk, dv) in [B,H,L,dh]."""
     lib = _lib.load()
     B, H, Lq, dh = q.shape
@@ -427,7 +449,7 @@ def attn_bwd(dout, o, q, k, v, lse, *, tokens_per_frame: int, window_frames: int
     dv = torch.empty(B, H, Lk, dh, device=q.device, dtype=bf16) if dv is None else dv
     delta = torch.empty(B, H, Lq, device=q.device, dtype=torch.float32)
     dq_acc = None if check else torch.empty(attn_bwd_workspace_elems(B, H, Lq, dh), device=q.device, dtype=torch.float32)
-    m = _mask(tokens_per_frame, window_frames, q_offset, causal, doc_id)
+    m = _mask(tokens_per_frame, window_frames, q_offset, causal, doc_id, doc_ext)
     fn = lib.owl_attn_bwd_check if check else lib.owl_attn_bwd
     rc = fn(dout.data_ptr(), o.data_ptr(), o.stride(0), o.stride(1), *_hm(q), *_hm(k), *_hm(v), lse.data_ptr(),
             delta.data_ptr(), _p(dq_acc), *_hm(dq), *_hm(dk), *_hm(dv), B, H, Lq, Lk, dh, C.byref(m), _stream())

@@ -76,6 +76,12 @@ class AudioCachingSampler:
 
     @torch.no_grad()
     def __call__(self, model, x, decode_fn=None, vae_scale=1.0, compile_on_decode=False):
+        # parameters do not change during one sampling call: operands are staged once on entry (picking up any EMA /
+        # optimizer update made since the last call) and reused by every model evaluation and graph capture inside
+        with OF.frozen_weights():
+            return self._run(model, x, decode_fn, vae_scale)
+
+    def _run(self, model, x, decode_fn=None, vae_scale=1.0):
         """model: AudioRFTCore; x [b, init_len, channels] -> [b, init_len + num_tokens, channels] (and waveforms when
         decode_fn is given).  `compile_on_decode` is accepted and ignored: the decode step already is hand-written kernels."""
         b, _, channels = x.shape

@@ -6,6 +6,7 @@ and append, drop the oldest frame once the window is full); with cfg_scale != 1 
 and on zeroed controls and extrapolates.  Both evaluations of a step sit in the per-frame CUDA graph."""
 import torch
 
+from .. import functional as OF
 from ..nn.kv_cache import KVCache
 from .audio_caching import AudioCachingSampler, get_deltas
 from .schedulers import get_sd3_euler
@@ -23,6 +24,10 @@ class AVCachingSamplerV2(AudioCachingSampler):
 
     @torch.no_grad()
     def __call__(self, model, x, mouse, btn, compile_on_decode=False):
+        with OF.frozen_weights():    # see AudioCachingSampler.__call__
+            return self._run(model, x, mouse, btn)
+
+    def _run(self, model, x, mouse, btn):
         """x [b, init_len, c, h, w], mouse [b, n, 2], btn [b, n, n_buttons] (n >= init_len: controls of the frames to
         generate follow those of the context) -> [b, init_len + frames, c, h, w]."""
         b, init_len = x.size(0), x.size(1)

@@ -46,6 +46,19 @@ CASES = [
     (1, 2, 130, 65 * 5, 64, 65, 3, True, False),       # cached, masked path with q_offset
     (2, 2, 520, 520, 64, 65, 3, False, False),         # bidirectional window
     (1, 2, 300, 300, 128, 1, 16, True, False),
+    # two-tile persistent forward (attn_fwd2.cu): odd tile counts, ragged tails, dh 128, prefix, many work items per CTA
+    (1, 2, 384, 384, 64, 64, 0, True, False),          # 3 query tiles: the last pair has only tile 0
+    (1, 1, 129, 129, 64, 1, 0, True, False),           # tile 1 holds a single row
+    (2, 3, 1100, 1100, 128, 1, 5, True, False),        # narrow window: tile 0 / tile 1 use different KV ranges
+    (1, 2, 700, 1470, 64, 70, 0, True, False),         # q_offset = 770 tokens of KV prefix, T = 70
+    (3, 20, 1280, 1280, 64, 64, 0, True, False),       # 300 work items > 148 CTAs: persistence, barrier phases
+    (1, 2, 1040, 1040, 128, 65, 0, True, False),
+    # document masks with extents (tile skipping): contiguous runs, and ids that re-open (bounding range + id compare)
+    (1, 2, 2048, 2048, 64, 64, 8, True, "ext"),
+    (1, 2, 4096, 4096, 64, 64, 0, True, "ext"),
+    (1, 2, 4096, 4096, 64, 64, 0, True, "ext_nc"),
+    (2, 2, 1536, 1536, 128, 64, 0, False, "ext"),      # bidirectional + docs
+    (1, 2, 8192, 8192, 64, 64, 0, True, "ext"),        # parity at L >= 8192 with doc ids
 ]
 
 
@@ -58,7 +71,12 @@ def _inputs(case, dev):
     doc = None
     if use_doc:
         nF = (Lk + T - 1) // T
-        doc = (torch.arange(nF)[None] // 11).repeat(B, 1).to(torch.int32).to(dev)
+        doc = (torch.arange(nF)[None] // 11).repeat(B, 1)
+        if use_doc == "ext_nc":
+            doc = doc % 3                      # ids 0,1,2,0,1,2,...: every id re-opens (not contiguous runs)
+        if B > 1:
+            doc[1] = (torch.arange(nF) // 7)   # different packing per batch row
+        doc = doc.to(torch.int32).to(dev)
     return q, k, v, doc
 
 
@@ -85,6 +103,17 @@ def _run(case, impl, want_bwd):
     dout = torch.randn(B, Lq, H * dh, generator=g).to(bf16).to(dev)
     o_ref, lse_ref, dq_ref, dk_ref, dv_ref = _reference(q, k, v, mask, dout)
     kw = dict(tokens_per_frame=T, window_frames=W, q_offset=q_offset, causal=causal, doc_id=doc, check=impl == "check")
+    if isinstance(use_doc, str):
+        first, last, breaks = ops.attn_doc_extents(doc)
+        kw["doc_ext"] = (first, last, breaks)
+        d = doc.cpu()
+        for b in range(B):       # the extents kernel against a plain scan
+            ids = d[b].tolist()
+            assert first[b].cpu().tolist() == [ids.index(x) for x in ids]
+            assert last[b].cpu().tolist() == [len(ids) - 1 - ids[::-1].index(x) for x in ids]
+            nb = sum(1 for f in range(1, len(ids)) if ids[f] != ids[f - 1] and ids.index(ids[f]) != f)
+            assert int(breaks[b]) == nb
+        assert (int(breaks[0]) == 0) == (use_doc == "ext")
     o, lse = ops.attn_fwd(q, k, v, **kw)
     torch.cuda.synchronize()
     assert relerr(o, o_ref) <= 1e-2

@@ -94,3 +94,50 @@ def test_gloo_world2_bucket_allreduce():
     out = mgr.dict()
     mp.spawn(_worker, args=(2, 29533, out), nprocs=2, join=True)
     assert out[0] and out[1]
+
+
+def test_zero_grad_set_to_none_is_reattached_and_sinks_overwrite_then_add():
+    """the reference trainers call opt.zero_grad(set_to_none=True) every step (rft_trainer.py:200); the
+    bucket views must be p.grad again at the next begin_step, and a sink's first write of a step overwrites while any
+    later write in the same step (second micro-batch or second backward through the block) adds."""
+    m = Wrapped()
+    b = engine.GradBuckets(m)
+    opt = torch.optim.SGD(m.parameters(), lr=0.1)
+    b.begin_step()
+    views = {id(p): p.grad for p in m.parameters()}
+    opt.zero_grad(set_to_none=True)
+    assert all(p.grad is None for p in m.parameters())
+    b.begin_step()
+    assert all(p.grad is views[id(p)] for p in m.parameters())
+    w = m.transformer.blocks[0].attn.qkv.weight._owl_grad_sink
+    assert w.accumulate is False        # first write of the step
+    assert w.accumulate is True         # the same sink written again in the same step
+    b.begin_step()
+    assert w.accumulate is False
+    bias = m.transformer.blocks[0].attn.qkv.bias._owl_grad_sink
+    assert bias.accumulate is True      # column sums always add into buffers zeroed by begin_step
+    cs = m.transformer._stage.cond_sink
+    assert cs.acc_rows(0) is False and cs.acc_rows(0) is True and cs.acc_rows(384) is False
+    b.detach()
+
+
+def test_backwards_per_step_defers_the_reduce_and_rejects_extra_passes():
+    m = Wrapped()
+    b = engine.GradBuckets(m, backwards_per_step=2)
+    sent = []
+    b._reduce = lambda flat: sent.append(flat.data_ptr())
+    b.begin_step()
+    blk = m.transformer.blocks[1]
+    blk._stage.after_backward()
+    assert sent == []                                   # first of two expected backward passes: nothing handed over
+    blk._stage.after_backward()
+    assert sent == [b.flats[1].data_ptr()]
+    try:
+        blk._stage.after_backward()
+        raise AssertionError("third backward pass must be rejected")
+    except RuntimeError as e:
+        assert "backwards_per_step" in str(e)
+    b.begin_step()                                      # counters reset per step
+    blk._stage.after_backward()
+    assert len(sent) == 1
+    b.detach()

@@ -124,3 +124,95 @@ def test_full_model_step_buckets_match_autograd(use_graph):
         assert relerr(p.grad, ref[k]) <= 1e-3, k
         assert relerr(p.grad, fx["grads"][k]) <= 2e-2, k     # and the reference model's own gradients
     buckets.detach()
+
+
+def test_multi_step_optimizer_with_zero_grad_set_to_none():
+    """optimizer.step() + zero_grad(set_to_none=True) with buckets, several steps: every parameter keeps
+    receiving its gradient (p.grad is re-attached to the bucket view) and the trajectory matches plain autograd."""
+    import copy
+    from owl_audio_exps_b200 import engine
+    fx = load_golden("audio_T1")
+    model = _model(fx)
+    ref_model = copy.deepcopy(model)
+    inputs = [fx["x"].to(DEV), fx["cond"].to(DEV), fx["dy"].to(DEV)]
+    opt_ref = torch.optim.SGD(ref_model.parameters(), lr=1e-2)
+    for _ in range(3):
+        opt_ref.zero_grad(set_to_none=True)
+        _loss(ref_model, *inputs).backward()
+        opt_ref.step()
+    buckets = engine.GradBuckets(model)
+    opt = torch.optim.SGD(model.parameters(), lr=1e-2)
+    p0 = {k: p.detach().clone() for k, p in model.named_parameters()}
+    for _ in range(3):
+        buckets.begin_step()
+        _loss(model, *inputs).backward()
+        buckets.finish_step()
+        assert all(p.grad is not None for p in model.parameters())
+        opt.step()
+        opt.zero_grad(set_to_none=True)      # what the reference trainers do (rft_trainer.py:200)
+    torch.cuda.synchronize()
+    ref = dict(ref_model.named_parameters())
+    for k, p in model.named_parameters():
+        assert not torch.equal(p, p0[k]), k                     # nothing was silently skipped by the optimizer
+        assert relerr(p - p0[k], ref[k] - p0[k]) <= 2e-2, k     # same update as plain autograd
+    buckets.detach()
+
+
+def test_two_model_calls_in_one_loss_accumulate_into_the_buckets():
+    """a loss that runs the stack twice (self-forcing / distillation trainers) with backwards_per_step=2:
+    the second backward through a block adds to the first instead of overwriting it."""
+    from owl_audio_exps_b200 import engine
+    fx = load_golden("av_T5_ortho")
+    model = _model(fx)
+    inputs = [fx["x"].to(DEV), fx["cond"].to(DEV), fx["dy"].to(DEV)]
+
+    def loss2(m, x, cond, dy):
+        return _loss(m, x, cond, dy) + 0.5 * _loss(m, x * 0.5, cond, dy)
+    loss2(model, *inputs).backward()
+    ref = {k: p.grad.clone() for k, p in model.named_parameters()}
+    model.zero_grad()
+    buckets = engine.GradBuckets(model, backwards_per_step=2)
+    for _ in range(2):
+        buckets.begin_step()
+        loss2(model, *inputs).backward()
+        buckets.finish_step()
+    torch.cuda.synchronize()
+    for k, p in model.named_parameters():
+        assert relerr(p.grad, ref[k]) <= 2e-3, k
+    buckets.detach()
+    buckets = engine.GradBuckets(model)   # default: one backward per block per micro-batch -> the second is refused
+    buckets.begin_step()
+    with pytest.raises(RuntimeError, match="backwards_per_step"):
+        loss2(model, *inputs).backward()
+    buckets.detach()
+
+
+def test_weight_stage_sees_data_mutations():
+    """`p.data.<op>_()` (ema_pytorch's update path) does not bump `_version`; outside frozen_weights() every
+    forward re-stages, inside it operands are cached until restage() / the next outermost frozen_weights()."""
+    from owl_audio_exps_b200 import functional as OF
+    fx = load_golden("audio_T1")
+    model = _model(fx)
+    x, cond = fx["x"].to(DEV), fx["cond"].to(DEV)
+    with torch.no_grad():
+        y0 = model(x, cond).clone()
+        w = model.blocks[0].mlp.fc2.weight
+        v0 = w._version
+        w.data.mul_(0.0)                       # EMA-style in-place update through .data
+        assert w._version == v0
+        y1 = model(x, cond).clone()
+        assert not torch.equal(y0, y1)         # picked up without any version bump
+        with OF.frozen_weights():
+            ya = model(x, cond).clone()
+            assert torch.equal(ya, y1)
+            model.blocks[0].attn.out.weight.data.mul_(0.0)
+            yb = model(x, cond).clone()
+            assert torch.equal(yb, ya)         # declared frozen: cached operands are reused ...
+            OF.restage()
+            yc = model(x, cond).clone()
+            assert not torch.equal(yc, ya)     # ... until restage()
+        with OF.frozen_weights():              # entering the outermost context re-stages as well
+            model.blocks[1].mlp.fc2.weight.data.mul_(0.0)
+        with OF.frozen_weights():
+            yd = model(x, cond).clone()
+        assert not torch.equal(yd, yc)

@@ -61,8 +61,11 @@ def test_kv_rollout_matches_reference():
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
-def test_rope_tables_match_reference_construction(name):
-    """The package's own table builders (nn/rope.py) against the tables the reference code built."""
+def test_rope_tables_match_reference_code_over_restated_package(name):
+    """nn/rope.py's table builders against the tables the REFERENCE CODE (rope.py:57-179) built on top of the generator's
+    restatement of the absent third-party `rotary_embedding_torch` (tests/golden/make_golden.py install_stubs).  This pins
+    the in-repo arithmetic (axis layout, audio-token slot, subsampling, MotionRoPE / Audio1DRoPE closed forms); it does
+    NOT pin the third-party package itself: PARITY UNPINNED there (nn/rope.py header)."""
     from owl_audio_exps_b200.nn.rope import get_rope_cls
     fx = load_golden(name)
     cfg = cfg_of(fx)
@@ -71,6 +74,40 @@ def test_rope_tables_match_reference_construction(name):
     assert r.cos.shape == cos.shape and r.cos.dtype == torch.float32
     assert (r.cos - cos).abs().max().item() < 1e-6
     assert (r.sin - sin).abs().max().item() < 1e-6
+
+
+def test_ortho_rope_axial_variants_and_real_package_hook():
+    """The two release behaviours of get_axial_freqs that nn/rope.py can restate differ only on the leading (time,
+    height) axes, and an importable `rotary_embedding_torch` is used verbatim for the table (init-time plumbing)."""
+    import sys, types
+    from owl_audio_exps_b200.nn import rope as R
+    cfg = types.SimpleNamespace(d_model=128, n_heads=2, n_frames=6, sample_size=3, has_audio=True)
+    a = R.OrthoRoPE(cfg)
+    cfg2 = types.SimpleNamespace(**{**vars(cfg), "rope_axial_variant": "last_two_linspace"})
+    b = R.OrthoRoPE(cfg2)
+    assert a.cos.shape == b.cos.shape == (6 * 10, 32)
+    assert (a.cos - b.cos).abs().max() > 1e-3           # the variants are distinguishable ...
+    dh4 = (cfg.d_model // cfg.n_heads) // 4             # ... but agree on the last-two-axes features (width, pad)
+    w0 = 2 * (2 * (dh4 // 2)) // 2                      # features [w0:] after the ::2 subsampling: width + pad axes
+    assert torch.equal(a.cos[:, w0:], b.cos[:, w0:])
+
+    class Fake:                                         # an "installed" package: whatever it returns is used
+        def __init__(self, dim, freqs_for, max_freq):
+            self.n = 2 * (dim // 2)
+        def get_axial_freqs(self, *dims, offsets=None):
+            return torch.full((*dims, 4 * self.n), 0.25)
+    mod = types.ModuleType("rotary_embedding_torch")
+    mod.RotaryEmbedding = Fake
+    old = sys.modules.get("rotary_embedding_torch")
+    sys.modules["rotary_embedding_torch"] = mod
+    try:
+        c = R.OrthoRoPE(cfg)
+    finally:
+        if old is None:
+            del sys.modules["rotary_embedding_torch"]
+        else:
+            sys.modules["rotary_embedding_torch"] = old
+    assert torch.allclose(c.cos, torch.full_like(c.cos, float(torch.cos(torch.tensor(0.25)))))
 
 
 def test_frame_mask_matches_package_descriptor():
