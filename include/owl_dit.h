@@ -171,9 +171,26 @@ int owl_gate_fwd(const void* x, const void* c, int64_t ld_c, const void* res, vo
 int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, void* dy, void* dc, int64_t ld_dc,
                  float* dbias, int dbias_accumulate, int64_t M, int64_t d, int64_t T, owl_stream_t stream);
 
+/* adaLN backward fused with the gate backward of the branch that produced the normalised tensor, one pass
+ * (block structure attn.py:130-143: x_in = x_prev + c * y, h = rms_norm(x_in) * (1 + a) + b):
+ *   dx = adaLN-backward(dh, x_in, a, rstd) + dres;  dy = dx * c[frame];  dc[frame] = sum dx * y;
+ *   dbias (+)= colsum(dy)  (bias gradient of the Linear that produced y; NULL: not wanted).
+ * Same argument meaning as owl_adaln_modulate_bwd followed by owl_gate_bwd(dx, ...); autograd of
+ * modulation.py:20-25 and 41-43.                                                                   */
+int owl_adaln_gate_bwd(const void* dh, const void* x, const void* a, int64_t ld_ab, const float* rstd,
+                       const void* dres, void* dx, void* da, void* db, int64_t ld_dab, const void* y, const void* c,
+                       int64_t ld_c, void* dy, void* dc, int64_t ld_dc, float* dbias, int dbias_accumulate, int64_t M,
+                       int64_t d, int64_t T, owl_stream_t stream);
+
 /* out[n] (+)= sum_m x[m,n]; x bf16 [M, ld], out fp32 [N]           (bias gradients)              */
 int owl_colsum_bf16(const void* x, int64_t ld, float* out, int accumulate, int64_t M, int64_t N,
                     owl_stream_t stream);
+
+/* Up to 4 column sums in one launch: outs[i][n] += sum_m xs[i][m, n] (bf16 [Ms[i], Ns[i]], row stride lds[i]).
+ * The four bias gradients of one DiT block (autograd of the nn.Linear biases, attn.py:72-73, mlp.py:10-11);
+ * outputs are added to, the caller zeroes them.                                                        */
+int owl_colsum_bf16_multi(const void* const* xs, const int64_t* lds, const int64_t* Ms, const int64_t* Ns,
+                          float* const* outs, int count, owl_stream_t stream);
 
 /* QK-RMSNorm + RoPE + head split                                    (attn.py:83-89, rope.py:43-51)
  *   qkv: bf16 [B, L, 3, H, dh] (the qkv Linear output)

@@ -59,6 +59,9 @@ SIGNATURES = {
     "owl_adaln_modulate_bwd": ([vp, vp, vp, i64, vp, vp, vp, vp, vp, i64, i64, i64, i64, vp], C.c_int),
     "owl_gate_fwd": ([vp, vp, i64, vp, vp, i64, i64, i64, vp], C.c_int),
     "owl_gate_bwd": ([vp, vp, vp, i64, vp, vp, i64, vp, C.c_int, i64, i64, i64, vp], C.c_int),
+    "owl_adaln_gate_bwd": ([vp, vp, vp, i64, vp, vp, vp, vp, vp, i64, vp, vp, i64, vp, vp, i64, vp, C.c_int,
+                            i64, i64, i64, vp], C.c_int),
+    "owl_colsum_bf16_multi": ([vp, vp, vp, vp, vp, C.c_int, vp], C.c_int),
     "owl_colsum_bf16": ([vp, i64, vp, C.c_int, i64, i64, vp], C.c_int),
     "owl_qk_norm_rope_fwd": ([vp, vp, vp, i64, vp, i64, i64, vp, i64, i64, vp, i64, i64, vp, vp,
                               i64, i64, i64, i64, f32, vp], C.c_int),

@@ -1,0 +1,485 @@
+// Attention backward, second generation (dh = 64, more than one tile): ONE persistent kernel per call instead of a dq pass
+// plus a dk/dv pass, so S and dP are computed once per (query tile, key tile) pair - 5 MMAs per pair instead of 7 - and
+// neither P nor dS makes a round trip through shared memory on its way back to the tensor core.
+//
+//   A CTA owns one 128-key tile (K_j, V_j resident in shared memory, dK_j / dV_j accumulating in TMEM) and walks the query
+//   tiles i that can see it (causal / window / document extents, heaviest key tiles first).  Everything is computed
+//   TRANSPOSED - thread = key row - so that P^T and dS^T land in tensor memory in the layout the A operand of the dV / dK
+//   MMAs wants:
+//     MMA 1   S^T  = K_j Q_i^T           dP^T = V_j dO_i^T                     (SS, 128 x 128 x 64 each)
+//     softmax P^T  = exp2(S^T c - lse_i) dS^T = P^T (dP^T - delta_i) / sqrt(dh)   -> bf16 over S^T / dP^T in TMEM,
+//                                                                              dS^T also into shared memory
+//     MMA 2   dV_j += P^T dO_i           dK_j += dS^T Q_i                      (A operand from TMEM)
+//             dQ_i(partial) = dS K_j                                           (A = the shared-memory dS^T read MN-major)
+//     drain   dQ partial: TMEM -> fp32 staging -> TMA reduce-add into the fp32 dq accumulator (owl_attn_bwd's dq_acc)
+//
+//   512 threads = 4 warpgroups, every warp touching TMEM owns lanes 32*(warp % 4):
+//     WG0 / WG1  softmax over query columns [0,64) / [64,128) of the pair (thread = key row), epilogue dV / dK
+//     WG2        warp 8 TMA producer, warp 9 MMA issuer, warps 10 / 11 load lse / delta of the query tile into shared memory
+//     WG3        dQ drain
+//   TMEM: S^T [0,128)  dP^T [128,256)  dV [256,320)  dK [320,384)  dQ partial, double-buffered [384,448) [448,512).
+//
+// Replaces the autograd of flex_attention (owl_wms/nn/attn.py:106-109 under rft_trainer.py:189) for dh = 64 training /
+// prefill shapes; dh = 128 and single-tile problems stay on attn_bwd.cu.
+#include <cuda_bf16.h>
+#include <math.h>
+#include <stdlib.h>
+
+#include "attn_common.cuh"
+#include "host_common.h"
+
+namespace owl {
+
+int fill_mask_params(const owl_attn_mask* mask, MaskParams* m);  // attn.cu
+
+struct AttnBwd2Params {
+  int B, H, Lq, Lk, n_qtiles, n_ktiles, total_items, Lq_pad;
+  float scale_log2, scale;
+  const float* lse;
+  const float* delta;
+  bf16 *dk, *dv;
+  long long dk_sb, dk_sh, dv_sb, dv_sh;
+  MaskParams m;
+};
+
+namespace bwd2 {
+static constexpr int DH = 64;
+static constexpr int kThreads = 512;
+static constexpr int kStages = 3;                        // {Q_i, dO_i, lse_i, delta_i} in flight
+static constexpr int kTileBytes = kTile * DH * 2;        // 16 KB
+static constexpr int kOffK = 0;
+static constexpr int kOffV = kTileBytes;
+static constexpr int kOffRing = 2 * kTileBytes;          // per stage: Q then dO
+static constexpr int kStageBytes = 2 * kTileBytes;
+static constexpr int kOffDS = kOffRing + kStages * kStageBytes;   // dS^T [128 keys][128 q] bf16, two swizzled panels
+static constexpr int kOffDQ = kOffDS + kTile * kTile * 2;         // fp32 staging [128 q][64] as two 128B-swizzled panels
+static constexpr int kOffStat = kOffDQ + kTile * DH * 4;          // per stage: lse2[128], delta[128] fp32
+static constexpr int kOffBar = kOffStat + kStages * 1024;
+static constexpr int kSmemBytes = kOffBar + 512;
+static constexpr uint32_t kColST = 0, kColDPT = 128, kColDV = 256, kColDK = 320, kColDQ = 384;
+}  // namespace bwd2
+
+struct Bwd2Item {
+  int b, h, j0, t0, n_q;
+};
+
+__device__ __forceinline__ Bwd2Item bwd2_item(const AttnBwd2Params& p, int w) {
+  Bwd2Item it;
+  const int bh = w / p.n_ktiles;
+  const int kt = w % p.n_ktiles;  // early key tiles are seen by the most queries under the causal mask: heaviest first
+  it.b = bh / p.H;
+  it.h = bh % p.H;
+  it.j0 = kt * kTile;
+  int t1;
+  q_tile_range(p.m, it.j0, min(it.j0 + kTile, p.Lk) - 1, p.Lq, it.t0, t1, it.b);
+  it.n_q = t1 - it.t0;
+  return it;
+}
+
+__global__ void __launch_bounds__(bwd2::kThreads, 1)
+attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
+                 const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                 const __grid_constant__ CUtensorMap tmDQ, const AttnBwd2Params p) {
+  using namespace bwd2;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* kv_full = bars;                 // TMA -> MMA
+  uint64_t* kv_empty = bars + 1;            // MMA -> TMA (every MMA of the item has read K_j / V_j)
+  uint64_t* qdo_full = bars + 2;            // [kStages] TMA -> MMA
+  uint64_t* qdo_empty = bars + 2 + kStages; // [kStages] MMA -> TMA and the lse / delta loaders
+  uint64_t* stat_full = bars + 2 + 2 * kStages;  // [kStages] lse / delta loaders -> softmax (2 arrivals)
+  uint64_t* sdp_full = bars + 2 + 3 * kStages;   // MMA -> softmax
+  uint64_t* pds_full = sdp_full + 1;        // softmax -> MMA (256 arrivals)
+  uint64_t* dq_full = sdp_full + 2;         // [2] MMA -> drain
+  uint64_t* dq_free = sdp_full + 4;         // [2] drain -> MMA (128 arrivals)
+  uint64_t* acc_done = sdp_full + 6;        // MMA -> softmax epilogue (dV / dK complete)
+  uint64_t* acc_free = sdp_full + 7;        // softmax epilogue -> MMA (256 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    if (smem_u32(smem) & 1023) __trap();
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmDO); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmDQ);
+    mbar_init(kv_full, 1);
+    mbar_init(kv_empty, 1);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&qdo_full[s], 1);
+      mbar_init(&qdo_empty[s], 1);
+      mbar_init(&stat_full[s], 2);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(pds_full, 256);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&dq_full[s], 1);
+      mbar_init(&dq_free[s], 128);
+    }
+    mbar_init(acc_done, 1);
+    mbar_init(acc_free, 256);
+    fence_barrier_init();
+  }
+  if (warp == 9) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  pdl_launch();
+
+  if (warp == 8) {
+    // ---------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      uint32_t item_n = 0, ring_n = 0;
+      for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
+        const Bwd2Item it = bwd2_item(p, w);
+        if (it.n_q <= 0) continue;
+        mbar_wait(kv_empty, (item_n & 1) ^ 1);
+        ++item_n;
+        mbar_arrive_expect_tx(kv_full, 2 * kTileBytes);
+        tma_load_4d(smem + kOffK, &tmK, kv_full, 0, it.j0, it.h, it.b);
+        tma_load_4d(smem + kOffV, &tmV, kv_full, 0, it.j0, it.h, it.b);
+        for (int q = 0; q < it.n_q; ++q) {
+          const uint32_t s = ring_n % kStages;
+          mbar_wait(&qdo_empty[s], ((ring_n / kStages) & 1) ^ 1);
+          ++ring_n;
+          mbar_arrive_expect_tx(&qdo_full[s], kStageBytes);
+          const int i0 = (it.t0 + q) * kTile;
+          tma_load_4d(smem + kOffRing + s * kStageBytes, &tmQ, &qdo_full[s], 0, i0, it.h, it.b);
+          tma_load_4d(smem + kOffRing + s * kStageBytes + kTileBytes, &tmDO, &qdo_full[s], 0, i0, it.h, it.b);
+        }
+      }
+    }
+  } else if (warp == 10 || warp == 11) {
+    // ---------------------------------------------------------------- lse (warp 10) / delta (warp 11) of the query tile
+    const bool is_lse = warp == 10;
+    const float* src = is_lse ? p.lse : p.delta;
+    uint32_t ring_n = 0;
+    for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
+      const Bwd2Item it = bwd2_item(p, w);
+      if (it.n_q <= 0) continue;
+      const float* row = src + (static_cast<long long>(it.b) * p.H + it.h) * p.Lq;
+      for (int q = 0; q < it.n_q; ++q) {
+        const uint32_t s = ring_n % kStages;
+        mbar_wait(&qdo_empty[s], ((ring_n / kStages) & 1) ^ 1);
+        ++ring_n;
+        const int i0 = (it.t0 + q) * kTile;
+        float* dst = reinterpret_cast<float*>(smem + kOffStat + s * 1024) + (is_lse ? 0 : 128);
+        float v[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = i0 + lane * 4 + e;
+          float x = i < p.Lq ? __ldg(row + i) : (is_lse ? -INFINITY : 0.f);
+          // rows with nothing visible (lse = -inf) and padding rows: exponent offset +inf -> P = 0
+          if (is_lse) x = x == -INFINITY ? INFINITY : x * 1.4426950408889634f;
+          v[e] = x;
+        }
+        *reinterpret_cast<float4*>(dst + lane * 4) = make_float4(v[0], v[1], v[2], v[3]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&stat_full[s]);
+      }
+    }
+  } else if (warp == 9) {
+    // ---------------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);   // S^T, dP^T
+      constexpr uint32_t idesc_acc = make_idesc_bf16(kTile, DH, false, true);     // dV, dK: A from TMEM, B MN-major
+      constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, true, true);       // dQ: A = dS^T tile read MN-major
+      const uint32_t sK = smem_u32(smem + kOffK), sV = smem_u32(smem + kOffV), sDS = smem_u32(smem + kOffDS);
+      const uint32_t tST = tmem_base + kColST, tDPT = tmem_base + kColDPT;
+      const uint32_t tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
+      uint32_t item_n = 0, ring_n = 0, pair_n = 0;
+      for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
+        const Bwd2Item it = bwd2_item(p, w);
+        if (it.n_q <= 0) continue;
+        mbar_wait(kv_full, item_n & 1);
+        for (int q = 0; q < it.n_q; ++q) {
+          const uint32_t s = ring_n % kStages;
+          mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
+          ++ring_n;
+          const uint32_t sQ = smem_u32(smem + kOffRing + s * kStageBytes), sDO = sQ + kTileBytes;
+          tc_fence_after();
+          // MMA 1 (in issue order behind MMA 2 of the previous pair, which still reads P^T / dS^T from these columns)
+#pragma unroll
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tST, desc_kmajor(sK, k), desc_kmajor(sQ, k), idesc_s, k > 0);
+#pragma unroll
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDPT, desc_kmajor(sV, k), desc_kmajor(sDO, k), idesc_s, k > 0);
+          umma_commit(sdp_full);
+          // MMA 2
+          mbar_wait(pds_full, pair_n & 1);
+          if (q == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);       // the previous item's epilogue has read dV / dK
+          const uint32_t buf = pair_n & 1;
+          mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);       // the drain has read this dQ buffer's previous content
+          tc_fence_after();
+          const uint32_t acc = q > 0 ? 1u : 0u;
+#pragma unroll
+          for (int k = 0; k < kTile / 16; ++k) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
+            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+            umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+          }
+#pragma unroll
+          for (int k = 0; k < kTile / 16; ++k) {
+            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+            umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+          }
+          const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
+#pragma unroll
+          for (int k = 0; k < kTile / 16; ++k)
+            umma_bf16_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+          umma_commit(&qdo_empty[s]);
+          umma_commit(&dq_full[buf]);
+          ++pair_n;
+        }
+        umma_commit(acc_done);
+        umma_commit(kv_empty);
+        ++item_n;
+      }
+    }
+  } else if (warp >= 12) {
+    // ---------------------------------------------------------------- WG3: dQ drain (thread = query row)
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+    const bool leader = threadIdx.x == 12 * 32;
+    uint8_t* stag = smem + kOffDQ;
+    uint32_t pair_n = 0;
+    for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
+      const Bwd2Item it = bwd2_item(p, w);
+      if (it.n_q <= 0) continue;
+      const long long row_base = (static_cast<long long>(it.b) * p.H + it.h) * p.Lq_pad;
+      for (int q = 0; q < it.n_q; ++q) {
+        const uint32_t buf = pair_n & 1;
+        mbar_wait(&dq_full[buf], (pair_n >> 1) & 1);
+        ++pair_n;
+        tc_fence_after();
+        uint32_t v[2][32];
+        tmem_ld_x32(tmem_base + kColDQ + buf * DH + lane_addr, v[0]);
+        tmem_ld_x32(tmem_base + kColDQ + buf * DH + lane_addr + 32, v[1]);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(&dq_free[buf]);
+        if (leader) tma_store_wait_read0();   // the previous reduce has finished reading the staging panels
+        named_bar_sync(1, 128);
+#pragma unroll
+        for (int pn = 0; pn < 2; ++pn)
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<uint4*>(stag + pn * 16384 + r * 128 + ((c ^ (r & 7)) << 4)) =
+                make_uint4(v[pn][4 * c], v[pn][4 * c + 1], v[pn][4 * c + 2], v[pn][4 * c + 3]);
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (leader) {
+          const int row0 = static_cast<int>(row_base + static_cast<long long>(it.t0 + q) * kTile);
+          tma_reduce_add_2d(&tmDQ, stag, 0, row0);
+          tma_reduce_add_2d(&tmDQ, stag + 16384, 32, row0);
+          tma_store_commit();
+        }
+      }
+    }
+    if (leader) tma_store_wait_all0();
+  } else {
+    // ---------------------------------------------------------------- WG0 / WG1: softmax, thread = key row
+    const int hf = warp >> 2;                 // query columns [64 hf, 64 hf + 64) of every pair
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
+    const uint32_t tST = tmem_base + kColST + lane_addr + hf * 64;
+    const uint32_t tDPT = tmem_base + kColDPT + lane_addr + hf * 64;
+    uint8_t* sDS = smem + kOffDS;
+    uint32_t item_n = 0, ring_n = 0, pair_n = 0;
+    for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
+      const Bwd2Item it = bwd2_item(p, w);
+      const int j = it.j0 + r;
+      bf16* dst = (hf == 0 ? p.dv + it.b * p.dv_sb + it.h * p.dv_sh : p.dk + it.b * p.dk_sb + it.h * p.dk_sh) +
+                  static_cast<long long>(j) * DH;
+      if (it.n_q <= 0) {  // no query sees these keys: zero gradients
+        if (j < p.Lk) {
+#pragma unroll
+          for (int c = 0; c < DH / 8; ++c) *reinterpret_cast<uint4*>(dst + c * 8) = make_uint4(0, 0, 0, 0);
+        }
+        continue;
+      }
+      int ilo, ihi;
+      bool doc_test;
+      key_q_range(p.m, it.b, min(j, p.Lk - 1), p.Lq, p.Lk, ilo, ihi, doc_test);
+      if (j >= p.Lk) ihi = ilo;
+      const int* doc_row = doc_test ? p.m.doc + it.b * p.m.doc_ld : nullptr;
+      const int dkey = doc_row != nullptr ? __ldg(doc_row + min(j, p.Lk - 1) / p.m.T) : 0;
+      for (int q = 0; q < it.n_q; ++q) {
+        const uint32_t s = ring_n % kStages;
+        const int i0 = (it.t0 + q) * kTile + hf * 64;   // first query column of this warpgroup's half
+        mbar_wait(&stat_full[s], (ring_n / kStages) & 1);
+        ++ring_n;
+        const float4* st_lse = reinterpret_cast<const float4*>(smem + kOffStat + s * 1024) + hf * 16;
+        const float4* st_del = st_lse + 32;
+        mbar_wait(sdp_full, pair_n & 1);
+        ++pair_n;
+        tc_fence_after();
+        const bool full = doc_row == nullptr && ilo <= i0 && i0 + 64 <= ihi;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t rs[32], rp[32], pk[16], dk[16];
+          tmem_ld_x32(tST + c * 32, rs);
+          tmem_ld_x32(tDPT + c * 32, rp);
+          uint32_t valid = 0xffffffffu;
+          if (!full) {
+            const int qc = i0 + c * 32;
+            int a = ilo - qc, z = ihi - qc;
+            a = a < 0 ? 0 : a;
+            z = z > 32 ? 32 : z;
+            valid = z <= a ? 0u : ((z >= 32 ? 0xffffffffu : ((1u << z) - 1u)) & ~((1u << a) - 1u));
+            if (doc_row != nullptr) {
+              for (int e = a; e < z; ++e)
+                if (__ldg(doc_row + (qc + e + p.m.q_offset) / p.m.T) != dkey) valid &= ~(1u << e);
+            }
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int e4 = 0; e4 < 8; ++e4) {
+            const float4 l4 = st_lse[c * 8 + e4], d4 = st_del[c * 8 + e4];
+            const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, dl[4] = {d4.x, d4.y, d4.z, d4.w};
+            float pv[4], dv[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int idx = e4 * 4 + e;
+              float pe = exp2f(fmaf(__uint_as_float(rs[idx]), p.scale_log2, -ls[e]));
+              if (!full && !((valid >> idx) & 1u)) pe = 0.f;
+              pv[e] = pe;
+              dv[e] = pe * (__uint_as_float(rp[idx]) - dl[e]) * p.scale;
+            }
+            pk[e4 * 2] = pack_bf16(pv[0], pv[1]);
+            pk[e4 * 2 + 1] = pack_bf16(pv[2], pv[3]);
+            dk[e4 * 2] = pack_bf16(dv[0], dv[1]);
+            dk[e4 * 2 + 1] = pack_bf16(dv[2], dv[3]);
+          }
+          // P^T / dS^T over the columns this thread has already read (first half of its own 64-column region)
+          tmem_st_x16(tST + c * 16, pk);
+          tmem_st_x16(tDPT + c * 16, dk);
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            *reinterpret_cast<uint4*>(sDS + tile_chunk_offset(r, hf * 8 + c * 4 + g)) =
+                make_uint4(dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        fence_proxy_async_smem();
+        mbar_arrive(pds_full);
+      }
+      // epilogue: WG0 stores dV_j, WG1 stores dK_j
+      mbar_wait(acc_done, item_n & 1);
+      ++item_n;
+      tc_fence_after();
+      const uint32_t tAcc = tmem_base + (hf == 0 ? kColDV : kColDK) + lane_addr;
+#pragma unroll
+      for (int c = 0; c < DH / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_x32(tAcc + c * 32, o);
+        tmem_ld_wait();
+        if (j < p.Lk) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 v;
+            v.x = pack_bf16(__uint_as_float(o[8 * g + 0]), __uint_as_float(o[8 * g + 1]));
+            v.y = pack_bf16(__uint_as_float(o[8 * g + 2]), __uint_as_float(o[8 * g + 3]));
+            v.z = pack_bf16(__uint_as_float(o[8 * g + 4]), __uint_as_float(o[8 * g + 5]));
+            v.w = pack_bf16(__uint_as_float(o[8 * g + 6]), __uint_as_float(o[8 * g + 7]));
+            *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) = v;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(acc_free);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// fp32 dq accumulator [B*H, Lq_pad, 64] -> bf16 dq [B, H, Lq, 64] (strides in elements)
+__global__ void __launch_bounds__(256)
+attn_dq_convert_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long dq_sb, long long dq_sh, int H,
+                       int Lq, int Lq_pad, long long total8) {
+  pdl_prologue();
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total8; t += stride) {
+    const int c = static_cast<int>(t & 7);            // 8-element group inside the 64-wide row
+    const long long row = t >> 3;                     // (b*H + h) * Lq + i
+    const int i = static_cast<int>(row % Lq);
+    const long long bh = row / Lq;
+    const float4* src = reinterpret_cast<const float4*>(acc + (bh * Lq_pad + i) * 64 + c * 8);
+    const float4 a = __ldg(src), b = __ldg(src + 1);
+    uint4 o;
+    o.x = pack_bf16(a.x, a.y); o.y = pack_bf16(a.z, a.w); o.z = pack_bf16(b.x, b.y); o.w = pack_bf16(b.z, b.w);
+    *reinterpret_cast<uint4*>(dq + (bh / H) * dq_sb + (bh % H) * dq_sh + static_cast<long long>(i) * 64 + c * 8) = o;
+  }
+}
+
+// called by owl_attn_bwd (attn_bwd.cu) after the delta pre-pass, for dh = 64 and more than one tile
+int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void* q, int64_t q_sb, int64_t q_sh,
+                       const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb, int64_t v_sh,
+                       const float* lse, const float* delta, float* dq_acc, void* dq, int64_t dq_sb, int64_t dq_sh,
+                       void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh, int64_t B,
+                       int64_t H, int64_t Lq, int64_t Lk, const owl_attn_mask* mask, cudaStream_t s) {
+  using namespace bwd2;
+  if (dq_acc == nullptr) return OWL_ERR_BAD_ARG;
+  AttnBwd2Params p{};
+  int rc = fill_mask_params(mask, &p.m);
+  if (rc != OWL_OK) return rc;
+  p.B = static_cast<int>(B); p.H = static_cast<int>(H); p.Lq = static_cast<int>(Lq); p.Lk = static_cast<int>(Lk);
+  p.n_qtiles = static_cast<int>((Lq + kTile - 1) / kTile);
+  p.n_ktiles = static_cast<int>((Lk + kTile - 1) / kTile);
+  p.Lq_pad = p.n_qtiles * kTile;
+  const long long total = B * H * static_cast<long long>(p.n_ktiles);
+  const long long acc_rows = B * H * static_cast<long long>(p.Lq_pad);
+  if (total > INT32_MAX || acc_rows > INT32_MAX) return OWL_ERR_UNSUPPORTED;
+  p.total_items = static_cast<int>(total);
+  p.scale = 1.0f / sqrtf(static_cast<float>(DH));
+  p.scale_log2 = 1.4426950408889634f * p.scale;
+  p.lse = lse; p.delta = delta;
+  p.dk = static_cast<bf16*>(dk); p.dv = static_cast<bf16*>(dv);
+  p.dk_sb = dk_sb; p.dk_sh = dk_sh; p.dv_sb = dv_sb; p.dv_sh = dv_sh;
+
+  CUtensorMap tmQ, tmDO, tmK, tmV, tmDQ;
+  if ((rc = make_tmap_4d_bf16(&tmQ, q, DH, Lq, H, B, DH, q_sh, q_sb, 64, kTile)) != OWL_OK) return rc;
+  if ((rc = make_tmap_4d_bf16(&tmDO, dout, DH, Lq, H, B, o_sl, DH, o_sb, 64, kTile)) != OWL_OK) return rc;
+  if ((rc = make_tmap_4d_bf16(&tmK, k, DH, Lk, H, B, DH, k_sh, k_sb, 64, kTile)) != OWL_OK) return rc;
+  if ((rc = make_tmap_4d_bf16(&tmV, v, DH, Lk, H, B, DH, v_sh, v_sb, 64, kTile)) != OWL_OK) return rc;
+  if ((rc = make_tmap_2d_f32(&tmDQ, dq_acc, static_cast<uint64_t>(acc_rows), DH, DH, 32, kTile)) != OWL_OK) return rc;
+
+  static PerDeviceOnce once;
+  rc = once.run([] {
+    return static_cast<int>(
+        cudaFuncSetAttribute(attn_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  });
+  if (rc != OWL_OK) return rc;
+  cudaError_t e = cudaMemsetAsync(dq_acc, 0, static_cast<size_t>(acc_rows) * DH * sizeof(float), s);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  LaunchOpts lo;
+  lo.pdl = false;  // follows a memset node
+  const int grid = min(p.total_items, sm_count());
+  e = launch_kx(lo, attn_bwd2_kernel, dim3(static_cast<unsigned>(grid)), dim3(kThreads), kSmemBytes, s, tmQ, tmDO, tmK,
+                tmV, tmDQ, p);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return static_cast<int>(e);
+  }
+  if ((rc = launch_status()) != OWL_OK) return rc;
+  const long long total8 = B * H * Lq * (DH / 8);
+  long long blocks = (total8 + 255) / 256;
+  const long long cap = static_cast<long long>(sm_count()) * 16;
+  if (blocks > cap) blocks = cap;
+  (void)launch_k(attn_dq_convert_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, s,
+                 static_cast<const float*>(dq_acc), static_cast<bf16*>(dq), static_cast<long long>(dq_sb),
+                 static_cast<long long>(dq_sh), p.H, p.Lq, p.Lq_pad, total8);
+  return launch_status();
+}
+
+}  // namespace owl

@@ -124,4 +124,31 @@ __device__ __forceinline__ void q_tile_range(const MaskParams& m, int j0, int j1
   t1 = static_cast<int>((ihi + kTile - 1) / kTile);
 }
 
+// One KEY's visible query range [ilo, ihi) (the transpose of row_range_doc: used by kernels whose threads own key rows),
+// document extent folded in; need_doc_test as in row_range_doc.
+__device__ __forceinline__ void key_q_range(const MaskParams& m, int b, int j, int Lq, int Lk, int& ilo_out, int& ihi_out,
+                                            bool& need_doc_test) {
+  long long ilo = 0, ihi = Lq;
+  const long long fk = j / m.T;
+  if (m.causal) ilo = fk * m.T - m.q_offset;
+  if (m.W > 0) {
+    const long long h = (fk + m.W) * m.T - m.q_offset;
+    if (h < ihi) ihi = h;
+    if (!m.causal) ilo = (fk - m.W + 1) * m.T - m.q_offset;
+  }
+  need_doc_test = m.doc != nullptr;
+  if (m.doc_first != nullptr && j < Lk) {
+    const long long a = static_cast<long long>(m.doc_first[b * m.doc_ld + fk]) * m.T - m.q_offset;
+    const long long z = (static_cast<long long>(m.doc_last[b * m.doc_ld + fk]) + 1) * m.T - m.q_offset;
+    if (a > ilo) ilo = a;
+    if (z < ihi) ihi = z;
+    if (m.doc_breaks[b] == 0) need_doc_test = false;
+  }
+  if (ilo < 0) ilo = 0;
+  if (ihi > Lq) ihi = Lq;
+  if (j >= Lk || ihi < ilo) ihi = ilo;
+  ilo_out = static_cast<int>(ilo);
+  ihi_out = static_cast<int>(ihi);
+}
+
 }  // namespace owl

@@ -265,6 +265,126 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
 }
 
 // ------------------------------------------------------------------------------------------------
+// adaLN backward fused with the gate backward of the branch that produced this norm's input, one pass over the
+// residual-stream gradient (block: x_in = x_prev + c * y;  h = rms_norm(x_in) * (1 + a) + b):
+//   dx   = rstd * (g - xh * mean(g * xh)) + dres        g = dh * (1 + a), xh = x_in * rstd     (as adaln_bwd_row_kernel)
+//   dy   = dx * c[frame]                                the gradient of the branch output y
+//   dc   = dx * y   (T == 1; frames of T > 1 rows are reduced by frame_reduce_kernel afterwards)
+//   dbias[n] += sum_m dy[m, n]                          bias gradient of the Linear that produced y (COLSUM only)
+// Replaces two launches (adaLN backward, gate backward + column sum) and one re-read of dx per branch.
+// ------------------------------------------------------------------------------------------------
+template <int NV, bool COLSUM>
+__global__ void __launch_bounds__(kRowThreads)
+adaln_gate_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, const bf16* __restrict__ a,
+                      int64_t ld_ab, const float* __restrict__ rstd_in, const bf16* __restrict__ dres,
+                      bf16* __restrict__ dx, bf16* __restrict__ da, bf16* __restrict__ db, int64_t ld_dab,
+                      const bf16* __restrict__ y, const bf16* __restrict__ c, int64_t ld_c, bf16* __restrict__ dy,
+                      bf16* __restrict__ dc, int64_t ld_dc, float* __restrict__ dbias, int64_t M, int d, int T) {
+  pdl_prologue();
+  __shared__ float s_col[COLSUM ? NV * 256 : 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t nwarps = (static_cast<int64_t>(gridDim.x) * blockDim.x) >> 5;
+  const bool write_ab = (T == 1) && (da != nullptr);
+  const bool write_dc = (T == 1) && (dc != nullptr);
+  float acc[COLSUM ? NV : 1][8];
+  if (COLSUM) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+  }
+  for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
+    const float rstd = rstd_in[row];
+    const int64_t frow = row / T;
+    uint4 xv[NV], gv[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int col = (i * 32 + lane) * 8;
+      if (col < d) {
+        xv[i] = ldg16(x + row * d + col);
+        gv[i] = ldg16(dh + row * d + col);
+        float fx[8], fg[8];
+        unpack8(xv[i], fx);
+        unpack8(gv[i], fg);
+        if (write_ab) {
+          float t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t[j] = fg[j] * fx[j] * rstd;
+          stg16(da + frow * ld_dab + col, pack8(t));
+          stg16(db + frow * ld_dab + col, gv[i]);
+        }
+        if (a != nullptr) {
+          float fa[8];
+          unpack8(ldg16(a + frow * ld_ab + col), fa);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) fg[j] *= (1.f + fa[j]);
+          gv[i] = pack8(fg);
+          unpack8(gv[i], fg);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += fg[j] * fx[j] * rstd;
+      }
+    }
+    s = warp_sum(s) / static_cast<float>(d);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int col = (i * 32 + lane) * 8;
+      if (col < d) {
+        float fx[8], fg[8], o[8];
+        unpack8(xv[i], fx);
+        unpack8(gv[i], fg);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (fg[j] - fx[j] * rstd * s);
+        if (dres != nullptr) {
+          float fr[8];
+          unpack8(ldg16(dres + row * d + col), fr);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += fr[j];
+        }
+        const uint4 dxp = pack8(o);
+        stg16(dx + row * d + col, dxp);
+        unpack8(dxp, o);  // the gate backward sees the bf16 residual gradient, exactly as the two-kernel path does
+        float fc[8], g[8];
+        unpack8(ldg16(c + frow * ld_c + col), fc);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = o[j] * fc[j];
+        const uint4 dyp = pack8(g);
+        stg16(dy + row * d + col, dyp);
+        if (COLSUM) {
+          unpack8(dyp, g);  // column sum over the bf16 values the next GEMM reads
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[i][j] += g[j];
+        }
+        if (write_dc) {
+          float fy[8];
+          unpack8(ldg16(y + row * d + col), fy);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = o[j] * fy[j];
+          stg16(dc + frow * ld_dc + col, pack8(g));
+        }
+      }
+    }
+  }
+  if (COLSUM) {
+    // the 8 warps of the CTA add their partial column sums into one shared row, then one fp32 atomic per column per CTA
+    for (int w = 0; w < kRowThreads / 32; ++w) {
+      if (warp == w) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int idx = (i * 32 + lane) * 8 + j;
+            s_col[idx] = (w == 0 ? 0.f : s_col[idx]) + acc[i][j];
+          }
+      }
+      __syncthreads();
+    }
+    for (int idx = threadIdx.x; idx < d; idx += kRowThreads) atomicAdd(dbias + idx, s_col[idx]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Per-frame column reductions (T > 1):
 //   out_pq[f, c] = sum_{r in frame f} p[r, c] * q[r, c] * (scale ? scale[r] : 1)
 //   out_p [f, c] = sum_{r in frame f} p[r, c]                       (optional)
@@ -457,6 +577,57 @@ colsum_kernel(const bf16* __restrict__ x, int64_t ld, float* __restrict__ out, i
 #pragma unroll
     for (int r = 0; r < 8; ++r) s += part[r][col];
     atomicAdd(out + blockIdx.x * 256 + col, s);
+  }
+}
+
+// Column sums of up to 4 matrices in ONE launch (the four bias gradients of a DiT block: fc2, fc1, out, qkv).  Segment i owns
+// blocks [blk0[i], blk0[i+1]) laid out as gx[i] column groups (256 columns) x row splits; outputs are ADDED to (the caller
+// zeroes them: engine.GradBuckets zeroes every bias sink once per step).
+struct ColsumSegs {
+  const bf16* x[4];
+  float* out[4];
+  long long ld[4];
+  long long M[4];
+  int N[4];
+  int gx[4];
+  int blk0[5];
+  int count;
+};
+__global__ void __launch_bounds__(256) colsum_multi_kernel(const ColsumSegs s) {
+  pdl_prologue();
+  __shared__ float part[8][256 + 8];
+  int i = 0;
+  while (i + 1 < s.count && static_cast<int>(blockIdx.x) >= s.blk0[i + 1]) ++i;
+  const int local = static_cast<int>(blockIdx.x) - s.blk0[i];
+  const int gx = s.gx[i];
+  const int bx = local % gx, by = local / gx;
+  const int splits = (s.blk0[i + 1] - s.blk0[i]) / gx;
+  const bf16* x = s.x[i];
+  const long long ld = s.ld[i], M = s.M[i];
+  const int N = s.N[i];
+  const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = (bx * 32 + cg) * 8;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (c < N) {
+#pragma unroll 4
+    for (long long r = static_cast<long long>(by) * 8 + rl; r < M; r += static_cast<long long>(splits) * 8) {
+      float f[8];
+      unpack8(ldg16(x + r * ld + c), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[rl][cg * 8 + j] = acc[j];
+  __syncthreads();
+  const int col = threadIdx.x;
+  if (bx * 256 + col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) t += part[r][col];
+    atomicAdd(s.out[i] + bx * 256 + col, t);
   }
 }
 
@@ -790,6 +961,105 @@ int owl_gate_bwd(const void* dx, const void* y, const void* c, int64_t ld_c, voi
     if (rc != OWL_OK) return rc;
   }
   return rc;
+}
+
+int owl_adaln_gate_bwd(const void* dh, const void* x, const void* a, int64_t ld_ab, const float* rstd,
+                       const void* dres, void* dx, void* da, void* db, int64_t ld_dab, const void* y, const void* c,
+                       int64_t ld_c, void* dy, void* dc, int64_t ld_dc, float* dbias, int dbias_accumulate, int64_t M,
+                       int64_t d, int64_t T, owl_stream_t stream) {
+  OWL_REQUIRE(dh && x && rstd && dx && y && c && dy && M > 0 && d > 0 && T > 0 && M % T == 0, OWL_ERR_BAD_ARG);
+  OWL_REQUIRE((da == nullptr) == (db == nullptr), OWL_ERR_BAD_ARG);
+  OWL_REQUIRE(d % 8 == 0 && d <= 4096, OWL_ERR_UNSUPPORTED);
+  OWL_REQUIRE(aligned16(dh) && aligned16(x) && aligned16(a) && aligned16(dres) && aligned16(dx) && aligned16(da) &&
+                  aligned16(db) && aligned16(y) && aligned16(c) && aligned16(dy) && aligned16(dc) &&
+                  (a == nullptr || ld_ab % 8 == 0) && (da == nullptr || ld_dab % 8 == 0) && ld_c % 8 == 0 &&
+                  (dc == nullptr || ld_dc % 8 == 0),
+              OWL_ERR_ALIGN);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // per-lane column-sum accumulators cost 8*NV registers: fused up to d = 2048, a separate column sum beyond
+  const bool colsum = dbias != nullptr && d <= 2048;
+  LaunchOpts o;
+  if (colsum && !dbias_accumulate) {
+    cudaError_t e = cudaMemsetAsync(dbias, 0, static_cast<size_t>(d) * sizeof(float), s);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    o.pdl = false;  // follows a memset node
+  }
+  // with the column sum every CTA ends in d atomics: two CTAs per SM keep that below the row traffic
+  int grid = row_grid(M);
+  if (colsum && grid > 2 * sm_count()) grid = 2 * sm_count();
+#define OWL_AGB_ARGS                                                                                                  \
+  static_cast<const bf16*>(dh), static_cast<const bf16*>(x), static_cast<const bf16*>(a), ld_ab, rstd,                \
+      static_cast<const bf16*>(dres), static_cast<bf16*>(dx), static_cast<bf16*>(da), static_cast<bf16*>(db), ld_dab, \
+      static_cast<const bf16*>(y), static_cast<const bf16*>(c), ld_c, static_cast<bf16*>(dy), static_cast<bf16*>(dc), \
+      ld_dc, dbias, M, static_cast<int>(d), static_cast<int>(T)
+  if (colsum) {
+    const int nv = static_cast<int>((d + 255) / 256);
+    if (nv <= 1) (void)launch_kx(o, adaln_gate_bwd_kernel<1, true>, dim3(grid), dim3(kRowThreads), 0, s, OWL_AGB_ARGS);
+    else if (nv <= 2) (void)launch_kx(o, adaln_gate_bwd_kernel<2, true>, dim3(grid), dim3(kRowThreads), 0, s, OWL_AGB_ARGS);
+    else if (nv <= 4) (void)launch_kx(o, adaln_gate_bwd_kernel<4, true>, dim3(grid), dim3(kRowThreads), 0, s, OWL_AGB_ARGS);
+    else if (nv <= 6) (void)launch_kx(o, adaln_gate_bwd_kernel<6, true>, dim3(grid), dim3(kRowThreads), 0, s, OWL_AGB_ARGS);
+    else (void)launch_kx(o, adaln_gate_bwd_kernel<8, true>, dim3(grid), dim3(kRowThreads), 0, s, OWL_AGB_ARGS);
+  } else {
+    OWL_DISPATCH_NV(d, ((void)launch_kx(o, adaln_gate_bwd_kernel<NV, false>, dim3(grid), dim3(kRowThreads), 0, s,
+                                        OWL_AGB_ARGS)));
+  }
+#undef OWL_AGB_ARGS
+  int rc = launch_status();
+  if (rc != OWL_OK) return rc;
+  if (dbias != nullptr && !colsum) {
+    rc = owl_colsum_bf16(dy, d, dbias, dbias_accumulate, M, d, stream);
+    if (rc != OWL_OK) return rc;
+  }
+  if (T > 1) {
+    dim3 grid2(static_cast<unsigned>(M / T), static_cast<unsigned>((d + 511) / 512));
+    if (da != nullptr) {
+      (void)launch_k(frame_reduce_kernel, dim3(grid2), dim3(64 * kFrLanes), 0, s, static_cast<const bf16*>(dh),
+                     static_cast<const bf16*>(x), rstd, static_cast<bf16*>(da), static_cast<bf16*>(db), ld_dab,
+                     static_cast<int>(d), static_cast<int>(T));
+      if ((rc = launch_status()) != OWL_OK) return rc;
+    }
+    if (dc != nullptr) {
+      (void)launch_k(frame_reduce_kernel, dim3(grid2), dim3(64 * kFrLanes), 0, s, static_cast<const bf16*>(dx),
+                     static_cast<const bf16*>(y), static_cast<const float*>(nullptr), static_cast<bf16*>(dc),
+                     static_cast<bf16*>(nullptr), ld_dc, static_cast<int>(d), static_cast<int>(T));
+      rc = launch_status();
+    }
+  }
+  return rc;
+}
+
+int owl_colsum_bf16_multi(const void* const* xs, const int64_t* lds, const int64_t* Ms, const int64_t* Ns,
+                          float* const* outs, int count, owl_stream_t stream) {
+  OWL_REQUIRE(xs && lds && Ms && Ns && outs && count > 0 && count <= 4, OWL_ERR_BAD_ARG);
+  ColsumSegs s{};
+  const long long budget = static_cast<long long>(sm_count()) * 6;  // CTAs over all segments
+  long long cells = 0;
+  for (int i = 0; i < count; ++i) {
+    OWL_REQUIRE(xs[i] && outs[i] && Ms[i] > 0 && Ns[i] > 0, OWL_ERR_BAD_ARG);
+    OWL_REQUIRE(Ns[i] % 8 == 0 && Ns[i] <= INT32_MAX, OWL_ERR_UNSUPPORTED);
+    OWL_REQUIRE(aligned16(xs[i]) && lds[i] % 8 == 0, OWL_ERR_ALIGN);
+    cells += Ms[i] * ((Ns[i] + 255) / 256);
+  }
+  int blk = 0;
+  for (int i = 0; i < count; ++i) {
+    const int gx = static_cast<int>((Ns[i] + 255) / 256);
+    long long splits = (budget * Ms[i] + cells - 1) / cells;       // CTAs in proportion to the bytes of the segment
+    const long long max_splits = (Ms[i] + 31) / 32;                 // >= 4 rows per row-lane
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    s.x[i] = static_cast<const bf16*>(xs[i]);
+    s.out[i] = outs[i];
+    s.ld[i] = lds[i];
+    s.M[i] = Ms[i];
+    s.N[i] = static_cast<int>(Ns[i]);
+    s.gx[i] = gx;
+    s.blk0[i] = blk;
+    blk += gx * static_cast<int>(splits);
+  }
+  s.blk0[count] = blk;
+  s.count = count;
+  (void)launch_k(colsum_multi_kernel, dim3(static_cast<unsigned>(blk)), dim3(256), 0, static_cast<cudaStream_t>(stream), s);
+  return launch_status();
 }
 
 int owl_kv_append(const void* src, int64_t src_sb, int64_t src_sh, void* cache, int64_t cache_sb, int64_t cache_sh,

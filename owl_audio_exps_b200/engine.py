@@ -86,11 +86,22 @@ def _align(n: int, a: int = 64) -> int:
 
 class GradBuckets:
     def __init__(self, model: torch.nn.Module, process_group=None, comm_stream: Optional[torch.cuda.Stream] = None,
-                 average: bool = True, wgrad_side_stream: bool = True, backwards_per_step: int = 1):
+                 average: bool = True, wgrad_side_stream: bool = True, backwards_per_step: int = 1,
+                 comm_dtype: Optional[torch.dtype] = None):
         """backwards_per_step: how many times every block runs backward in one micro-batch (2 when the loss calls the
         model twice, as the reference's self-forcing / causvid / distillation trainers do).  A block's bucket is handed
         to NCCL after its LAST expected backward; one more than declared raises (the bucket would be reduced twice)."""
         from .nn.attn import DiT, DiTBlock
+        import os
+        # Wire format of the gradient exchange.  fp32 (default) is what DistributedDataParallel sends (rft_trainer.py:96).
+        # bf16 (comm_dtype=torch.bfloat16 or OWL_COMM_DTYPE=bf16) halves the bytes NCCL moves and the time its CTAs share
+        # the SMs / HBM with backward: the fp32 bucket is cast on the communication stream, all-reduced and written back
+        # as fp32 (each rank's contribution is rounded to bf16 once: relative error 2^-9 per element, inside the 2e-2
+        # gradient tolerance the path is held to; the optimizer still sees fp32 gradients).
+        if comm_dtype is None:
+            comm_dtype = torch.bfloat16 if os.environ.get("OWL_COMM_DTYPE", "fp32").lower() in ("bf16", "bfloat16") else f32
+        self.comm_dtype = comm_dtype
+        self._wire: dict = {}        # bucket slice (data_ptr, numel) -> persistent bf16 wire buffer
         self.backwards_per_step = max(1, int(backwards_per_step))
         self.step_id = 0
         self._seen: dict = {}
@@ -225,8 +236,19 @@ class GradBuckets:
             self.comm_stream.wait_stream(torch.cuda.current_stream())
             if self.side_stream is not None:
                 self.comm_stream.wait_stream(self.side_stream)
+            op = dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM
             with torch.cuda.stream(self.comm_stream):
-                dist.all_reduce(flat, op=dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM, group=self.group)
+                if self.comm_dtype == torch.bfloat16 and flat.numel() >= 4096 and flat.numel() % 8 == 0:
+                    from . import ops
+                    key = (flat.data_ptr(), flat.numel())
+                    wire = self._wire.get(key)
+                    if wire is None:
+                        wire = self._wire[key] = torch.empty(flat.numel(), device=flat.device, dtype=torch.bfloat16)
+                    ops.cast_f32_bf16(flat, wire)
+                    dist.all_reduce(wire, op=op, group=self.group)
+                    flat.copy_(wire)
+                else:
+                    dist.all_reduce(flat, op=op, group=self.group)
         else:  # gloo (CPU tests of the host logic): no AVG op
             dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
             if self.average:

@@ -276,6 +276,40 @@ def _wgrad(dy: torch.Tensor, x: torch.Tensor, p: torch.Tensor, M: int) -> Option
     return _grad_like(g, p)
 
 
+def _bgrad_multi(items):
+    """[(dy [M, N], bias parameter, wanted), ...] (<= 4) -> bias gradients for autograd (None where the gradient went into
+    the parameter's bucket sink or is not wanted); all column sums in ONE launch."""
+    out = [None] * len(items)
+    sunk, fresh = [], []
+    for i, (dy, p, want) in enumerate(items):
+        if not want or p is None:
+            continue
+        sink = _sink(p)
+        if sink is not None and sink.pre_zeroed:
+            _ = sink.accumulate          # marks the sink written this step (engine bookkeeping)
+            sunk.append((dy, sink.view))
+        elif sink is not None:
+            if not sink.accumulate:
+                sink.view.zero_()
+            sunk.append((dy, sink.view))
+        else:
+            fresh.append((i, dy, p))
+    if sunk:
+        _on_side(lambda: ops.colsum_multi(sunk), *[dy for dy, _ in sunk])
+    if fresh:
+        buf = torch.zeros(sum(p.shape[0] for _, _, p in fresh), device=fresh[0][1].device, dtype=f32)
+        views, o = [], 0
+        for i, dy, p in fresh:
+            v = buf[o:o + p.shape[0]]
+            o += p.shape[0]
+            views.append((dy, v))
+            out[i] = v
+        ops.colsum_multi(views)
+        for i, dy, p in fresh:
+            out[i] = _grad_like(out[i], p)
+    return out
+
+
 def _bgrad(dy: torch.Tensor, p: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
     if p is None:
         return None
@@ -621,6 +655,13 @@ class CondBank:
         self.sunk = False        # gw/gb are engine bucket views (then the group wgrads may run on the side stream)
         self.sink = None         # engine.CondSink (decides add-vs-overwrite per row group at write time)
         self.token_grad = None
+        # Cross-layer fusion inside a linear stack (DiT.forward sets `chain`): the memory-bound passes either side of a
+        # layer boundary are one kernel, handed over through these slots (a cache of work done early, no autograd edge):
+        #   pre[l]      = (x_in, h1, rstd1)  block l-1 already normalised block l's input (residual+gate+adaLN pass)
+        #   tail[l]     = (y2, c2)     what block l+1's backward needs to run block l's last gate backward
+        #   pre_bwd[l]  = (dx2, dy2)   block l+1's backward already did it
+        self.chain = False
+        self.pre, self.tail, self.pre_bwd = {}, {}, {}
         self._done = set()
         self._flushed = 0        # layers [_flushed_lo, n_layers) already went through the group wgrad
         self._lo = n_layers
@@ -745,6 +786,7 @@ class CondBankFn(torch.autograd.Function):
                     grads[i + 1] = _grad_like(bank.gb[r:r + n], P[i + 1])
                 r += n
         bank.dmod_all = bank.mod_all = None
+        bank.pre.clear(), bank.tail.clear(), bank.pre_bwd.clear()
         side_mark()
         return (dscond, None, *grads)
 
@@ -823,7 +865,11 @@ class DiTBlockFn(torch.autograd.Function):
         a1, b1, c1 = mod[:, 0:d], mod[:, d:2 * d], mod[:, 2 * d:3 * d]
         a2, b2, c2 = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], mod[:, 5 * d:6 * d]
 
-        h1, rstd1 = ops.adaln_modulate_fwd(x16, a1, b1, T, RMS_EPS, want_rstd=need_grad)
+        pre = bank.pre.pop(plan.layer_idx, None) if bank is not None else None
+        if pre is not None and pre[0].data_ptr() == x16.data_ptr() and pre[0].shape == x16.shape:
+            h1, rstd1 = pre[1], pre[2]   # the previous block's last pass already produced them
+        else:
+            h1, rstd1 = ops.adaln_modulate_fwd(x16, a1, b1, T, RMS_EPS, want_rstd=need_grad)
         ops.stamp("f1 adaln1")
         qkv = torch.empty(B, L, 3 * d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, h1, W["wqkv"], M, 3 * d, d, mode=OWL_EPI_STORE, bias=W["bqkv"], out0=qkv)
@@ -846,7 +892,15 @@ class DiTBlockFn(torch.autograd.Function):
         y2 = torch.empty(M, d, device=x16.device, dtype=bf16)
         ops.gemm(OWL_GEMM_NT, s, W["w2"], M, d, 4 * d, mode=OWL_EPI_STORE, bias=W["b2"], out0=y2)
         ops.stamp("f7 fc2")
-        x2 = ops.gate_fwd(y2, c2, x1, T)
+        nxt = plan.layer_idx + 1
+        if bank is not None and bank.chain and nxt < bank.n_layers:
+            # x2 = x1 + c2*y2 and the NEXT block's h1 = rms_norm(x2)*(1+a1')+b1' in one pass (its modulation vectors are
+            # already in the bank)
+            nm = bank.mod(nxt)
+            x2, h1n, r1n = ops.residual_adaln_fwd(x1, y2, c2, nm[:, 0:d], nm[:, d:2 * d], T, RMS_EPS, want_rstd=True)
+            bank.pre[nxt] = (x2, h1n, r1n)
+        else:
+            x2 = ops.gate_fwd(y2, c2, x1, T)
         ops.stamp("f8 gate2")
 
         if need_grad:
@@ -859,6 +913,8 @@ class DiTBlockFn(torch.autograd.Function):
             ctx.stage = stage
             ctx.bank = bank
             ctx.layer = plan.layer_idx
+            if bank is not None and bank.chain:
+                bank.tail[plan.layer_idx] = (y2, c2)
         return x2.view(B, L, d) if x.dtype == bf16 else x2.view(B, L, d).to(x.dtype)
 
     @staticmethod
@@ -880,45 +936,56 @@ class DiTBlockFn(torch.autograd.Function):
         ops.stamp("b0 start")
 
         # ---- MLP branch: x2 = x1 + c2 * (s W2^T + b2)
-        g_b2 = _fresh_or_sink(b2, need[np0 + 7])
-        dy2 = ops.gate_bwd(dx2, y2, c2, dmod[:, 5 * d:6 * d], g_b2[0], T, dbias_accumulate=g_b2[1])
+        pb = bank.pre_bwd.pop(ctx.layer, None) if bank is not None else None
+        if pb is not None:
+            # the next block's backward ran this block's last gate backward together with its own adaLN backward
+            if pb[0].data_ptr() != dx2.data_ptr():
+                raise RuntimeError("DiT stack: the gradient reaching block %d is not the tensor block %d produced (the "
+                                   "stack output of an inner block was used elsewhere); run the blocks without the "
+                                   "conditioning bank (DiT.cond_group = 0)" % (ctx.layer, ctx.layer + 1))
+            dy2 = pb[1]
+        else:
+            dy2 = ops.gate_bwd(dx2, y2, c2, dmod[:, 5 * d:6 * d], None, T)
         ops.stamp("b1 gate2")
-        g_b2 = None if (g_b2[0] is None or g_b2[2]) else _grad_like(g_b2[0], b2)
         dz = torch.empty(M, 4 * d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dy2, w216, M, 4 * d, d, mode=OWL_EPI_DSILU, aux0=z, out0=dz)
         ops.stamp("b2 dz")
         g_w2 = _wgrad(dy2, s, w2, M) if need[np0 + 6] else None
-        del dy2
-        g_b1 = _bgrad(dz, b1) if need[np0 + 5] else None
         dh2 = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dz, w116, M, d, 4 * d, mode=OWL_EPI_STORE, out0=dh2)
         ops.stamp("b3 dh2")
         g_w1 = _wgrad(dz, h2, w1, M) if need[np0 + 4] else None
-        del dz
-        dx1 = ops.adaln_modulate_bwd(dh2, x1, a2, rstd2, dx2, dmod[:, 3 * d:4 * d], dmod[:, 4 * d:5 * d], T)
-        ops.stamp("b4 adaln2")
+        # ---- adaLN-2 backward and the attention branch's gate backward (x1 = x + c1 * (o Wout^T + bout)) in ONE pass
+        dx1, dy1 = ops.adaln_gate_bwd(dh2, x1, a2, rstd2, dx2, dmod[:, 3 * d:4 * d], dmod[:, 4 * d:5 * d],
+                                      y1, c1, dmod[:, 2 * d:3 * d], None, T)
+        ops.stamp("b5 adaln2+gate1")
         del dh2
-
-        # ---- attention branch: x1 = x + c1 * (o Wout^T + bout)
-        g_bout = _fresh_or_sink(bout, need[np0 + 3])
-        dy1 = ops.gate_bwd(dx1, y1, c1, dmod[:, 2 * d:3 * d], g_bout[0], T, dbias_accumulate=g_bout[1])
-        ops.stamp("b5 gate1")
-        g_bout = None if (g_bout[0] is None or g_bout[2]) else _grad_like(g_bout[0], bout)
         do = torch.empty(B, L, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dy1, wout16, M, d, d, mode=OWL_EPI_STORE, out0=do)
         ops.stamp("b6 do")
         g_wout = _wgrad(dy1, o2, wout, M) if need[np0 + 2] else None
-        del dy1
         dqkv = _attn_core_bwd(do, o2.view(B, L, d), (q, k_all, v_all, lse, rq, rk, offset, mask), cos, sin, L)
         ops.stamp("b7 attn+rope")
         dqkv2 = dqkv.view(M, 3 * d)
-        g_bqkv = _bgrad(dqkv2, bqkv) if need[np0 + 1] else None
+        # the block's four bias gradients = column sums of dy2 / dz / dy1 / dqkv: ONE launch (next to the weight gradients
+        # on the side stream when the engine's buckets are installed)
+        g_b2, g_b1, g_bout, g_bqkv = _bgrad_multi([(dy2, b2, need[np0 + 7]), (dz, b1, need[np0 + 5]),
+                                                   (dy1, bout, need[np0 + 3]), (dqkv2, bqkv, need[np0 + 1])])
+        del dy2, dz, dy1
         dh1 = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm(OWL_GEMM_NN, dqkv2, wqkv16, M, d, 3 * d, mode=OWL_EPI_STORE, out0=dh1)
         ops.stamp("b8 dh1")
         g_wqkv = _wgrad(dqkv2, h1, wqkv, M) if need[np0 + 0] else None
         del dqkv, dqkv2
-        dx = ops.adaln_modulate_bwd(dh1, x16, a1, rstd1, dx1, dmod[:, 0:d], dmod[:, d:2 * d], T)
+        tail = bank.tail.pop(ctx.layer - 1, None) if (bank is not None and bank.chain and need[0]) else None
+        if tail is not None and xdtype == bf16:
+            # adaLN-1 backward of this block + the last gate backward of the PREVIOUS block in one pass
+            y2p, c2p = tail
+            dx, dy2p = ops.adaln_gate_bwd(dh1, x16, a1, rstd1, dx1, dmod[:, 0:d], dmod[:, d:2 * d], y2p, c2p,
+                                          bank.dmod(ctx.layer - 1)[:, 5 * d:6 * d], None, T)
+            bank.pre_bwd[ctx.layer - 1] = (dx, dy2p)
+        else:
+            dx = ops.adaln_modulate_bwd(dh1, x16, a1, rstd1, dx1, dmod[:, 0:d], dmod[:, d:2 * d], T)
         ops.stamp("b9 adaln1")
 
         # ---- conditioning projections: mod = silu(cond) Wc^T + bc

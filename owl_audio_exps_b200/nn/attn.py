@@ -164,6 +164,9 @@ class DiT(nn.Module):
             # all 4 x n_layers conditioning projections as one GEMM (cond is the same for every block)
             bank, token = OF.cond_bank(scond, [b.cond_params() for b in self.blocks], self.config.d_model,
                                        self._stage, self.cond_group)
+            # the blocks below form a linear chain on a bf16 residual stream: the passes either side of every layer
+            # boundary fuse (functional.CondBank.pre / tail / pre_bwd)
+            bank.chain = x.dtype == torch.bfloat16 and getattr(self, "chain_fusion", True)
         for layer_idx, block in enumerate(self.blocks):
             block_mask = local_block_mask if self.local_layers[layer_idx] else global_block_mask
             if ckpt:

@@ -112,7 +112,7 @@ class SingleKVCache:
         rows.  `private`: return a copy that does not alias the cache buffers.  `batch` / `device`: those of the
         incoming qkv -- the kernel sizes its writes from qkv, so a mismatch must fail here, on the host."""
         self._check()
-        if self.dtype != torch.bfloat16:
+        if batch is not None and self.dtype != torch.bfloat16:   # (called from the kernel path: batch / device given)
             raise RuntimeError(f"KV cache dtype {self.dtype}: the sm_100a attention path stores K/V in bf16 "
                                "(kv_cache.py:18 default); call cache.to(dtype=torch.bfloat16)")
         if device is not None and torch.device(self.device).type != device.type:

@@ -278,6 +278,21 @@ def adaln_modulate_bwd(dh, x, a, rstd, dres, da, db, T: int):
     return dx
 
 
+@_prof("adaln_gate_bwd")
+def adaln_gate_bwd(dh, x, a, rstd, dres, da, db, y, c, dc, dbias, T: int, dbias_accumulate: bool = False):
+    """adaLN backward + gate backward of the producing branch in one pass -> (dx, dy); da/db/dc written in place,
+    dbias (+)= colsum(dy).  See owl_adaln_gate_bwd."""
+    M, d, _ = _rows(x)
+    dx, dy = torch.empty_like(x), torch.empty_like(x)
+    rc = _lib.load().owl_adaln_gate_bwd(dh.data_ptr(), x.data_ptr(), _p(a), _rows(a)[2] if a is not None else 0,
+                                        rstd.data_ptr(), _p(dres), dx.data_ptr(), _p(da), _p(db),
+                                        _rows(da)[2] if da is not None else 0, y.data_ptr(), c.data_ptr(), _rows(c)[2],
+                                        dy.data_ptr(), _p(dc), _rows(dc)[2] if dc is not None else 0, _p(dbias),
+                                        int(dbias_accumulate), M, d, T, _stream())
+    _lib.check(rc, "owl_adaln_gate_bwd")
+    return dx, dy
+
+
 @_prof("gate_fwd")
 def gate_fwd(x, c, res, T: int):
     M, d, _ = _rows(x)
@@ -305,6 +320,20 @@ def colsum(x, out, accumulate: bool = False):
     _lib.check(_lib.load().owl_colsum_bf16(x.data_ptr(), ld, out.data_ptr(), int(accumulate), M, N, _stream()),
                "owl_colsum_bf16")
     return out
+
+
+@_prof("colsum")
+def colsum_multi(items) -> None:
+    """[(x bf16 [M, N], out fp32 [N]), ...] (at most 4): out += column sums of x, one launch.  Outputs must be zeroed /
+    hold what is to be accumulated onto."""
+    n = len(items)
+    info = [_rows(x) for x, _ in items]
+    xs = (C.c_void_p * n)(*[x.data_ptr() for x, _ in items])
+    outs = (C.c_void_p * n)(*[o.data_ptr() for _, o in items])
+    lds = (C.c_int64 * n)(*[i[2] for i in info])
+    Ms = (C.c_int64 * n)(*[i[0] for i in info])
+    Ns = (C.c_int64 * n)(*[i[1] for i in info])
+    _lib.check(_lib.load().owl_colsum_bf16_multi(xs, lds, Ms, Ns, outs, n, _stream()), "owl_colsum_bf16_multi")
 
 
 @_prof("layer_norm")

@@ -242,6 +242,9 @@ def test_gradient_checkpointing_same_grads():
             # stored path: the stack's CondBank takes these gradients as one GEMM per group of layers;
             # recompute path: one GEMM per layer -> same operands, different fp32 summation order
             assert relerr(p.grad, ref[k]) <= 1e-3, k
+        elif k.endswith(".bias"):
+            # column sums meet in fp32 atomics (one per column per CTA): the addition order is not fixed
+            assert relerr(p.grad, ref[k]) <= 1e-5, k
         else:
             assert torch.equal(p.grad, ref[k]), k
 
