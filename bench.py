@@ -43,7 +43,44 @@ WORKLOADS = {
                         causal=True, has_audio=True, rope_impl="ortho", local_window=16, global_window=None,
                         backbone="dit"), B=8, F=16, name="configs/av_v5_8x8_sf.yml (block geometry)"),
 }
+# configs/dit_v4_5B.yml: d=2560, H=20 (dh=128), 36 layers, per-block gradient checkpointing, B=1, 1536 frames x 64 tokens
+WORKLOADS["dit_v4_5B"] = dict(cfg=dict(d_model=2560, n_heads=20, n_layers=36, tokens_per_frame=64, n_frames=1536,
+                                       sample_size=8, causal=True, has_audio=False, rope_impl="motion", rope_ats_delta=2.0,
+                                       local_window=16, global_window=None, backbone="dit", gradient_checkpointing=True),
+                              B=1, F=1536, name="configs/dit_v4_5B.yml")
 METRIC = "train tokens/sec (audio DiT stack fwd+bwd+grad all-reduce), whole job"
+
+
+def unmasked_pairs(F_, T, W):
+    """(query, key) token pairs the frame-block causal mask leaves visible (attn.py:43-59, no doc ids)."""
+    if W is None or W >= F_:
+        return T * T * F_ * (F_ + 1) // 2
+    return T * T * (W * (W + 1) // 2 + (F_ - W) * W)
+
+
+def step_flops(B, L, d, T, n_layers, local_window, global_window, local_idx=4):
+    """fwd+bwd algorithmic FLOPs (SURVEY 8d closed forms): 3x linear + 3.5x attention, masked pairs excluded, activation
+    recomputation under gradient checkpointing NOT counted."""
+    F_ = L // T
+    lin_fwd = B * L * (24 * d * d + 12 * d * d / T) * n_layers
+    att_fwd = 0.0
+    for i in range(n_layers):
+        w = local_window if (i % local_idx) != 0 else global_window
+        att_fwd += 4.0 * d * B * unmasked_pairs(F_, T, w)
+    return {"linear_fwd": lin_fwd, "attn_fwd": att_fwd, "step": 3 * lin_fwd + 3.5 * att_fwd}
+
+
+def measured_traffic(workload, dom_gemm):
+    """dram__bytes_read+write per launch of the dominant kernel, from the ncu --set full capture summarised in
+    profiles/traffic.json (one entry per workload, each naming the .md file it was read from); None when there is no
+    capture for this workload/kernel."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    ent = json.load(open(p)).get(workload, {}).get("gemm" if dom_gemm else "attn")
+    if not ent:
+        return None, None
+    return float(ent["dram_bytes_per_launch"]), ent.get("source")
 
 
 def _peaks():
@@ -117,7 +154,7 @@ def cpu_port_step_time(workload, B, n_layers, steps, warmup, threads=None):
     import owl_audio_exps_b200.nn.rope as R
     w = WORKLOADS[workload]
     cfg = types.SimpleNamespace(**{**w["cfg"], "n_layers": n_layers})
-    F_ = w["F"] if workload != "dit_v4" else 32   # dense-mask SDPA is O(L^2): 98k tokens does not fit; 32 frames = 2048 tokens
+    F_ = w["F"] if not workload.startswith("dit_v4") else 32   # dense-mask SDPA is O(L^2): 98k tokens does not fit; 32 frames = 2048 tokens
     L = F_ * cfg.tokens_per_frame
     if threads:
         torch.set_num_threads(threads)
@@ -154,23 +191,30 @@ def cpu_port_step_time(workload, B, n_layers, steps, warmup, threads=None):
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU path for the block (torch CPU ops via the oracle port)."""
+    """--impl reference: the reference's CPU path for the block (torch CPU ops via the oracle port) on the GPU arm's
+    config: same per-GPU batch, same sequence, 2 of the stack's layers timed and scaled to full depth (layers are
+    identical in cost).  BASELINE.json's own CPU case (batch 1) is timed beside it and reported under `batch_1`."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     w = WORKLOADS[args.workload]
-    n_layers, B = 2, 1    # bounded sample: each step stays in the seconds range on any host
-    dt, toks, sample, cores = cpu_port_step_time(args.workload, B, n_layers, max(args.steps, 1), max(args.warmup, 1),
-                                                 threads=host_threads())
+    n_layers = 2
+    B = args.batch or w["B"]
+    steps, warmup = max(min(args.steps, 10), 1), max(min(args.warmup, 2), 1)   # bounded: seconds per step on the host
+    dt, toks, sample, cores = cpu_port_step_time(args.workload, B, n_layers, steps, warmup, threads=host_threads())
     # per-layer cost is uniform: scale the measured layers to the full stack
     dt_full = dt * w["cfg"]["n_layers"] / n_layers
     val = toks / dt_full
+    dt1, toks1, sample1, _ = cpu_port_step_time(args.workload, 1, n_layers, 3, 1, threads=host_threads())
+    val1 = toks1 / (dt1 * w["cfg"]["n_layers"] / n_layers)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt_full * 1e3, "higher_is_better": True,
+        "steps": steps, "warmup": warmup, "ms_per_step": dt_full * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": w["name"], "note": "CPU reference arm; time of measured layers scaled to the full depth"},
+        "config": {"workload": w["name"], "per_gpu_batch": B,
+                   "note": "CPU reference arm; time of the measured layers scaled to the full depth"},
         "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
+        "batch_1": {"value": val1, "unit": "tokens/s", "sample": sample1},
         "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -193,7 +237,6 @@ def run_owl(args):
     import torch.distributed as dist
     from owl_audio_exps_b200 import engine, ops
     import owl_audio_exps_b200.nn as N
-    from oracle.dit_oracle import step_flops  # closed-form FLOP count only; no oracle compute here
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -216,13 +259,14 @@ def run_owl(args):
     L = F_ * T
     torch.manual_seed(0)
     model = N.DiT(cfg).to(dev)                       # fp32 master weights, reference init
+    model.train()                                    # (gradient_checkpointing of dit_v4_5B is a training-mode switch)
     n_params = sum(p.numel() for p in model.parameters())
     buckets = engine.GradBuckets(model, wgrad_side_stream=os.environ.get("OWL_WGRAD_SIDE", "1") != "0")
     g = torch.Generator().manual_seed(1000 + rank)   # each rank draws its own batch (DistributedSampler analogue)
     host = [torch.randn(B, L, d, generator=g).to(torch.bfloat16).pin_memory(),
             torch.randn(B, F_, d, generator=g).to(torch.bfloat16).pin_memory(),
             torch.randn(B, L, d, generator=g).to(torch.bfloat16).pin_memory()]
-    if args.workload == "dit_v4":
+    if args.workload.startswith("dit_v4"):
         # 98 304 tokens: ~90 GB of saved activations per step; a graph-private pool next to the eager warm-up's pool
         # does not fit 180 GB, and with 50-3000 us kernels there is no launch overhead for a graph to remove
         args.no_graph = True
@@ -293,11 +337,10 @@ def run_owl(args):
         att_tf = 3.5 * fl["attn_fwd"] / (att_ms * 1e-3) / 1e12 if att_ms > 0 else 0.0
         dom_gemm = gemm_ms >= att_ms
         ach = gemm_tf if dom_gemm else att_tf
+        traffic, traffic_src = measured_traffic(args.workload, dom_gemm)
         roofline = {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)" if dom_gemm else "attn fwd/bwd kernels (tcgen05)",
                     "achieved": ach, "peak": pk["tf"], "unit": "TFLOP/s", "frac": ach / pk["tf"],
-                    # dram__bytes_read+write per GEMM launch, mean over the four block shapes of the ncu --set full
-                    # capture in profiles/r01_ncu_gemm_full.md (audio shapes; algorithmic mean 60 MB: outputs stay in L2)
-                    "traffic": 32.8e6 if (dom_gemm and args.workload == "audio") else None,
+                    "traffic": traffic, "traffic_source": traffic_src,
                     "peak_source": pk["src"], "launches_per_step": gemm_n if dom_gemm else att_n,
                     "avg_launch_us": 1e3 * (gemm_ms / gemm_n if dom_gemm else att_ms / max(att_n, 1)),
                     "share_of_step_kernel_time": (gemm_ms if dom_gemm else att_ms) / total_ms,
@@ -322,10 +365,14 @@ def run_owl(args):
             "roofline": roofline, "clocks": clk.summary(),
         }
         if world == 1 and not args.no_cpu:
-            dt, toks, sample, cores = cpu_port_step_time(args.workload, 1, 2, 3, 1, threads=host_threads())
+            # same per-GPU batch as the GPU arm (bounded: 2 layers, 3 steps), and BASELINE.json's batch-1 CPU case beside it
+            dt, toks, sample, cores = cpu_port_step_time(args.workload, B, 2, 3, 1, threads=host_threads())
             dt_full = dt * cfg.n_layers / 2
             line["cpu_baseline"] = {"value": toks / dt_full, "unit": "tokens/s", "cores": cores, "kind": "port",
                                     "sample": sample + "; scaled to full depth"}
+            dt1, toks1, sample1, _ = cpu_port_step_time(args.workload, 1, 2, 3, 1, threads=host_threads())
+            line["cpu_baseline"]["batch_1"] = {"value": toks1 / (dt1 * cfg.n_layers / 2), "unit": "tokens/s",
+                                               "sample": sample1 + "; scaled to full depth"}
         print(json.dumps(line), flush=True)
     if world > 1:
         # End of job without NCCL: the other ranks wait on the rendezvous store (not on a collective) until rank 0

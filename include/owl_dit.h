@@ -102,6 +102,18 @@ typedef struct owl_gemm_epilogue {
 int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* B,
                   int64_t ldb, const owl_gemm_epilogue* epi, owl_stream_t stream);
 
+/* Weight-streaming GEMM of the decode regime: out0[M <= 128, N] = epi(A[M, K] . W[N, K]^T + bias), bf16.
+ * Replaces every nn.Linear of one KV-cached model evaluation of the causal rollout (attn.py:82,113, mlp.py:34-36 at
+ * 1 frame = 65 tokens or 1 token; owl_wms/sampling/av_caching_v2.py:89-140, inference/causvid_pipeline.py:112-163):
+ * the problem is split over N AND K into about one chunk per SM so all SMs stream weights at once; split-K partial
+ * sums meet in `workspace` (fp32 L2 atomics) and the last-arriving chunk applies the epilogue.  Modes: OWL_EPI_STORE,
+ * OWL_EPI_BIAS_SILU (ONE output: out0 = silu(bf16(acc + bias)), the pre-activation is not kept), OWL_EPI_GATE_RESIDUAL.
+ * `workspace`: owl_gemm_smallm_workspace_bytes(N) bytes, ZERO before the first call; every call leaves it zero again.
+ * Calls sharing a workspace must be ordered on one stream. */
+int64_t owl_gemm_smallm_workspace_bytes(int64_t N);
+int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
+                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, owl_stream_t stream);
+
 /* Plain CUDA-core GEMM with the same contract (OWL_EPI_STORE / OWL_EPI_F32 only, no bias).
  * Verification aid for tests: an independent on-device answer at sizes where the CPU oracle is
  * too slow.  Never called by the product path. */
@@ -293,6 +305,32 @@ int owl_attn_bwd_check(const void* dout, const void* o, int64_t o_sb, int64_t o_
                        int64_t dq_sh, void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh,
                        int64_t B, int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask,
                        owl_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Decode regime of the KV-cached causal rollout (attn.py:92-109 with block_mask None; av_caching_v2.py:89-140,
+ * audio_caching.py:120-150, causvid_pipeline.py:112-163): <= 128 new query rows against a RING cache whose state
+ * lives in device memory, so one captured CUDA graph serves every frame.
+ *   state (int32[4], device): [0] rows cached, [1] ring start slot, [2] RoPE position of the next new token.
+ *   k_cache / v_cache: bf16 [B, H, cap, dh] (strides c_sb, c_sh in elements; rows contiguous).
+ * owl_qk_norm_rope_decode: QK-RMSNorm + RoPE + head split of qkv [B, L, 3*H*dh] (attn.py:83-89, rope.py:43-51);
+ *   q -> [B, H, L, dh]; K (post-norm, post-RoPE) and V rows -> ring slots (state[1] + state[0] + l) % cap.  The rows
+ *   are NOT counted in state[0] until owl_decode_state_advance commits them (KVCache.update, kv_cache.py:50-58).
+ * owl_attn_decode: o[B, Lq, H*dh] = softmax(q K^T / sqrt(dh)) V over the cached rows plus the Lq rows just written
+ *   (no mask); vis_rows > 0: only the last vis_rows rows of [cache, new] (local layers, attn.py:102-105).  The KV
+ *   tiles of a head are split over n CTAs (B*H*n ~ #SMs); the last CTA of a head merges the partials.
+ *   `workspace`: owl_attn_decode_workspace_bytes() bytes, ZERO before the first call; left zero-countered by each call.
+ * owl_decode_state_advance: state after committing commit_rows and ejecting the drop_rows oldest rows
+ *   (KVCache.truncate, kv_cache.py:60-75). */
+int64_t owl_attn_decode_workspace_bytes(int64_t B, int64_t H, int64_t cap, int64_t dh);
+int owl_attn_decode(const void* q, int64_t q_sb, int64_t q_sh, const void* k_cache, const void* v_cache, int64_t c_sb,
+                    int64_t c_sh, int64_t cap, const int32_t* state, int64_t vis_rows, void* o, int64_t o_sb, int64_t o_sl,
+                    int64_t B, int64_t H, int64_t Lq, int64_t dh, void* workspace, int64_t workspace_bytes,
+                    owl_stream_t stream);
+int owl_qk_norm_rope_decode(const void* qkv, const float* cos_tab, const float* sin_tab, int64_t table_rows,
+                            const int32_t* state, void* q, int64_t q_sb, int64_t q_sh, void* k_cache, void* v_cache,
+                            int64_t c_sb, int64_t c_sh, int64_t cap, int64_t B, int64_t L, int64_t H, int64_t dh, float eps,
+                            owl_stream_t stream);
+int owl_decode_state_advance(int32_t* state, int64_t commit_rows, int64_t drop_rows, int64_t cap, owl_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -11,12 +11,20 @@ __version__ = "0.1.0"
 _NN_MODULES = ("attn", "embeddings", "kv_cache", "mlp", "modulation", "normalization", "rope")
 
 
-def install(package: str = "owl_wms"):
+def install(package: str = "owl_wms", patch_compile: bool = True):
     """Make `<package>.nn.{attn,embeddings,kv_cache,mlp,modulation,normalization,rope}` resolve to this
     implementation, so the reference's models / samplers / trainers / inference pipeline (which do
     `from ..nn.attn import DiT, FinalLayer`, `from ..nn.kv_cache import KVCache`, ...) pick up the
-    sm_100a path without any edit.  Call before importing `<package>.models`.  See INTEGRATION.md."""
+    sm_100a path without any edit.  Call before importing `<package>.models`.  See INTEGRATION.md.
+
+    `patch_compile`: also route `torch.compile` through `compat.compile`, so the reference's `torch.compile(model)` /
+    `torch.compile(DDP(model))` / `fullgraph=True` lines (rft_trainer.py:96-99, causvid_pipeline.py:63,
+    gamerft_audio.py:36) wrap these modules in a pass-through with OptimizedModule's surface instead of handing
+    ctypes launches to Dynamo."""
     from . import nn as _nn
+    if patch_compile:
+        from . import compat
+        compat.patch_torch_compile()
     sys.modules[f"{package}.nn"] = sys.modules.get(f"{package}.nn", _nn)
     for name in _NN_MODULES:
         sys.modules[f"{package}.nn.{name}"] = getattr(_nn, name)

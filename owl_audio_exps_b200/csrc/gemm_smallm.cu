@@ -1,0 +1,389 @@
+// Weight-streaming bf16 GEMM for the decode regime: y[M <= 128, N] = epi(x[M, K] . W[N, K]^T + bias).
+//
+// One KV-cached model evaluation of the causal rollout (owl_wms/sampling/av_caching_v2.py:89-140,
+// inference/causvid_pipeline.py:112-163) runs every nn.Linear of the stack on 1 frame = 65 tokens (or 1 token for the
+// audio model, 1 conditioning row per frame): the weights (2 GB at AV geometry) are read once per evaluation and
+// nothing is reused, so the GEMMs are HBM-bound and what matters is that ALL SMs pull weight bytes at the same time.
+// The training GEMM (gemm.cu) gives a [<=128, N] problem N/BN CTAs that each walk all of K serially (measured:
+// 19.8 us per call where the weights stream in 2 us, profiles/r01_launches_av_decode.md).  Here:
+//
+//   * the problem is cut into tiles_n x splits (n-tile, K-range) chunks, about one per SM, so every SM streams
+//     ~1/148th of the weight matrix through a deep TMA ring (up to 8 x 24 KB in flight per SM);
+//   * each chunk is a 128 x BN x (64 * kb) tcgen05 MMA with the fp32 accumulator in TMEM (the token rows are padded
+//     to 128 by TMA zero fill: no traffic for them, and the tensor pipe is idle anyway);
+//   * split-K partials meet in an fp32 workspace tile with red.global.add.v4.f32 (L2 atomics); a per-tile arrival
+//     counter elects the LAST chunk's CTA, which reads the sum back, applies the epilogue (bias, bias+SiLU,
+//     bias+gate*y+residual) and writes bf16.  That CTA also zeroes the tile and the counter again, so the workspace
+//     is zero between launches and no memset node precedes the kernel (one launch per Linear, graph-friendly);
+//   * persistent over chunks (conditioning bank at decode: M = 1 row, N = 6d * n_layers -> 1728 tiles).
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
+#include "host_common.h"
+#include "sm100.cuh"
+
+namespace owl {
+
+static constexpr int kSmThreads = 192;   // warp 0 TMA, warp 1 MMA + TMEM, warps 2-5 epilogue (thread = token row)
+static constexpr int kSmBK = 64;
+static constexpr int kSmABytes = 128 * kSmBK * 2;
+static constexpr int kSmMaxStages = 8;
+static constexpr int kSmSmemLimit = 232448;
+
+struct SmallMParams {
+  int M, N, K;
+  int tiles_n, splits, kb_per_split, kb_total, stages;
+  int mode, rows_per_frame;
+  const float* bias;
+  bf16* out;
+  long long ldo;
+  const bf16* res;
+  long long ldres;
+  const bf16* gate;
+  long long ldgate;
+  float* ws;            // [tiles_n][128][BN] fp32, zero between launches
+  unsigned* counters;   // [tiles_n], zero between launches
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float4 ld_cg_v4(const float* addr) {
+  float4 v;
+  asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ float sm_tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sm_silu(float z) {
+  const float h = 0.5f * z;
+  return fmaf(h, sm_tanh_approx(h), h);
+}
+
+// 8 consecutive output columns of one row: bias, activation / gate+residual, bf16 store (16 bytes)
+__device__ __forceinline__ void finish8(const SmallMParams& p, int row, int col, float (&a)[8]) {
+  if (col >= p.N) return;
+  if (p.bias != nullptr) {
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+    a[0] += b0.x; a[1] += b0.y; a[2] += b0.z; a[3] += b0.w;
+    a[4] += b1.x; a[5] += b1.y; a[6] += b1.z; a[7] += b1.w;
+  }
+  uint4 o;
+  if (p.mode == OWL_EPI_STORE) {
+    o = make_uint4(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]), pack_bf16(a[4], a[5]), pack_bf16(a[6], a[7]));
+  } else {
+    // the Linear's own output is a bf16 tensor in the reference (mlp.py:34-35, modulation.py:41-43): round once
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = round_bf16(a[j]);
+    if (p.mode == OWL_EPI_BIAS_SILU) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] = sm_silu(a[j]);
+    } else {  // OWL_EPI_GATE_RESIDUAL: out = res + gate[frame] * y
+      const uint4 rv = __ldg(reinterpret_cast<const uint4*>(p.res + static_cast<long long>(row) * p.ldres + col));
+      const uint4 gv =
+          __ldg(reinterpret_cast<const uint4*>(p.gate + static_cast<long long>(row / p.rows_per_frame) * p.ldgate + col));
+      const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        a[2 * j] = fmaf(bf16_lo(gg[j]), a[2 * j], bf16_lo(rr[j]));
+        a[2 * j + 1] = fmaf(bf16_hi(gg[j]), a[2 * j + 1], bf16_hi(rr[j]));
+      }
+    }
+    o = make_uint4(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]), pack_bf16(a[4], a[5]), pack_bf16(a[6], a[7]));
+  }
+  *reinterpret_cast<uint4*>(p.out + static_cast<long long>(row) * p.ldo + col) = o;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kSmThreads, 1)
+gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const SmallMParams p) {
+  constexpr int kBBytes = BN * kSmBK * 2;
+  constexpr int kStageBytes = kSmABytes + kBBytes;
+  constexpr uint32_t kTmemCols = 2 * BN;   // double-buffered accumulator
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty_bar = full_bar + kSmMaxStages;
+  uint64_t* tfull_bar = empty_bar + kSmMaxStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint32_t* last_flag = tmem_slot + 1;
+  const int kStages = p.stages;
+  uint8_t* smem_a = smem + 1024;
+  uint8_t* smem_b = smem_a + kStages * kSmABytes;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();     // the activations (and the zeroed workspace) come from the previous kernel
+  pdl_launch();
+
+  const int total = p.tiles_n * p.splits;
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int tn = t % p.tiles_n, ks = t / p.tiles_n;
+        const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+          tma_load_2d(smem_b + stage * kBBytes, &tmB, &full_bar[stage], kb * kSmBK, tn * BN);   // weights first: HBM
+          tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);       // activations: L2
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
+      int stage = 0, as = 0;
+      uint32_t phase = 0, aphase = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int ks = t / p.tiles_n;
+        const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        mbar_wait(&tempty_bar[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + static_cast<uint32_t>(as * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem_a + stage * kSmABytes), sb = smem_u32(smem_b + stage * kBBytes);
+#pragma unroll
+          for (int k = 0; k < kSmBK / 16; ++k)
+            umma_bf16_ss(tacc, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
+                         (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit(&empty_bar[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    const int q = warp & 3;            // TMEM lane quarter this warp may read
+    const int r = q * 32 + lane;       // token row
+    const bool row_ok = r < p.M;
+    const bool elected = threadIdx.x == 64;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int tn = t % p.tiles_n;
+      const int n0 = tn * BN;
+      mbar_wait(&tfull_bar[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN);
+      float* wrow = p.ws + (static_cast<long long>(tn) * 128 + r) * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t acc[32];
+        tmem_ld_x32(taddr + c * 32, acc);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        if (p.splits == 1) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float a[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = __uint_as_float(acc[g * 8 + j]);
+            finish8(p, r, n0 + c * 32 + g * 8, a);
+          }
+        } else {
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            red_add_v4(wrow + c * 32 + g * 4, __uint_as_float(acc[4 * g]), __uint_as_float(acc[4 * g + 1]),
+                       __uint_as_float(acc[4 * g + 2]), __uint_as_float(acc[4 * g + 3]));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[as]);    // accumulator buffer back to the MMA warp
+      if (++as == 2) { as = 0; aphase ^= 1; }
+      if (p.splits > 1) {
+        __threadfence();               // this thread's partial sums are at L2 before the arrival is counted
+        named_bar_sync(1, 128);
+        if (elected) {
+          const unsigned prev = atomicAdd(p.counters + tn, 1u);
+          const unsigned last = prev == static_cast<unsigned>(p.splits - 1) ? 1u : 0u;
+          if (last) __threadfence();   // order the counter read before the workspace reads below
+          *last_flag = last;
+        }
+        named_bar_sync(1, 128);
+        const bool last = *last_flag != 0;
+        named_bar_sync(1, 128);        // everyone has read the flag before the next tile's election rewrites it
+        if (last) {
+          if (row_ok) {
+#pragma unroll 1
+            for (int c = 0; c < BN / 8; ++c) {
+              const float4 v0 = ld_cg_v4(wrow + c * 8), v1 = ld_cg_v4(wrow + c * 8 + 4);
+              *reinterpret_cast<float4*>(wrow + c * 8) = make_float4(0.f, 0.f, 0.f, 0.f);
+              *reinterpret_cast<float4*>(wrow + c * 8 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+              float a[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+              finish8(p, r, n0 + c * 8, a);
+            }
+          }
+          if (elected) p.counters[tn] = 0u;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+template <int BN>
+static int launch_smallm(const CUtensorMap& tmA, const CUtensorMap& tmB, const SmallMParams& p, int grid, int smem_bytes,
+                         cudaStream_t s) {
+  static PerDeviceOnce once;
+  const int rc0 = once.run([] {
+    return static_cast<int>(
+        cudaFuncSetAttribute(gemm_smallm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmSmemLimit));
+  });
+  if (rc0 != OWL_OK) return rc0;
+  cudaError_t e = launch_k(gemm_smallm_kernel<BN>, dim3(static_cast<unsigned>(grid)), dim3(kSmThreads),
+                           static_cast<size_t>(smem_bytes), s, tmA, tmB, p);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return static_cast<int>(e);
+  }
+  return launch_status();
+}
+
+struct SmallMPlan {
+  int bn, splits;
+};
+
+// One wave of ~equal chunks: time ~ waves x (fixed + bytes one CTA streams / per-SM bandwidth) + the reduce round trip.
+static SmallMPlan plan_smallm(long long M, long long N, int kb_total, int sms) {
+  SmallMPlan best{64, 1};
+  double best_cost = 1e300;
+  const int cand[2] = {128, 64};
+  for (int i = 0; i < 2; ++i) {
+    const int bn = cand[i];
+    if (bn == 128 && N <= 64) continue;
+    const long long tiles = (N + bn - 1) / bn;
+    for (int sp = 1; sp <= 16 && sp <= kb_total; ++sp) {
+      const int kbps = (kb_total + sp - 1) / sp;
+      const int real_sp = (kb_total + kbps - 1) / kbps;
+      if (real_sp != sp) continue;
+      const long long ctas = tiles * sp;
+      const long long waves = (ctas + sms - 1) / sms;
+      const double bytes = static_cast<double>(kbps) * (bn * 128.0 + static_cast<double>(M) * 128.0);
+      const double cost = static_cast<double>(waves) * (1500.0 + bytes / 45.0) + (sp > 1 ? 700.0 : 0.0);  // ns
+      if (cost < best_cost) { best_cost = cost; best = SmallMPlan{bn, sp}; }
+      if (ctas >= 2LL * sms) break;
+    }
+  }
+  return best;
+}
+
+}  // namespace owl
+
+using namespace owl;
+
+extern "C" {
+
+int64_t owl_gemm_smallm_workspace_bytes(int64_t N) {
+  // fp32 [ceil(N/64)][128][64] partial-sum tiles (covers BN = 128 too) + one arrival counter per 64 columns
+  const int64_t tiles = (N + 63) / 64;
+  return tiles * 128 * 64 * 4 + tiles * 4;
+}
+
+int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
+                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, owl_stream_t stream) {
+  if (!A || !W || !epi || !epi->out0 || M <= 0 || N <= 0 || K <= 0) return OWL_ERR_BAD_ARG;
+  if (M > 128) return OWL_ERR_UNSUPPORTED;
+  if (N % 8 != 0 || K % 8 != 0) return OWL_ERR_UNSUPPORTED;
+  if (lda % 8 || ldw % 8 || epi->ld0 % 8 || !aligned16(A) || !aligned16(W) || !aligned16(epi->out0)) return OWL_ERR_ALIGN;
+  if (lda < K || ldw < K) return OWL_ERR_BAD_ARG;
+  if (epi->bias && !aligned16(epi->bias)) return OWL_ERR_ALIGN;
+  SmallMParams p{};
+  p.M = static_cast<int>(M); p.N = static_cast<int>(N); p.K = static_cast<int>(K);
+  p.mode = epi->mode;
+  p.rows_per_frame = epi->rows_per_frame > 0 ? epi->rows_per_frame : 1;
+  p.bias = epi->bias;
+  p.out = static_cast<bf16*>(epi->out0);
+  p.ldo = epi->ld0;
+  switch (p.mode) {
+    case OWL_EPI_STORE:
+    case OWL_EPI_BIAS_SILU:   // single output here: silu(bf16(x W^T + b)); the pre-activation is not kept (no backward)
+      break;
+    case OWL_EPI_GATE_RESIDUAL:
+      if (!epi->aux0 || !epi->aux1) return OWL_ERR_BAD_ARG;
+      if (epi->lda0 % 8 || epi->lda1 % 8 || !aligned16(epi->aux0) || !aligned16(epi->aux1)) return OWL_ERR_ALIGN;
+      if (M % p.rows_per_frame) return OWL_ERR_BAD_ARG;
+      p.res = static_cast<const bf16*>(epi->aux0); p.ldres = epi->lda0;
+      p.gate = static_cast<const bf16*>(epi->aux1); p.ldgate = epi->lda1;
+      break;
+    default: return OWL_ERR_UNSUPPORTED;
+  }
+  const int sms = gemm_sm_count();
+  const int kb_total = static_cast<int>((K + kSmBK - 1) / kSmBK);
+  SmallMPlan plan = plan_smallm(M, N, kb_total, sms);
+  if (const char* e = getenv("OWL_SMALLM_BN")) {
+    const int v = atoi(e);
+    if (v == 64 || v == 128) plan.bn = v;
+  }
+  if (const char* e = getenv("OWL_SMALLM_SPLITS")) {
+    const int v = atoi(e);
+    if (v >= 1 && v <= kb_total) plan.splits = v;
+  }
+  const int bn = plan.bn;
+  p.tiles_n = static_cast<int>((N + bn - 1) / bn);
+  p.kb_total = kb_total;
+  p.kb_per_split = (kb_total + plan.splits - 1) / plan.splits;
+  p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  if (p.splits > 1) {
+    if (!workspace || !aligned16(workspace)) return OWL_ERR_BAD_ARG;
+    const int64_t ws_floats = static_cast<int64_t>(p.tiles_n) * 128 * bn;
+    if (workspace_bytes < ws_floats * 4 + static_cast<int64_t>(p.tiles_n) * 4) return OWL_ERR_BAD_ARG;
+    p.ws = static_cast<float*>(workspace);
+    p.counters = reinterpret_cast<unsigned*>(static_cast<float*>(workspace) + ws_floats);
+  }
+  const int stage_bytes = kSmABytes + bn * kSmBK * 2;
+  int stages = (kSmSmemLimit - 2048) / stage_bytes;
+  if (stages > kSmMaxStages) stages = kSmMaxStages;
+  if (stages > p.kb_per_split + 1 && static_cast<long long>(p.tiles_n) * p.splits <= sms) stages = p.kb_per_split + 1;
+  if (stages < 2) stages = 2;
+  p.stages = stages;
+  const int smem_bytes = 2048 + stages * stage_bytes;
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if ((rc = make_tmap_2d_bf16(&tmA, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), lda, 64, 128)) != OWL_OK) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmB, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldw, 64, bn)) != OWL_OK) return rc;
+  const long long total = static_cast<long long>(p.tiles_n) * p.splits;
+  const int grid = static_cast<int>(total < sms ? total : sms);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  return bn == 128 ? launch_smallm<128>(tmA, tmB, p, grid, smem_bytes, s) : launch_smallm<64>(tmA, tmB, p, grid, smem_bytes, s);
+}
+
+}  // extern "C"

@@ -339,6 +339,10 @@ class _Linear(torch.autograd.Function):
         a = ops.silu(x16) if silu_in else x16
         y = torch.empty(M, N, device=x16.device, dtype=bf16)
         z = None
+        if M <= 128 and K % 8 == 0 and not (torch.is_grad_enabled() and any(ctx.needs_input_grad[:3])):
+            # inference at decode shapes (one frame / one token per call): the weight-streaming split-K GEMM
+            ops.gemm_smallm(a, w16, M, N, K, mode=OWL_EPI_BIAS_SILU if silu_out else OWL_EPI_STORE, bias=b32, out0=y)
+            return y.view(*shp[:-1], N)
         if silu_out:
             z = torch.empty_like(y)
             ops.gemm(OWL_GEMM_NT, a, w16, M, N, K, mode=OWL_EPI_BIAS_SILU, bias=b32, out0=z, out1=y)

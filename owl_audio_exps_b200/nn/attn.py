@@ -149,6 +149,12 @@ class DiT(nn.Module):
 
     def forward(self, x, cond, doc_id=None, kv_cache=None, local_block_mask=None, global_block_mask=None):
         """attn.py:175-191."""
+        from .decode import RingKVCache, dit_decode_forward
+        if isinstance(kv_cache, RingKVCache):
+            # device-state ring cache: the gradient-free decode schedule (nn/decode.py); decode mode only (no mask)
+            if not self.decoding:
+                raise RuntimeError("RingKVCache serves decode mode only: call enable_decoding() first (attn.py:102-109)")
+            return dit_decode_forward(self, x, cond, kv_cache)
         seq_len, device = x.size(1), x.device
         q_offset = kv_cache.length_at(0) if kv_cache is not None else 0
 

@@ -169,6 +169,47 @@ def gemm(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, 
         _lib.check(rc, "owl_gemm_bf16")
 
 
+_SMALLM_WS = {}   # device index -> zeroed workspace tensor (the kernel leaves it zero)
+
+
+def _smallm_workspace(dev: torch.device, N: int) -> torch.Tensor:
+    """Workspace of the split-K reduce, one per device: the decode-regime launches of a device are ordered on one
+    stream (eager) or inside one graph; concurrent decode streams on the SAME device would need one workspace each.
+    Grown (never shrunk) to the widest N seen; allocated outside any graph capture so its address is stable."""
+    key = dev.index
+    need = int(_lib.load().owl_gemm_smallm_workspace_bytes(N))
+    ws = _SMALLM_WS.get(key)
+    if ws is None or ws.numel() < need:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("owl: small-M GEMM workspace must exist before graph capture (run one eager call first)")
+        ws = torch.zeros(max(need, 1 << 22), device=dev, dtype=torch.uint8)
+        _SMALLM_WS[key] = ws
+    return ws
+
+
+@_prof("gemm_smallm", lambda a, w, M, N, K, **k: 2.0 * M * N * K)
+def gemm_smallm(a: torch.Tensor, w: torch.Tensor, M: int, N: int, K: int, *, mode: int = OWL_EPI_STORE,
+                bias: Optional[torch.Tensor] = None, out0: Optional[torch.Tensor] = None,
+                aux0: Optional[torch.Tensor] = None, aux1: Optional[torch.Tensor] = None, rows_per_frame: int = 1) -> None:
+    """out0[M <= 128, N] = epi(a[M, K] . w[N, K]^T + bias): the decode regime's weight-streaming GEMM (owl_gemm_smallm)."""
+    _req(a), _req(w), _req(out0)
+    e = GemmEpilogue()
+    e.mode, e.rows_per_frame = mode, rows_per_frame
+    if bias is not None:
+        _req(bias, torch.float32)
+        e.bias = bias.data_ptr()
+    e.out0, e.ld0 = out0.data_ptr(), _ld(out0)
+    if aux0 is not None:
+        e.aux0, e.lda0 = aux0.data_ptr(), _ld(aux0)
+    if aux1 is not None:
+        e.aux1, e.lda1 = aux1.data_ptr(), _ld(aux1)
+    ws = _smallm_workspace(a.device, N)
+    rc = _lib.load().owl_gemm_smallm(M, N, K, a.data_ptr(), _ld(a), w.data_ptr(), _ld(w), C.byref(e), ws.data_ptr(),
+                                     ws.numel(), _stream())
+    if rc != 0:
+        _lib.check(rc, "owl_gemm_smallm")
+
+
 def gemm_check(layout: int, a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int) -> torch.Tensor:
     lib = _lib.load()
     c = torch.empty(M, N, device=a.device, dtype=torch.float32)
@@ -489,3 +530,58 @@ def attn_bwd(dout, o, q, k, v, lse, *, tokens_per_frame: int, window_frames: int
 def attn_bwd_workspace_elems(B: int, H: int, Lq: int, dh: int) -> int:
     """fp32 elements of the dq accumulator workspace owl_attn_bwd needs (query rows padded to 128)."""
     return B * H * ((Lq + 127) // 128 * 128) * dh
+
+
+# ------------------------------------------------------------------------------------------------
+# decode regime: ring KV cache with device-resident state (owl_qk_norm_rope_decode / owl_attn_decode)
+# ------------------------------------------------------------------------------------------------
+@_prof("qk_norm_rope_decode")
+def qk_norm_rope_decode(qkv, cos, sin, state, q, k_cache, v_cache, H: int, eps: float):
+    """qkv [B, L, 3*H*dh] -> q [B, H, L, dh]; new K / V rows -> ring slots of k_cache / v_cache [B, H, cap, dh]
+    behind the cached rows; slot and RoPE position come from the device `state` (int32[4])."""
+    B, L, three_d = qkv.shape
+    dh = three_d // (3 * H)
+    _req(qkv), _req(q), _req(k_cache), _req(v_cache), _req(state, torch.int32)
+    if k_cache.stride() != v_cache.stride() or k_cache.stride(3) != 1 or k_cache.stride(2) != dh:
+        raise RuntimeError("ring cache buffers must be [B, H, cap, dh] with contiguous rows and equal strides")
+    rc = _lib.load().owl_qk_norm_rope_decode(qkv.data_ptr(), cos.data_ptr(), sin.data_ptr(), cos.shape[0], state.data_ptr(),
+                                             q.data_ptr(), q.stride(0), q.stride(1), k_cache.data_ptr(), v_cache.data_ptr(),
+                                             k_cache.stride(0), k_cache.stride(1), k_cache.shape[2], B, L, H, dh, eps,
+                                             _stream())
+    _lib.check(rc, "owl_qk_norm_rope_decode")
+
+
+_DECODE_WS = {}
+
+
+def _decode_workspace(dev, B: int, H: int, cap: int, dh: int) -> torch.Tensor:
+    key = dev.index
+    need = int(_lib.load().owl_attn_decode_workspace_bytes(B, H, cap, dh))
+    ws = _DECODE_WS.get(key)
+    if ws is None or ws.numel() < need:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("owl: decode attention workspace must exist before graph capture (run one eager call first)")
+        ws = torch.zeros(need, device=dev, dtype=torch.uint8)
+        _DECODE_WS[key] = ws
+    return ws
+
+
+@_prof("attn_decode")
+def attn_decode(q, k_cache, v_cache, state, vis_rows: int = 0, out=None):
+    """q [B, H, Lq <= 128, dh] against the ring cache (cached rows + the Lq rows just written), no mask ->
+    o [B, Lq, H*dh].  vis_rows > 0: only the last vis_rows rows of [cache, new] (local layers)."""
+    B, H, Lq, dh = q.shape
+    o = torch.empty(B, Lq, H * dh, device=q.device, dtype=bf16) if out is None else out
+    cap = k_cache.shape[2]
+    ws = _decode_workspace(q.device, B, H, cap, dh)
+    qp, q_sb, q_sh = _hm(q)
+    rc = _lib.load().owl_attn_decode(qp, q_sb, q_sh, k_cache.data_ptr(), v_cache.data_ptr(), k_cache.stride(0),
+                                     k_cache.stride(1), cap, state.data_ptr(), vis_rows, o.data_ptr(), o.stride(0),
+                                     o.stride(1), B, H, Lq, dh, ws.data_ptr(), ws.numel(), _stream())
+    _lib.check(rc, "owl_attn_decode")
+    return o
+
+
+def decode_state_advance(state, commit_rows: int, drop_rows: int, cap: int) -> None:
+    _lib.check(_lib.load().owl_decode_state_advance(state.data_ptr(), commit_rows, drop_rows, cap, _stream()),
+               "owl_decode_state_advance")

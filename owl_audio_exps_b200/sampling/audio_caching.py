@@ -24,7 +24,10 @@ def get_deltas(custom_schedule):
 
 class AudioCachingSampler:
     def __init__(self, n_steps: int = 16, num_tokens: int = 120, noise_prev: float = 0.2, custom_schedule=None,
-                 max_window=None, noise_fn=None, graph_decode: bool = True, graph_min_steps: int = 10) -> None:
+                 max_window=None, noise_fn=None, graph_decode: bool = True, graph_min_steps: int = 10,
+                 use_ring: bool = True) -> None:
+        self.use_ring = use_ring        # device-state ring cache + ONE decode graph per rollout (nn/decode.py)
+        self.last_ring = None
         self.n_steps = n_steps
         self.num_tokens = num_tokens
         self.noise_prev = noise_prev
@@ -66,6 +69,73 @@ class AudioCachingSampler:
         del graph, v
         return out
 
+    # ---- ring path: ONE graph of the model call for the whole rollout (nn/decode.py) ----------------------------
+    def _ring_ok(self, model, b, rows, x):
+        from ..nn.attn import DiT
+        return (self.graph_decode and self.use_ring and x.is_cuda and isinstance(getattr(model, "transformer", None), DiT)
+                and b * rows <= 128 and x.dtype in (torch.bfloat16, torch.float32))
+
+    def _ring_window_rows(self, init_frames, n_new, rows):
+        """Most rows the cache holds when a model call starts, by replaying the loop's commit / truncate bookkeeping."""
+        frames, n_lat, most = init_frames, 1, init_frames
+        for _ in range(n_new):
+            frames += 1
+            n_lat += 1
+            if self.max_window is not None and n_lat > self.max_window:
+                frames -= 1
+            most = max(most, frames)
+        return (most + 1) * rows
+
+    def _ring_rollout(self, model, cache, statics, call, n_new, rows, dt, fresh, renoise, extra_inputs, commit_call=None):
+        """statics = [cur, t, *controls] (device buffers the captured call reads); call(ring) -> velocity tensor.
+        Per new latent / frame: n_steps replays with the Euler update in between, one more replay on the re-noised
+        result to write its K/V rows, then the ring state is advanced (commit + optional truncate).  `commit_call`: the
+        model call whose K/V rows are kept when it differs from `call` (guidance evaluates the model twice per step; the
+        cache commit of av_caching_v2.py:68-76 is one conditional evaluation)."""
+        from ..nn.decode import RingKVCache
+        cur, t = statics[0], statics[1]
+        ring = RingKVCache.from_cache(cache, self._ring_window_rows(len(cache) // rows, n_new, rows), rows)
+        extra_inputs(0)
+        cur.copy_(fresh(0))
+        t.fill_(1.0)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            call(ring)                                   # eager once: stages weights, creates the kernel workspaces
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        if self._pool is None:
+            self._pool = torch.cuda.graph_pool_handle()
+        with torch.cuda.graph(graph, pool=self._pool):
+            v = call(ring)
+        commit_graph = graph
+        if commit_call is not None:
+            commit_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(commit_graph, pool=self._pool):
+                commit_call(ring)
+        out, n_lat = [], 1
+        for idx in range(n_new):
+            if idx > 0:
+                extra_inputs(idx)
+                cur.copy_(fresh(idx))
+                t.fill_(1.0)
+            for step in range(self.n_steps):
+                graph.replay()
+                cur.copy_(cur - dt[step] * v.to(cur.dtype))      # the eager loop's arithmetic, into the graph's inputs
+                t.copy_(t - dt[step])
+            done = cur.clone()
+            out.append(done)
+            cur.copy_(renoise(done))
+            t.fill_(self.noise_prev)
+            commit_graph.replay()                        # writes this latent's K/V rows behind the cached ones
+            ring.commit(rows)
+            n_lat += 1
+            if self.max_window is not None and n_lat > self.max_window:
+                ring.truncate(1, front=False)
+        self.last_ring = ring
+        del graph, commit_graph
+        return out
+
     def _randn(self, shape, like):
         if self.noise_fn is not None:
             return self.noise_fn(tuple(shape), like)
@@ -102,6 +172,18 @@ class AudioCachingSampler:
         commit(x)
         model.transformer.enable_decoding()
         try:
+            if self._ring_ok(model, b, 1, x):
+                cur = torch.empty(b, 1, channels, device=x.device, dtype=x.dtype)
+                t = torch.empty(b, 1, device=x.device, dtype=x.dtype)
+                new = self._ring_rollout(
+                    model, cache, [cur, t], lambda ring: model(cur, t, doc_id=None, kv_cache=ring), self.num_tokens, 1, dt,
+                    fresh=lambda i: self._randn((b, 1, channels), x), renoise=lambda z: self.zlerp(z, self.noise_prev),
+                    extra_inputs=lambda i: None)
+                latents.extend(new)
+                full = torch.cat(latents, dim=1)
+                if decode_fn is not None:
+                    return full, decode_fn(full * vae_scale)
+                return full
             for _ in range(self.num_tokens):
                 cur = self._randn((b, 1, channels), x)
                 t = x.new_ones(b, 1)

@@ -15,10 +15,10 @@ from .schedulers import get_sd3_euler
 class AVCachingSamplerV2(AudioCachingSampler):
     def __init__(self, n_steps: int = 16, cfg_scale: float = 1.3, num_frames: int = 60, noise_prev: float = 0.2,
                  max_window=None, custom_schedule=None, noise_fn=None, graph_decode: bool = True,
-                 graph_min_steps: int = 10) -> None:
+                 graph_min_steps: int = 10, use_ring: bool = True) -> None:
         super().__init__(n_steps=n_steps, num_tokens=num_frames, noise_prev=noise_prev, custom_schedule=custom_schedule,
                          max_window=max_window, noise_fn=noise_fn, graph_decode=graph_decode,
-                         graph_min_steps=graph_min_steps)
+                         graph_min_steps=graph_min_steps, use_ring=use_ring)
         self.cfg_scale = cfg_scale
         self.num_frames = num_frames
 
@@ -47,6 +47,31 @@ class AVCachingSamplerV2(AudioCachingSampler):
         n_frames = min(self.num_frames, mouse.size(1) - init_len)
         model.transformer.enable_decoding()
         try:
+            if self._ring_ok(model, b, rows, x):
+                cur = torch.empty_like(x[:, :1])
+                t = torch.empty(b, 1, device=x.device, dtype=x.dtype)
+                m = torch.empty_like(mouse[:, :1])
+                bt = torch.empty_like(btn[:, :1])
+                m0, bt0 = torch.zeros_like(m), torch.zeros_like(bt)
+
+                def controls(idx):
+                    at = init_len + idx
+                    m.copy_(mouse[:, at:at + 1])
+                    bt.copy_(btn[:, at:at + 1])
+
+                def call(ring):
+                    v = model(cur, t, m, bt, kv_cache=ring)
+                    if self.cfg_scale != 1.0:
+                        v0 = model(cur, t, m0, bt0, kv_cache=ring)
+                        v = v0 + self.cfg_scale * (v - v0)
+                    return v
+
+                commit_call = (lambda ring: model(cur, t, m, bt, kv_cache=ring)) if self.cfg_scale != 1.0 else None
+                new = self._ring_rollout(model, cache, [cur, t, m, bt], call, n_frames, rows, dt,
+                                         fresh=lambda i: self._randn(x[:, :1].shape, x),
+                                         renoise=lambda z: self.zlerp(z, self.noise_prev), extra_inputs=controls,
+                                         commit_call=commit_call)
+                return torch.cat(latents + new, dim=1)
             for idx in range(n_frames):
                 cur = self._randn(x[:, :1].shape, x)
                 t = x.new_ones(b, 1)

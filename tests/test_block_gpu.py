@@ -221,6 +221,65 @@ def test_av_shape_T65_vs_oracle():
     assert worst[0] <= TOL, worst
 
 
+def _stack_vs_oracle(cfg, B, F_, seed, train=False, doc=None):
+    """Random-init stack (weights rounded to bf16 on both sides) fwd + bwd on the CUDA path against the fp32 CPU oracle."""
+    N = _nn()
+    torch.manual_seed(seed)
+    model = N.DiT(cfg)
+    with torch.no_grad():
+        for p in model.parameters():
+            p.copy_(p.to(torch.bfloat16).float())
+    W = {k: v.requires_grad_(True) for k, v in _oracle_weights(model).items()}
+    rope = [(b.attn.rope.cos.clone(), b.attn.rope.sin.clone()) for b in model.blocks]
+    model = model.to(DEV)
+    if train:
+        model.train()
+    g = torch.Generator().manual_seed(seed)
+    d, L = cfg.d_model, F_ * cfg.tokens_per_frame
+    x = torch.randn(B, L, d, generator=g).to(torch.bfloat16)
+    cond = torch.randn(B, F_, d, generator=g).to(torch.bfloat16)
+    dy = torch.randn(B, L, d, generator=g).to(torch.bfloat16)
+    xo, co = x.float().requires_grad_(True), cond.float().requires_grad_(True)
+    yo = O.dit_forward(xo, co, W, cfg, rope, doc_id=doc)
+    yo.backward(dy.float())
+    xg, cg = x.to(DEV).requires_grad_(True), cond.to(DEV).requires_grad_(True)
+    y = model(xg, cg, None if doc is None else doc.to(DEV))
+    y.backward(dy.to(DEV))
+    assert relerr(y, yo) <= TOL
+    assert relerr(xg.grad, xo.grad) <= TOL and relerr(cg.grad, co.grad) <= TOL
+    worst = max((relerr(p.grad, W[k].grad), k) for k, p in model.named_parameters())
+    assert worst[0] <= TOL, worst
+
+
+def test_av_real_geometry_vs_oracle():
+    """configs/av_v5_8x8_sf.yml / causvid.yml at FULL width: d=1536, H=24 (dh=64), T=65, 16 frames (L=1040), 2 layers
+    (global + local with a binding 4-frame window), ortho RoPE."""
+    cfg = types.SimpleNamespace(d_model=1536, n_heads=24, n_layers=2, tokens_per_frame=65, n_frames=16, sample_size=8,
+                                causal=True, has_audio=True, rope_impl="ortho", local_window=4, global_window=None,
+                                backbone="dit")
+    _stack_vs_oracle(cfg, B=1, F_=16, seed=3)
+
+
+def test_dit_v4_5B_geometry_checkpointed_vs_oracle():
+    """configs/dit_v4_5B.yml block geometry: d=2560, H=20 (dh=128), T=64, motion RoPE, per-block gradient checkpointing
+    (attn.py:187-188) in training mode, 2 layers, 12 frames (L=768: six 128-row tiles on the dh=128 kernels), packed
+    documents (doc ids, attn.py:52-55)."""
+    cfg = types.SimpleNamespace(d_model=2560, n_heads=20, n_layers=2, tokens_per_frame=64, n_frames=12, sample_size=8,
+                                causal=True, has_audio=False, rope_impl="motion", rope_ats_delta=2.0, local_window=3,
+                                global_window=None, backbone="dit", gradient_checkpointing=True)
+    doc = torch.tensor([[0] * 5 + [1] * 7], dtype=torch.int32)
+    _stack_vs_oracle(cfg, B=1, F_=12, seed=4, train=True, doc=doc)
+
+
+def test_dit_v4_geometry_packed_docs_vs_oracle():
+    """configs/dit_v4.yml block geometry: d=1536, H=24, T=64, motion RoPE, packed documents, L=1536 (24 frames), 2 layers."""
+    cfg = types.SimpleNamespace(d_model=1536, n_heads=24, n_layers=2, tokens_per_frame=64, n_frames=24, sample_size=8,
+                                causal=True, has_audio=False, rope_impl="motion", rope_ats_delta=2.0, local_window=4,
+                                global_window=None, backbone="dit")
+    doc = torch.tensor([[0] * 9 + [1] * 4 + [2] * 11], dtype=torch.int32)
+    _stack_vs_oracle(cfg, B=1, F_=24, seed=5, doc=doc)
+
+
 def test_gradient_checkpointing_same_grads():
     """attn.py:187-188 (dit_v4_5B.yml: gradient_checkpointing true): recompute path == stored path."""
     fx = load_golden("av_T5_ortho")

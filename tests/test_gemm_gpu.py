@@ -147,3 +147,75 @@ def test_gemm_single_cta_and_cta_pair(monkeypatch, ctas, layout, M, N, K):
     torch.cuda.synchronize()
     assert relerr(out, ref + bias) <= 1e-2
     assert relerr(outf, ref) <= 1e-4
+
+
+# ------------------------------------------------------------------------------------------------
+# weight-streaming small-M GEMM of the decode regime (owl_gemm_smallm)
+# ------------------------------------------------------------------------------------------------
+SMALLM_SHAPES = [
+    # M, N, K: the Linears of one AV decode evaluation (65 tokens, d = 1536), the conditioning bank at one frame,
+    # the audio model's single token, and ragged / tiny shapes
+    (65, 1536, 1536), (65, 4608, 1536), (65, 6144, 1536), (65, 1536, 6144), (1, 6 * 1536 * 4, 1536),
+    (1, 1024, 1024), (1, 3072, 1024), (128, 192, 320), (7, 64, 64), (130 // 2, 72, 136),
+]
+
+
+def _smallm_ref(mode, A, W, bias, res, gate, T):
+    y = A.float() @ W.float().t() + (bias if bias is not None else 0.0)
+    if mode == 0:
+        return y
+    y = y.to(bf16).float()
+    if mode == 1:
+        return torch.nn.functional.silu(y)
+    return res.float() + gate.float().repeat_interleave(T, dim=0) * y
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("M,N,K", SMALLM_SHAPES)
+def test_gemm_smallm(mode, M, N, K):
+    import os
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device="cpu").manual_seed(M + 3 * N + 7 * K + mode)
+    A = torch.randn(M, K, generator=g).to(bf16).to(dev)
+    W = (torch.randn(N, K, generator=g) * K ** -0.5).to(bf16).to(dev)
+    bias = torch.randn(N, generator=g).to(dev)
+    T = 65 if M % 65 == 0 else 1
+    res = torch.randn(M, N, generator=g).to(bf16).to(dev)
+    gate = torch.randn(M // T, N, generator=g).to(bf16).to(dev)
+    ref = _smallm_ref(mode, A, W, bias, res, gate, T)
+    kw = dict(mode=mode, bias=bias)
+    if mode == 2:
+        kw.update(aux0=res, aux1=gate, rows_per_frame=T)
+    outs = []
+    for forced in (None, "1", "3"):            # the planner's choice, no split, an odd split count
+        if forced is None:
+            os.environ.pop("OWL_SMALLM_SPLITS", None)
+        else:
+            os.environ["OWL_SMALLM_SPLITS"] = forced
+        try:
+            for rep in range(2):               # twice: the kernel must leave its workspace zeroed
+                out = torch.full((M, N), float("nan"), device=dev, dtype=bf16)
+                ops.gemm_smallm(A, W, M, N, K, out0=out, **kw)
+                torch.cuda.synchronize()
+                assert relerr(out, ref) <= 1e-2, (forced, rep)
+                outs.append(out)
+        finally:
+            os.environ.pop("OWL_SMALLM_SPLITS", None)
+    from owl_audio_exps_b200 import ops as O
+    for ws in O._SMALLM_WS.values():
+        assert int(ws.count_nonzero()) == 0
+    # same problem through the training GEMM (store mode): both tensor-core paths agree to rounding
+    if mode == 0:
+        big = torch.empty(M, N, device=dev, dtype=bf16)
+        ops.gemm(0, A, W, M, N, K, mode=0, bias=bias, out0=big)
+        assert relerr(outs[0], big) <= 1e-2
+
+
+def test_gemm_smallm_rejects_large_m():
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    A = torch.zeros(129, 64, device=dev, dtype=bf16)
+    W = torch.zeros(64, 64, device=dev, dtype=bf16)
+    with pytest.raises(RuntimeError):
+        ops.gemm_smallm(A, W, 129, 64, 64, out0=torch.empty(129, 64, device=dev, dtype=bf16))

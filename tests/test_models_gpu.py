@@ -153,31 +153,38 @@ def test_audio_caching_sampler_matches_reference_rollout():
         z = next(draws)
         assert tuple(z.shape) == tuple(shape)
         return z.to(device=like.device, dtype=like.dtype)
-    sampler = AudioCachingSampler(n_steps=len(fx["schedule"]), num_tokens=fx["num_tokens"], noise_prev=fx["noise_prev"],
-                                  custom_schedule=list(fx["schedule"]), max_window=fx["max_window"], noise_fn=noise_fn)
-    out = sampler(model, fx["x"].to(DEV))
-    assert next(draws, None) is None
-    assert out.shape == fx["out"].shape
-    assert relerr(out, fx["out"]) <= 3e-2
-    assert not model.transformer.decoding
+    for ring in (True, False):      # ONE ring-cache graph per rollout / the per-latent graph on the growing cache
+        draws = iter(fx["draws"])
+        sampler = AudioCachingSampler(n_steps=len(fx["schedule"]), num_tokens=fx["num_tokens"], noise_prev=fx["noise_prev"],
+                                      custom_schedule=list(fx["schedule"]), max_window=fx["max_window"], noise_fn=noise_fn,
+                                      use_ring=ring, graph_min_steps=2)
+        out = sampler(model, fx["x"].to(DEV))
+        assert next(draws, None) is None
+        assert out.shape == fx["out"].shape
+        assert relerr(out, fx["out"]) <= 3e-2, ring
+        assert not model.transformer.decoding
+        assert (sampler.last_ring is not None) == ring
     # default schedule + default noise source run end to end
     out = AudioCachingSampler(n_steps=2, num_tokens=2)(model, fx["x"].to(DEV))
     assert out.shape == (2, 8, 64) and torch.isfinite(out).all()
 
 
 def test_sampler_graph_replay_equals_eager_steps():
-    """The per-latent CUDA graph of the decode step launches the same kernels as the eager loop: identical latents."""
+    """The per-latent CUDA graph of the decode step launches the same kernels as the eager loop: identical latents.  The
+    ring path (ONE graph per rollout, weight-streaming GEMMs, split-KV attention) is a different kernel schedule: same
+    latents to the rollout tolerance."""
     from owl_audio_exps_b200.sampling import AudioCachingSampler
     core = load_golden("audiorft_core")
     model = _core(cfg_of(core), core["state"], core["rope"]).eval()
     x = torch.randn(2, 5, 64, device=DEV)
     outs = []
-    for graph in (False, True):
+    for graph, ring in ((False, False), (True, False), (True, True)):
         g = torch.Generator(device=DEV).manual_seed(11)
         noise_fn = lambda shape, like: torch.randn(*shape, device=like.device, dtype=like.dtype, generator=g)  # noqa: E731
-        outs.append(AudioCachingSampler(n_steps=5, num_tokens=4, max_window=6, noise_fn=noise_fn,
-                                        graph_decode=graph, graph_min_steps=2)(model, x))
+        outs.append(AudioCachingSampler(n_steps=5, num_tokens=4, max_window=6, noise_fn=noise_fn, graph_decode=graph,
+                                        graph_min_steps=2, use_ring=ring)(model, x))
     assert torch.equal(outs[0], outs[1])
+    assert relerr(outs[2], outs[0]) <= 3e-2
 
 
 def test_gamerft_audio_core_golden():
@@ -244,7 +251,7 @@ def test_step_condition_posenc_embeddings_vs_oracle():
     assert torch.equal(pe(x), x + pe.p.unsqueeze(0))
 
 
-@pytest.mark.parametrize("graph", [False, True])
+@pytest.mark.parametrize("graph", [False, True, "ring"])
 def test_av_caching_sampler_matches_reference_rollout(graph):
     """AVCachingSamplerV2 on the decode path (T=4 tokens per frame, CFG on the controls, window truncation) vs the reference
     sampler's recorded rollout; eager and with the per-frame CUDA graph (two model evaluations inside it).  3 frames x 3
@@ -262,8 +269,8 @@ def test_av_caching_sampler_matches_reference_rollout(graph):
         return z.to(device=like.device, dtype=like.dtype)
     sampler = AVCachingSamplerV2(n_steps=len(fx["schedule"]), cfg_scale=fx["cfg_scale"], num_frames=fx["num_frames"],
                                  noise_prev=fx["noise_prev"], max_window=fx["max_window"],
-                                 custom_schedule=list(fx["schedule"]), noise_fn=noise_fn, graph_decode=graph,
-                                 graph_min_steps=2)
+                                 custom_schedule=list(fx["schedule"]), noise_fn=noise_fn, graph_decode=bool(graph),
+                                 graph_min_steps=2, use_ring=graph == "ring")
     out = sampler(model, fx["x"].to(DEV), fx["mouse"].to(DEV), fx["btn"].to(DEV))
     assert next(draws, None) is None
     assert out.shape == fx["out"].shape

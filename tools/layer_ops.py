@@ -47,7 +47,7 @@ def main():
     a, b, cc = mod[:, :d], mod[:, d:2 * d], mod[:, 2 * d:3 * d]
     rstd = torch.rand(M, device=dev) + 0.5
     qkv = g(B, L, 3 * d)
-    cos, sin = torch.rand(4096, dh // 2, device=dev), torch.rand(4096, dh // 2, device=dev)
+    cos, sin = torch.rand(max(4096, L), dh // 2, device=dev), torch.rand(max(4096, L), dh // 2, device=dev)
     q, k, v = (torch.empty(B, H, L, dh, device=dev, dtype=bf16) for _ in range(3))
     rq, rk = ops.qk_norm_rope_fwd(qkv, cos, sin, 0, H, 1e-6, q, k, v)
     mk = dict(tokens_per_frame=T, window_frames=0, q_offset=0, causal=True, doc_id=None)
