@@ -48,6 +48,13 @@ WORKLOADS["dit_v4_5B"] = dict(cfg=dict(d_model=2560, n_heads=20, n_layers=36, to
                                        sample_size=8, causal=True, has_audio=False, rope_impl="motion", rope_ats_delta=2.0,
                                        local_window=16, global_window=None, backbone="dit", gradient_checkpointing=True),
                               B=1, F=1536, name="configs/dit_v4_5B.yml")
+# configs/causvid.yml: game_rft_audio, 24 layers, d=1536, H=24, T=65 (8x8 video tokens + 1 audio token), window 16 frames,
+# B=1 causal rollout (inference/causvid_pipeline.py; KV-cached per-frame loop of av_caching_v2.py:89-140)
+WORKLOADS["causvid"] = dict(cfg=dict(d_model=1536, n_heads=24, n_layers=24, tokens_per_frame=65, n_frames=16, sample_size=8,
+                                     channels=64, audio_channels=64, n_buttons=11, n_mouse_axes=2, causal=True,
+                                     uncond=False, has_audio=True, rope_impl="ortho", local_window=16, global_window=None,
+                                     backbone="dit", cfg_prob=0.0), B=1, F=16, name="configs/causvid.yml")
+METRIC_ROLLOUT = "rollout frames/sec (causvid.yml KV-cached causal rollout, 1 flow step + cache commit per frame), whole job"
 METRIC = "train tokens/sec (audio DiT stack fwd+bwd+grad all-reduce), whole job"
 
 
@@ -389,6 +396,250 @@ def run_owl(args):
         os._exit(0)
 
 
+
+# ------------------------------------------------------------------------------------------------
+# causvid.yml: causal rollout inference (frames/s)
+# ------------------------------------------------------------------------------------------------
+def cpu_rollout_frame_time(n_layers_sample=2, window=15):
+    """Seconds per generated frame on the host cores: the oracle port's KV-cached decode of one 65-token frame against a
+    `window`-frame cache (one denoise evaluation + one cache-commit evaluation), `n_layers_sample` layers, scaled by the
+    caller.  fp32 torch CPU."""
+    from oracle import dit_oracle as O
+    import owl_audio_exps_b200.nn.rope as R
+    w = WORKLOADS["causvid"]
+    cfg = types.SimpleNamespace(**{**w["cfg"], "n_layers": n_layers_sample, "n_frames": window + 4})
+    torch.manual_seed(0)
+    d, T = cfg.d_model, cfg.tokens_per_frame
+    W = {}
+    for i in range(n_layers_sample):
+        pre = f"blocks.{i}."
+        for name, (n, k) in {"attn.qkv": (3 * d, d), "attn.out": (d, d), "mlp.fc1": (4 * d, d), "mlp.fc2": (d, 4 * d),
+                             "adaln1.fc": (2 * d, d), "gate1.fc_c": (d, d), "adaln2.fc": (2 * d, d),
+                             "gate2.fc_c": (d, d)}.items():
+            W[pre + name + ".weight"] = torch.randn(n, k) * k ** -0.5
+            W[pre + name + ".bias"] = torch.zeros(n)
+    rope = R.get_rope_cls(cfg.rope_impl)(cfg)
+    tables = [(rope.cos, rope.sin)] * n_layers_sample
+    with torch.no_grad():
+        cache = O.OracleKVCache(n_layers_sample, T)
+        cache.should_update = True
+        O.dit_forward(torch.randn(1, window * T, d), torch.randn(1, window, d), W, cfg, tables, kv_cache=cache)
+        x, c = torch.randn(1, T, d), torch.randn(1, 1, d)
+
+        def frame():
+            cache.should_update = False
+            O.dit_forward(x, c, W, cfg, tables, kv_cache=cache, decoding=True)          # denoise evaluation
+            cache.should_update = True
+            O.dit_forward(x, c, W, cfg, tables, kv_cache=cache, decoding=True)          # cache-commit evaluation
+            cache.truncate(1)
+        frame()
+        t0 = time.perf_counter()
+        n = 3
+        for _ in range(n):
+            frame()
+        return (time.perf_counter() - t0) / n
+
+
+def run_causvid(args):
+    """configs/causvid.yml rollout.  Per GPU one independent replica on its own stream (north_star: 'inference rollout runs
+    per-GPU on independent streams'); no collective on the data path, frames/s adds up over ranks."""
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    w = WORKLOADS["causvid"]
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        torch.set_num_threads(host_threads())
+        dt = cpu_rollout_frame_time(2) * w["cfg"]["n_layers"] / 2
+        val = 1.0 / dt
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC_ROLLOUT, "value": val, "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": w["name"], "note": "CPU reference arm: oracle port of the DiT stack's KV-cached decode "
+                       "(2 evaluations of one 65-token frame against a 15-frame cache), 2 of 24 layers scaled to full depth"},
+            "cpu_baseline": {"value": val, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": "3 frames x 2 evaluations, 2 of 24 layers, fp32 torch CPU"},
+            "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}),
+            flush=True)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the sm_100a kernels are the only implementation)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from owl_audio_exps_b200 import functional as OF, ops
+    from owl_audio_exps_b200.models import GameRFTAudioCore
+    from owl_audio_exps_b200.nn.decode import RingKVCache
+    import owl_audio_exps_b200.nn as N
+    window, frames_per_step = w["F"], 16            # a "step" = 16 generated frames
+    n_warm = max(args.warmup, 3)
+    total_frames = (n_warm + 2 * args.steps + 4) * frames_per_step
+    cfg = types.SimpleNamespace(**{**w["cfg"], "n_frames": window + total_frames + 2})   # RoPE table spans the rollout
+    torch.manual_seed(0)
+    model = GameRFTAudioCore(cfg).to(dev).bfloat16().eval()          # causvid_pipeline.py:36 (.cuda().bfloat16().eval())
+    n_params = sum(p.numel() for p in model.parameters())
+    T, C = cfg.tokens_per_frame, cfg.channels
+    g = torch.Generator().manual_seed(7 + rank)
+    ctx = window - 1
+    hist = torch.randn(1, ctx, C, 8, 8, generator=g).to(dev, torch.bfloat16)
+    aud = torch.randn(1, ctx, cfg.audio_channels, generator=g).to(dev, torch.bfloat16)
+    mouse_h = torch.randn(total_frames + ctx, 2, generator=g).to(torch.bfloat16).pin_memory()
+    btn_h = (torch.rand(total_frames + ctx, 11, generator=g) > 0.5).to(torch.bfloat16).pin_memory()
+    out_h = torch.empty(C * 64 + cfg.audio_channels, dtype=torch.bfloat16).pin_memory()
+    alpha = 0.2
+    with torch.no_grad(), OF.frozen_weights():
+        # prefill of the noised context with cache updates on (masked, training-shape kernels), then the ring
+        cache = N.KVCache(cfg)
+        cache.reset(1)
+        cache.enable_cache_updates()
+        t_ctx = torch.full((1, ctx), alpha, device=dev, dtype=torch.bfloat16)
+        model(hist, aud, t_ctx, mouse_h[:ctx].to(dev)[None], btn_h[:ctx].to(dev)[None], kv_cache=cache)
+        cache.disable_cache_updates()
+        model.transformer.enable_decoding()
+        ring = RingKVCache.from_cache(cache, window_rows=window * T, new_rows=T)
+        x_in = torch.empty(1, 1, C, 8, 8, device=dev, dtype=torch.bfloat16)
+        a_in = torch.empty(1, 1, cfg.audio_channels, device=dev, dtype=torch.bfloat16)
+        t_in = torch.empty(1, 1, device=dev, dtype=torch.bfloat16)
+        m_in = torch.empty(1, 1, 2, device=dev, dtype=torch.bfloat16)
+        b_in = torch.empty(1, 1, 11, device=dev, dtype=torch.bfloat16)
+        x_in.normal_(), a_in.normal_(), t_in.fill_(1.0), m_in.zero_(), b_in.zero_()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            n0 = ops.launch_count()
+            model(x_in, a_in, t_in, m_in, b_in, kv_cache=ring)
+            launches_per_eval = ops.launch_count() - n0
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            v_x, v_a = model(x_in, a_in, t_in, m_in, b_in, kv_cache=ring)
+        out_d = torch.empty(C * 64 + cfg.audio_channels, device=dev, dtype=torch.bfloat16)
+        frame_no = [0]
+
+        def one_frame(from_host):
+            i = frame_no[0]
+            frame_no[0] += 1
+            if from_host:                                   # this frame's controls arrive from pinned host memory
+                m_in.copy_(mouse_h[ctx + i].view(1, 1, 2), non_blocking=True)
+                b_in.copy_(btn_h[ctx + i].view(1, 1, 11), non_blocking=True)
+            x_in.normal_(), a_in.normal_(), t_in.fill_(1.0)
+            graph.replay()                                  # ONE flow step (causvid.yml rollout_steps: 1): x <- x - 1.0 * v
+            x_in.sub_(v_x), a_in.sub_(v_a)
+            out_d[:C * 64].copy_(x_in.view(-1)), out_d[C * 64:].copy_(a_in.view(-1))
+            # re-noise the new frame to alpha (zlerp, causvid_pipeline.py:15-16) and run it once more to write its K/V rows
+            x_in.mul_(1.0 - alpha).add_(torch.randn_like(x_in), alpha=alpha)
+            a_in.mul_(1.0 - alpha).add_(torch.randn_like(a_in), alpha=alpha)
+            t_in.fill_(alpha)
+            graph.replay()
+            ring.commit(T)
+            if ring.n_frames() >= window:
+                ring.truncate(1)
+            if from_host:
+                out_h.copy_(out_d, non_blocking=True)       # the generated latents go back to the host every frame
+                torch.cuda.current_stream().synchronize()   # the caller consumes the frame before producing the next controls
+
+        def barrier():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+
+        def timed(n_frames, from_host):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record()
+            for _ in range(n_frames):
+                one_frame(from_host)
+            e1.record()
+            barrier()
+            ms = e0.elapsed_time(e1)
+            if world > 1:
+                tt = torch.tensor([ms], device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                ms = tt.item()
+            return ms
+
+        for _ in range(n_warm * frames_per_step):
+            one_frame(False)
+        with ClockSampler(local) as clk:
+            ms = timed(args.steps * frames_per_step, False)
+        for _ in range(4):
+            one_frame(True)
+        ms_e2e = timed(args.steps * frames_per_step, True)
+        # one decode evaluation alone (graph replays back to back), for the roofline of the weight-streaming schedule
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            graph.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        eval_ms = e0.elapsed_time(e1) / 20
+        # the pipeline's own call shape (inference/causvid_pipeline.py:112-163): the whole 16-frame window through the model,
+        # sampling_steps = 1, no cache
+        model.transformer.disable_decoding()
+        xw = torch.randn(1, window, C, 8, 8, device=dev, dtype=torch.bfloat16)
+        aw = torch.randn(1, window, cfg.audio_channels, device=dev, dtype=torch.bfloat16)
+        tw = torch.full((1, window), alpha, device=dev, dtype=torch.bfloat16)
+        mw, bw = mouse_h[:window].to(dev)[None], btn_h[:window].to(dev)[None]
+        for _ in range(3):
+            model(xw, aw, tw, mw, bw)
+        gw = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gw):
+            model(xw, aw, tw, mw, bw)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(10):
+            gw.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        window_ms = e0.elapsed_time(e1) / 10
+    n_frames = args.steps * frames_per_step
+    value = world * n_frames / (ms * 1e-3)
+    e2e = world * n_frames / (ms_e2e * 1e-3)
+    if rank == 0:
+        pk = _peaks()
+        weight_bytes = 2.0 * n_params
+        ach = weight_bytes / (eval_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC_ROLLOUT, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": n_warm, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": w["name"], "model": "GameRFTAudioCore (24 layers, d=1536, H=24, 65 tokens per frame)",
+                       "params": n_params, "batch": 1, "window_frames": window, "frames_per_step": frames_per_step,
+                       "flow_steps_per_frame": 1, "evaluations_per_frame": 2, "parallelism": f"{world} independent replicas",
+                       "cuda_graph": "one graph of the model call, replayed for every denoise step and cache commit",
+                       "l2": "2 GB of weights per evaluation exceed the 126 MB L2; no flush"},
+            "ms_per_frame": ms / n_frames, "ms_per_evaluation": eval_ms, "launches_per_evaluation": launches_per_eval,
+            "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": frames_per_step * (2 + 11) * 2,
+                    "d2h_bytes_per_step": frames_per_step * out_h.numel() * 2, "ms_per_frame": ms_e2e / n_frames},
+            "gpu_launches": launches_per_eval * 2 * n_frames,
+            "roofline": {"bound": "hbm", "kernel": "gemm_smallm_kernel (weight-streaming split-K, tcgen05) over one model evaluation",
+                         "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
+                         "traffic": None, "peak_source": pk["src"],
+                         "algorithmic_bytes_per_evaluation": weight_bytes,
+                         "note": "achieved = bf16 weight bytes of the model (every weight is read once per evaluation) / "
+                                 "time of one evaluation (graph replays back to back)"},
+            "other": {"pipeline_full_window_ms": window_ms, "pipeline_full_window_frames_per_s": 1e3 / window_ms,
+                      "note": "inference/causvid_pipeline.py's own call: all 16 frames through the model per new frame"},
+            "clocks": clk.summary(),
+        }
+        if world == 1 and not args.no_cpu:
+            torch.set_num_threads(host_threads())
+            dtc = cpu_rollout_frame_time(2) * cfg.n_layers / 2
+            line["cpu_baseline"] = {"value": 1.0 / dtc, "unit": "frames/s", "cores": torch.get_num_threads(), "kind": "port",
+                                    "sample": "oracle port, KV-cached decode of one 65-token frame vs a 15-frame cache, 2 "
+                                              "evaluations per frame, 2 of 24 layers scaled to full depth, fp32 torch CPU"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+        os._exit(0)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -401,7 +652,9 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.workload == "causvid":
+        run_causvid(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_owl(args)

@@ -463,6 +463,8 @@ static int launch_attn_decode(const CUtensorMap& tmQ, const CUtensorMap& tmK, co
   return launch_status();
 }
 
+static constexpr int64_t kDecCounterBytes = 4096;
+
 static int decode_splits(int64_t B, int64_t H, int tiles_total) {
   int s = static_cast<int>((sm_count() + B * H - 1) / (B * H));
   if (s > tiles_total) s = tiles_total;
@@ -479,7 +481,7 @@ extern "C" {
 int64_t owl_attn_decode_workspace_bytes(int64_t B, int64_t H, int64_t cap, int64_t dh) {
   const int tiles = static_cast<int>((cap + kTile - 1) / kTile);
   const int64_t s = decode_splits(B, H, tiles);
-  return B * H * s * kTile * (dh + 2) * 4 + B * H * 4;
+  return kDecCounterBytes + B * H * s * kTile * (dh + 2) * 4;
 }
 
 int owl_attn_decode(const void* q, int64_t q_sb, int64_t q_sh, const void* k_cache, const void* v_cache, int64_t c_sb,
@@ -504,10 +506,13 @@ int owl_attn_decode(const void* q, int64_t q_sb, int64_t q_sh, const void* k_cac
   if (p.n_splits > 1) {
     if (!workspace || !aligned16(workspace) || workspace_bytes < owl_attn_decode_workspace_bytes(B, H, cap, dh))
       return OWL_ERR_BAD_ARG;
+    // the counters sit at a FIXED place: the partials of an earlier launch with another geometry must never be read
+    // as arrival counts (more than one split only when B*H < #SMs, so B*H counters always fit)
+    if (B * H * 4 > kDecCounterBytes) return OWL_ERR_UNSUPPORTED;
     const int64_t n_part = B * H * p.n_splits * kTile;
-    p.part_o = static_cast<float*>(workspace);
+    p.counters = static_cast<unsigned*>(workspace);
+    p.part_o = reinterpret_cast<float*>(static_cast<char*>(workspace) + kDecCounterBytes);
     p.part_ml = p.part_o + n_part * dh;
-    p.counters = reinterpret_cast<unsigned*>(p.part_ml + n_part * 2);
   }
   CUtensorMap tmQ, tmK, tmV;
   int rc;

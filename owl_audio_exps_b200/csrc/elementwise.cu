@@ -146,19 +146,35 @@ adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const b
   for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
     const bf16* xr = x + row * d;
     const int64_t frow = row / T;
-    uint4 xv[NV];
-    float ss = 0.f;
+    // every load of the row is issued before the first use: NV (x) to 5 NV (x, y, gate, a, b) independent 16-byte
+    // requests per lane in flight (one row per warp at a time otherwise leaves HBM idle: ncu r02, 34 % warps active)
+    uint4 xv[NV], yv[NV], gtv[NV], av[NV], bv[NV];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * 8;
       if (c < d) {
         xv[i] = ldg16(xr + c);
+        if (y != nullptr) {
+          yv[i] = ldg16(y + row * d + c);
+          gtv[i] = ldg16(gate + frow * ld_g + c);
+        }
+        if (a != nullptr) {
+          av[i] = ldg16(a + frow * ld_ab + c);
+          bv[i] = ldg16(b + frow * ld_ab + c);
+        }
+      }
+    }
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
         float f[8];
         unpack8(xv[i], f);
         if (y != nullptr) {  // x <- x + gate[frame] * y, the residual of the previous branch (attn.py:135,141)
           float fy[8], fg[8];
-          unpack8(ldg16(y + row * d + c), fy);
-          unpack8(ldg16(gate + frow * ld_g + c), fg);
+          unpack8(yv[i], fy);
+          unpack8(gtv[i], fg);
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = fmaf(fg[j], fy[j], f[j]);
           xv[i] = pack8(f);  // the residual stream is bf16: normalise exactly what is stored
@@ -180,8 +196,8 @@ adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const b
         unpack8(xv[i], f);
         if (a != nullptr) {
           float fa[8], fb[8];
-          unpack8(ldg16(a + frow * ld_ab + c), fa);
-          unpack8(ldg16(b + frow * ld_ab + c), fb);
+          unpack8(av[i], fa);
+          unpack8(bv[i], fb);
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = f[j] * rstd * (1.f + fa[j]) + fb[j];
         } else {
@@ -212,14 +228,22 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
   for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
     const float rstd = rstd_in[row];
     const int64_t frow = row / T;
-    uint4 xv[NV], gv[NV];
+    uint4 xv[NV], gv[NV], av[NV], rv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {   // all loads of the row first (see adaln_fwd_kernel)
+      const int c = (i * 32 + lane) * 8;
+      if (c < d) {
+        xv[i] = ldg16(x + row * d + c);
+        gv[i] = ldg16(dh + row * d + c);
+        if (a != nullptr) av[i] = ldg16(a + frow * ld_ab + c);
+        if (dres != nullptr) rv[i] = ldg16(dres + row * d + c);
+      }
+    }
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * 8;
       if (c < d) {
-        xv[i] = ldg16(x + row * d + c);
-        gv[i] = ldg16(dh + row * d + c);
         float fx[8], fg[8];
         unpack8(xv[i], fx);
         unpack8(gv[i], fg);
@@ -232,10 +256,10 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
         }
         if (a != nullptr) {
           float fa[8];
-          unpack8(ldg16(a + frow * ld_ab + c), fa);
+          unpack8(av[i], fa);
 #pragma unroll
           for (int j = 0; j < 8; ++j) fg[j] *= (1.f + fa[j]);
-          gv[i] = pack8(fg);  // keep g (bf16-rounded) for the second pass: saves the re-read of a
+          gv[i] = pack8(fg);  // keep g (bf16-rounded) for the second pass
           unpack8(gv[i], fg);
         }
 #pragma unroll
@@ -254,7 +278,7 @@ adaln_bwd_row_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, co
         for (int j = 0; j < 8; ++j) o[j] = rstd * (fg[j] - fx[j] * rstd * s);
         if (dres != nullptr) {
           float fr[8];
-          unpack8(ldg16(dres + row * d + c), fr);
+          unpack8(rv[i], fr);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += fr[j];
         }
@@ -296,14 +320,24 @@ adaln_gate_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, c
   for (int64_t row = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5; row < M; row += nwarps) {
     const float rstd = rstd_in[row];
     const int64_t frow = row / T;
-    uint4 xv[NV], gv[NV];
+    uint4 xv[NV], gv[NV], av[NV], rv[NV], cv[NV], yv[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {   // all loads of the row first (see adaln_fwd_kernel): up to 6 NV requests per lane in flight
+      const int col = (i * 32 + lane) * 8;
+      if (col < d) {
+        xv[i] = ldg16(x + row * d + col);
+        gv[i] = ldg16(dh + row * d + col);
+        if (a != nullptr) av[i] = ldg16(a + frow * ld_ab + col);
+        if (dres != nullptr) rv[i] = ldg16(dres + row * d + col);
+        cv[i] = ldg16(c + frow * ld_c + col);
+        if (write_dc) yv[i] = ldg16(y + row * d + col);
+      }
+    }
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int col = (i * 32 + lane) * 8;
       if (col < d) {
-        xv[i] = ldg16(x + row * d + col);
-        gv[i] = ldg16(dh + row * d + col);
         float fx[8], fg[8];
         unpack8(xv[i], fx);
         unpack8(gv[i], fg);
@@ -316,7 +350,7 @@ adaln_gate_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, c
         }
         if (a != nullptr) {
           float fa[8];
-          unpack8(ldg16(a + frow * ld_ab + col), fa);
+          unpack8(av[i], fa);
 #pragma unroll
           for (int j = 0; j < 8; ++j) fg[j] *= (1.f + fa[j]);
           gv[i] = pack8(fg);
@@ -338,7 +372,7 @@ adaln_gate_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, c
         for (int j = 0; j < 8; ++j) o[j] = rstd * (fg[j] - fx[j] * rstd * s);
         if (dres != nullptr) {
           float fr[8];
-          unpack8(ldg16(dres + row * d + col), fr);
+          unpack8(rv[i], fr);
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] += fr[j];
         }
@@ -346,7 +380,7 @@ adaln_gate_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, c
         stg16(dx + row * d + col, dxp);
         unpack8(dxp, o);  // the gate backward sees the bf16 residual gradient, exactly as the two-kernel path does
         float fc[8], g[8];
-        unpack8(ldg16(c + frow * ld_c + col), fc);
+        unpack8(cv[i], fc);
 #pragma unroll
         for (int j = 0; j < 8; ++j) g[j] = o[j] * fc[j];
         const uint4 dyp = pack8(g);
@@ -358,7 +392,7 @@ adaln_gate_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ x, c
         }
         if (write_dc) {
           float fy[8];
-          unpack8(ldg16(y + row * d + col), fy);
+          unpack8(yv[i], fy);
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] = o[j] * fy[j];
           stg16(dc + frow * ld_dc + col, pack8(g));

@@ -29,6 +29,7 @@ static constexpr int kSmBK = 64;
 static constexpr int kSmABytes = 128 * kSmBK * 2;
 static constexpr int kSmMaxStages = 8;
 static constexpr int kSmSmemLimit = 232448;
+static constexpr int kSmSmemPerCta = 113 * 1024;   // two CTAs (of consecutive kernels) per SM
 
 struct SmallMParams {
   int M, N, K;
@@ -48,11 +49,6 @@ struct SmallMParams {
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-__device__ __forceinline__ float4 ld_cg_v4(const float* addr) {
-  float4 v;
-  asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(addr) : "memory");
-  return v;
-}
 __device__ __forceinline__ float sm_tanh_approx(float x) {
   float y;
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -63,43 +59,62 @@ __device__ __forceinline__ float sm_silu(float z) {
   return fmaf(h, sm_tanh_approx(h), h);
 }
 
-// 8 consecutive output columns of one row: bias, activation / gate+residual, bf16 store (16 bytes)
-__device__ __forceinline__ void finish8(const SmallMParams& p, int row, int col, float (&a)[8]) {
+// 32 consecutive output columns of one row: bias (staged in shared memory once per tile), activation or gate+residual,
+// four 16-byte bf16 stores.  All global loads of the chunk (residual, gate) are issued before the first use: the
+// epilogue of a decode GEMM is a latency chain, not a bandwidth problem.
+__device__ __forceinline__ void finish32(const SmallMParams& p, const float* s_bias, int row, int col_in_tile, int n0,
+                                         float (&a)[32]) {
+  const int col = n0 + col_in_tile;
   if (col >= p.N) return;
-  if (p.bias != nullptr) {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-    a[0] += b0.x; a[1] += b0.y; a[2] += b0.z; a[3] += b0.w;
-    a[4] += b1.x; a[5] += b1.y; a[6] += b1.z; a[7] += b1.w;
-  }
-  uint4 o;
-  if (p.mode == OWL_EPI_STORE) {
-    o = make_uint4(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]), pack_bf16(a[4], a[5]), pack_bf16(a[6], a[7]));
-  } else {
-    // the Linear's own output is a bf16 tensor in the reference (mlp.py:34-35, modulation.py:41-43): round once
+  const int ng = min(4, (p.N - col) >> 3);   // N % 8 == 0: whole 8-column groups
+  uint4 rv[4], gv[4];
+  if (p.mode == OWL_EPI_GATE_RESIDUAL) {
+    const bf16* rp = p.res + static_cast<long long>(row) * p.ldres + col;
+    const bf16* gp = p.gate + static_cast<long long>(row / p.rows_per_frame) * p.ldgate + col;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] = round_bf16(a[j]);
-    if (p.mode == OWL_EPI_BIAS_SILU) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) a[j] = sm_silu(a[j]);
-    } else {  // OWL_EPI_GATE_RESIDUAL: out = res + gate[frame] * y
-      const uint4 rv = __ldg(reinterpret_cast<const uint4*>(p.res + static_cast<long long>(row) * p.ldres + col));
-      const uint4 gv =
-          __ldg(reinterpret_cast<const uint4*>(p.gate + static_cast<long long>(row / p.rows_per_frame) * p.ldgate + col));
-      const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        a[2 * j] = fmaf(bf16_lo(gg[j]), a[2 * j], bf16_lo(rr[j]));
-        a[2 * j + 1] = fmaf(bf16_hi(gg[j]), a[2 * j + 1], bf16_hi(rr[j]));
+    for (int g = 0; g < 4; ++g) {
+      if (g < ng) {
+        rv[g] = __ldg(reinterpret_cast<const uint4*>(rp + g * 8));
+        gv[g] = __ldg(reinterpret_cast<const uint4*>(gp + g * 8));
       }
     }
-    o = make_uint4(pack_bf16(a[0], a[1]), pack_bf16(a[2], a[3]), pack_bf16(a[4], a[5]), pack_bf16(a[6], a[7]));
   }
-  *reinterpret_cast<uint4*>(p.out + static_cast<long long>(row) * p.ldo + col) = o;
+  bf16* op = p.out + static_cast<long long>(row) * p.ldo + col;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    if (g >= ng) break;
+    float v[8];
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) v[jj] = a[g * 8 + jj];
+    if (p.bias != nullptr) {
+      const float4 b0 = *reinterpret_cast<const float4*>(s_bias + col_in_tile + g * 8);
+      const float4 b1 = *reinterpret_cast<const float4*>(s_bias + col_in_tile + g * 8 + 4);
+      v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+      v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+    }
+    if (p.mode != OWL_EPI_STORE) {
+      // the Linear's own output is a bf16 tensor in the reference (mlp.py:34-35, modulation.py:41-43): round once
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) v[jj] = round_bf16(v[jj]);
+      if (p.mode == OWL_EPI_BIAS_SILU) {
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) v[jj] = sm_silu(v[jj]);
+      } else {  // OWL_EPI_GATE_RESIDUAL: out = res + gate[frame] * y
+        const uint32_t rr[4] = {rv[g].x, rv[g].y, rv[g].z, rv[g].w}, gg[4] = {gv[g].x, gv[g].y, gv[g].z, gv[g].w};
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          v[2 * jj] = fmaf(bf16_lo(gg[jj]), v[2 * jj], bf16_lo(rr[jj]));
+          v[2 * jj + 1] = fmaf(bf16_hi(gg[jj]), v[2 * jj + 1], bf16_hi(rr[jj]));
+        }
+      }
+    }
+    *reinterpret_cast<uint4*>(op + g * 8) =
+        make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+  }
 }
 
 template <int BN>
-__global__ void __launch_bounds__(kSmThreads, 1)
+__global__ void __launch_bounds__(kSmThreads, 2)
 gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const SmallMParams p) {
   constexpr int kBBytes = BN * kSmBK * 2;
   constexpr int kStageBytes = kSmABytes + kBBytes;
@@ -138,10 +153,24 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const int total = p.tiles_n * p.splits;
+  // WEIGHT PREFETCH AHEAD OF THE GRID DEPENDENCY.  The weights do not depend on the previous kernel, only the activations
+  // do: under programmatic dependent launch this CTA is resident while the previous kernel still runs (two CTAs fit an SM:
+  // <= 113 KB of shared memory each), so the producer fills the ring with the first weight tiles BEFORE
+  // griddepcontrol.wait and HBM keeps streaming across the kernel boundary (reduction round trips, launch, flush).
+  int pre = 0;
+  if (warp == 0 && lane == 0 && static_cast<int>(blockIdx.x) < total) {
+    const int t = blockIdx.x;
+    const int tn = t % p.tiles_n, ks = t / p.tiles_n;
+    const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+    for (int kb = kb0; kb < kb1 && pre < kStages; ++kb, ++pre) {
+      mbar_arrive_expect_tx(&full_bar[pre], kStageBytes);
+      tma_load_2d(smem_b + pre * kBBytes, &tmB, &full_bar[pre], kb * kSmBK, tn * BN);
+    }
+  }
   pdl_wait();     // the activations (and the zeroed workspace) come from the previous kernel
   pdl_launch();
 
-  const int total = p.tiles_n * p.splits;
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
@@ -150,10 +179,15 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int tn = t % p.tiles_n, ks = t / p.tiles_n;
         const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
-          tma_load_2d(smem_b + stage * kBBytes, &tmB, &full_bar[stage], kb * kSmBK, tn * BN);   // weights first: HBM
-          tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);       // activations: L2
+          if (pre > 0) {   // this stage's weights are already on their way: add the activations
+            --pre;
+            tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);
+          } else {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+            tma_load_2d(smem_b + stage * kBBytes, &tmB, &full_bar[stage], kb * kSmBK, tn * BN);   // weights: HBM
+            tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);       // activations: L2
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -187,31 +221,35 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   } else {
     const int q = warp & 3;            // TMEM lane quarter this warp may read
     const int r = q * 32 + lane;       // token row
+    const int et = static_cast<int>(threadIdx.x) - 64;   // 0..127 among the epilogue threads
     const bool row_ok = r < p.M;
-    const bool elected = threadIdx.x == 64;
+    const bool elected = et == 0;
+    float* s_bias = reinterpret_cast<float*>(smem + 512);   // this tile's BN bias values
     int as = 0;
     uint32_t aphase = 0;
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
       const int tn = t % p.tiles_n;
       const int n0 = tn * BN;
+      if (p.bias != nullptr) {
+        named_bar_sync(1, 128);        // the previous tile's epilogue has read its bias row
+        if (et < BN) s_bias[et] = n0 + et < p.N ? __ldg(p.bias + n0 + et) : 0.f;
+        named_bar_sync(1, 128);
+      }
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as * BN);
       float* wrow = p.ws + (static_cast<long long>(tn) * 128 + r) * BN;
-#pragma unroll 1
+#pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t acc[32];
         tmem_ld_x32(taddr + c * 32, acc);
         tmem_ld_wait();
         if (!row_ok) continue;
         if (p.splits == 1) {
+          float a[32];
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float a[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) a[j] = __uint_as_float(acc[g * 8 + j]);
-            finish8(p, r, n0 + c * 32 + g * 8, a);
-          }
+          for (int jj = 0; jj < 32; ++jj) a[jj] = __uint_as_float(acc[jj]);
+          finish32(p, s_bias, r, c * 32, n0, a);
         } else {
 #pragma unroll
           for (int g = 0; g < 8; ++g)
@@ -236,13 +274,25 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         named_bar_sync(1, 128);        // everyone has read the flag before the next tile's election rewrites it
         if (last) {
           if (row_ok) {
-#pragma unroll 1
-            for (int c = 0; c < BN / 8; ++c) {
-              const float4 v0 = ld_cg_v4(wrow + c * 8), v1 = ld_cg_v4(wrow + c * 8 + 4);
-              *reinterpret_cast<float4*>(wrow + c * 8) = make_float4(0.f, 0.f, 0.f, 0.f);
-              *reinterpret_cast<float4*>(wrow + c * 8 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
-              float a[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-              finish8(p, r, n0 + c * 8, a);
+#pragma unroll
+            for (int hf = 0; hf < BN / 64; ++hf) {
+              // the whole 64-column half in flight at once (16 independent 16-byte L2 reads), then zeroed for the next launch
+              float4 v[16];
+#pragma unroll
+              for (int g = 0; g < 16; ++g) v[g] = __ldcg(reinterpret_cast<const float4*>(wrow + hf * 64 + g * 4));
+#pragma unroll
+              for (int g = 0; g < 16; ++g)
+                *reinterpret_cast<float4*>(wrow + hf * 64 + g * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+              for (int cc = 0; cc < 2; ++cc) {
+                float a[32];
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                  a[4 * g] = v[cc * 8 + g].x; a[4 * g + 1] = v[cc * 8 + g].y;
+                  a[4 * g + 2] = v[cc * 8 + g].z; a[4 * g + 3] = v[cc * 8 + g].w;
+                }
+                finish32(p, s_bias, r, hf * 64 + cc * 32, n0, a);
+              }
             }
           }
           if (elected) p.counters[tn] = 0u;
@@ -369,9 +419,9 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
     p.counters = reinterpret_cast<unsigned*>(static_cast<float*>(workspace) + ws_floats);
   }
   const int stage_bytes = kSmABytes + bn * kSmBK * 2;
-  int stages = (kSmSmemLimit - 2048) / stage_bytes;
+  int stages = (kSmSmemPerCta - 2048) / stage_bytes;
   if (stages > kSmMaxStages) stages = kSmMaxStages;
-  if (stages > p.kb_per_split + 1 && static_cast<long long>(p.tiles_n) * p.splits <= sms) stages = p.kb_per_split + 1;
+  if (stages > p.kb_per_split && static_cast<long long>(p.tiles_n) * p.splits <= sms) stages = p.kb_per_split;
   if (stages < 2) stages = 2;
   p.stages = stages;
   const int smem_bytes = 2048 + stages * stage_bytes;

@@ -339,10 +339,6 @@ class _Linear(torch.autograd.Function):
         a = ops.silu(x16) if silu_in else x16
         y = torch.empty(M, N, device=x16.device, dtype=bf16)
         z = None
-        if M <= 128 and K % 8 == 0 and not (torch.is_grad_enabled() and any(ctx.needs_input_grad[:3])):
-            # inference at decode shapes (one frame / one token per call): the weight-streaming split-K GEMM
-            ops.gemm_smallm(a, w16, M, N, K, mode=OWL_EPI_BIAS_SILU if silu_out else OWL_EPI_STORE, bias=b32, out0=y)
-            return y.view(*shp[:-1], N)
         if silu_out:
             z = torch.empty_like(y)
             ops.gemm(OWL_GEMM_NT, a, w16, M, N, K, mode=OWL_EPI_BIAS_SILU, bias=b32, out0=z, out1=y)
@@ -388,6 +384,16 @@ def linear(x, weight, bias, stage: WeightStage, key: str, silu_in=False, silu_ou
         return _Linear.apply(x, weight, bias, weight.detach().to(bf16), b32, silu_in, silu_out)
     w16 = stage.get(key + ".w", [weight])
     b32 = stage.get(key + ".b", [bias]) if bias is not None else None
+    if not torch.is_grad_enabled():
+        M = x.numel() // K
+        if 0 < M <= 128:
+            # inference at decode shapes (one frame / one token per call): the weight-streaming split-K GEMM
+            x16 = _as_bf16(x).view(M, K)
+            a = ops.silu(x16) if silu_in else x16
+            y = torch.empty(M, w16.shape[0], device=x16.device, dtype=bf16)
+            ops.gemm_smallm(a, w16, M, w16.shape[0], K, mode=OWL_EPI_BIAS_SILU if silu_out else OWL_EPI_STORE, bias=b32,
+                            out0=y)
+            return y.view(*x.shape[:-1], w16.shape[0])
     return _Linear.apply(x, weight, bias, w16, b32, silu_in, silu_out)
 
 

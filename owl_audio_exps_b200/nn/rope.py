@@ -83,6 +83,18 @@ class RoPE(nn.Module):
         self.cos = nn.Buffer(freqs.cos().contiguous(), persistent=False)
         self.sin = nn.Buffer(freqs.sin().contiguous(), persistent=False)
 
+    def _apply(self, fn, recurse=True):
+        """`.to(device)` moves the tables, dtype casts (`model.bfloat16()`, causvid_pipeline.py:36) never touch them:
+        the kernels read fp32 tables (rope.py:45 asserts fp32; the reference's trainers call cast_rope_buffers_to_fp32
+        after the cast, which would rebuild them from bf16-rounded values)."""
+        cos, sin = self.cos, self.sin
+        super()._apply(fn, recurse) if recurse is not True else super()._apply(fn)
+        for name, old in (("cos", cos), ("sin", sin)):
+            new = getattr(self, name)
+            if new.dtype != torch.float32:
+                setattr(self, name, nn.Buffer(old.to(device=new.device), persistent=False))
+        return self
+
     def forward(self, x, offset: int = 0):
         """x [B,H,L,dh]: rotate pairs (2i, 2i+1); output halves are [y_even | y_odd] (rope.py:43-51)."""
         from .. import functional as OF

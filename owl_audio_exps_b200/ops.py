@@ -399,6 +399,9 @@ def qk_norm_rope_fwd(qkv, cos, sin, pos_offset: int, H: int, eps: float, q, k, v
     """qkv [B,L,3*H*dh] -> q,k,v written into caller views [B,H,L,dh] (dh contiguous, L stride dh)."""
     B, L, three_d = qkv.shape
     dh = three_d // (3 * H)
+    _req(cos, torch.float32), _req(sin, torch.float32)      # a bf16 table read as fp32 is an out-of-bounds read
+    if cos.shape[0] < pos_offset + L:
+        raise RuntimeError(f"RoPE table has {cos.shape[0]} positions; need {pos_offset + L}")
     for t in (q, k, v):
         assert t.stride(3) == 1 and t.stride(2) == dh, "head-major views need contiguous [L, dh] rows"
     rq = torch.empty(B, H, L, device=qkv.device, dtype=torch.float32) if want_rstd else None
@@ -415,6 +418,7 @@ def qk_norm_rope_fwd(qkv, cos, sin, pos_offset: int, H: int, eps: float, q, k, v
 def qk_norm_rope_bwd(dq, dk, dv, q, k, rq, rk, cos, sin, pos_offset: int):
     """dq/dk/dv share strides ([B,H,L,dh]); returns dqkv [B,L,3*H*dh]."""
     B, H, L, dh = dq.shape
+    _req(cos, torch.float32), _req(sin, torch.float32)
     assert dq.stride() == dk.stride() == dv.stride()
     dqkv = torch.empty(B, L, 3 * H * dh, device=dq.device, dtype=bf16)
     rc = _lib.load().owl_qk_norm_rope_bwd(dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), dq.stride(0), dq.stride(1),
@@ -429,6 +433,7 @@ def qk_norm_rope_bwd(dq, dk, dv, q, k, rq, rk, cos, sin, pos_offset: int):
 def rope_apply(x, cos, sin, pos_offset: int, inverse: bool = False):
     """x contiguous bf16 [..., L, dh] -> rotated copy (see owl_rope_apply)."""
     _req(x)
+    _req(cos, torch.float32), _req(sin, torch.float32)
     L, dh = x.shape[-2], x.shape[-1]
     y = torch.empty_like(x)
     rc = _lib.load().owl_rope_apply(x.data_ptr(), cos.data_ptr(), sin.data_ptr(), pos_offset, y.data_ptr(),
@@ -542,6 +547,7 @@ def qk_norm_rope_decode(qkv, cos, sin, state, q, k_cache, v_cache, H: int, eps: 
     B, L, three_d = qkv.shape
     dh = three_d // (3 * H)
     _req(qkv), _req(q), _req(k_cache), _req(v_cache), _req(state, torch.int32)
+    _req(cos, torch.float32), _req(sin, torch.float32)
     if k_cache.stride() != v_cache.stride() or k_cache.stride(3) != 1 or k_cache.stride(2) != dh:
         raise RuntimeError("ring cache buffers must be [B, H, cap, dh] with contiguous rows and equal strides")
     rc = _lib.load().owl_qk_norm_rope_decode(qkv.data_ptr(), cos.data_ptr(), sin.data_ptr(), cos.shape[0], state.data_ptr(),
