@@ -109,10 +109,13 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
  * sums meet in `workspace` (fp32 L2 atomics) and the last-arriving chunk applies the epilogue.  Modes: OWL_EPI_STORE,
  * OWL_EPI_BIAS_SILU (ONE output: out0 = silu(bf16(acc + bias)), the pre-activation is not kept), OWL_EPI_GATE_RESIDUAL.
  * `workspace`: owl_gemm_smallm_workspace_bytes(N) bytes, ZERO before the first call; every call leaves it zero again.
- * Calls sharing a workspace must be ordered on one stream. */
+ * Calls sharing a workspace must be ordered on one stream.
+ * `next_w` / `next_bytes` (optional, NULL / 0): the weight matrix the NEXT Linear of the schedule will read; its bytes are
+ * requested into L2 (cp.async.bulk.prefetch.L2) while this call reduces, so HBM keeps streaming across kernel boundaries. */
 int64_t owl_gemm_smallm_workspace_bytes(int64_t N);
 int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
-                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, owl_stream_t stream);
+                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, const void* next_w,
+                    int64_t next_bytes, owl_stream_t stream);
 
 /* Plain CUDA-core GEMM with the same contract (OWL_EPI_STORE / OWL_EPI_F32 only, no bias).
  * Verification aid for tests: an independent on-device answer at sizes where the CPU oracle is
@@ -331,6 +334,17 @@ int owl_qk_norm_rope_decode(const void* qkv, const float* cos_tab, const float* 
                             int64_t c_sb, int64_t c_sh, int64_t cap, int64_t B, int64_t L, int64_t H, int64_t dh, float eps,
                             owl_stream_t stream);
 int owl_decode_state_advance(int32_t* state, int64_t commit_rows, int64_t drop_rows, int64_t cap, owl_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Rectified-flow glue either side of the model call (bf16, 16-byte vectors).
+ * owl_rf_noise: lerpd = x * (1 - t[row]) + z * t[row]; target = z - x, x / z [rows, inner], t [rows]
+ *   (models/gamerft.py:93-96, audiorft.py:75-79, gamerft_audio.py:139-146).
+ * owl_mse_fwd: *loss = mean((pred - target)^2) accumulated in fp32 (F.mse_loss(pred.float(), target.float()) of
+ *   models/*.py without the fp32 copies); owl_mse_bwd: dpred = 2 (pred - target) * *dloss / n. */
+int owl_rf_noise(const void* x, const void* z, const void* t, void* lerpd, void* target, int64_t rows, int64_t inner,
+                 owl_stream_t stream);
+int owl_mse_fwd(const void* pred, const void* target, float* loss, int64_t n, owl_stream_t stream);
+int owl_mse_bwd(const void* pred, const void* target, const float* dloss, void* dpred, int64_t n, owl_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -360,3 +360,22 @@ def step_flops(B: int, L: int, d: int, T: int, n_layers: int, local_window: Opti
         w = local_window if (i % local_idx) != 0 else global_window
         att_fwd += 4.0 * d * B * unmasked_pairs(F_, T, w)
     return {"linear_fwd": lin_fwd, "attn_fwd": att_fwd, "step": 3 * lin_fwd + 3.5 * att_fwd}
+
+
+# ---------------------------------------------------------------------------------------------
+# muon.py (optimizer neighbour of the path)
+# ---------------------------------------------------------------------------------------------
+def newton_schulz5(G: Tensor, steps: int, dtype=torch.float32) -> Tensor:
+    """owl_wms/muon.py:11-38 (zeropower_via_newtonschulz5) for a 2-D G, iterated in `dtype` (the reference runs bf16)."""
+    a, b, c = (3.4445, -4.7750, 2.0315)
+    X = G.to(dtype)
+    if G.size(-2) > G.size(-1):
+        X = X.mT
+    X = X / (X.norm(dim=(-2, -1), keepdim=True) + 1e-7)
+    for _ in range(steps):
+        A = X @ X.mT
+        B = b * A + c * A @ A
+        X = a * X + B @ X
+    if G.size(-2) > G.size(-1):
+        X = X.mT
+    return X

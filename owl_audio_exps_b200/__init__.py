@@ -28,4 +28,6 @@ def install(package: str = "owl_wms", patch_compile: bool = True):
     sys.modules[f"{package}.nn"] = sys.modules.get(f"{package}.nn", _nn)
     for name in _NN_MODULES:
         sys.modules[f"{package}.nn.{name}"] = getattr(_nn, name)
+    from . import muon as _muon          # `from ..muon import init_muon` in the trainers (av_trainer.py:19)
+    sys.modules[f"{package}.muon"] = _muon
     return _nn

@@ -50,7 +50,7 @@ SIGNATURES = {
     "owl_debug_timestamp": ([vp, vp], C.c_int),
     "owl_gemm_bf16": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp], C.c_int),
     "owl_gemm_smallm_workspace_bytes": ([i64], i64),
-    "owl_gemm_smallm": ([i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp, i64, vp], C.c_int),
+    "owl_gemm_smallm": ([i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp, i64, vp, i64, vp], C.c_int),
     "owl_gemm_bf16_check": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, vp, i64, vp], C.c_int),
     "owl_cast_f32_bf16": ([vp, vp, i64, vp], C.c_int),
     "owl_silu_bf16": ([vp, vp, i64, vp], C.c_int),
@@ -80,6 +80,9 @@ SIGNATURES = {
     "owl_qk_norm_rope_decode": ([vp, vp, vp, i64, vp, vp, i64, i64, vp, vp, i64, i64, i64, i64, i64, i64, i64, f32, vp],
                                 C.c_int),
     "owl_decode_state_advance": ([vp, i64, i64, i64, vp], C.c_int),
+    "owl_rf_noise": ([vp, vp, vp, vp, vp, i64, i64, vp], C.c_int),
+    "owl_mse_fwd": ([vp, vp, vp, i64, vp], C.c_int),
+    "owl_mse_bwd": ([vp, vp, vp, vp, i64, vp], C.c_int),
     "owl_attn_fwd": (_ATTN_FWD, C.c_int),
     "owl_attn_bwd": (_ATTN_BWD, C.c_int),
     "owl_attn_fwd_check": (_ATTN_FWD, C.c_int),

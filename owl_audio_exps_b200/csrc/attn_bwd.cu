@@ -22,7 +22,7 @@ int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void*
                        const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb, int64_t v_sh,
                        const float* lse, const float* delta, float* dq_acc, void* dq, int64_t dq_sb, int64_t dq_sh,
                        void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh, int64_t B,
-                       int64_t H, int64_t Lq, int64_t Lk, const owl_attn_mask* mask, cudaStream_t s);  // attn_bwd2.cu
+                       int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask, cudaStream_t s);  // attn_bwd2.cu
 
 struct AttnBwdParams {
   int B, H, Lq, Lk, n_qtiles, n_ktiles;
@@ -567,12 +567,13 @@ int owl_attn_bwd(const void* dout, const void* o, int64_t o_sb, int64_t o_sl, co
   if ((rc = launch_status()) != OWL_OK) return rc;
 
   {
-    // dh = 64 and more than one tile: the single-pass kernel (attn_bwd2.cu; S and dP once per tile pair, dq through a
-    // TMA reduce-add into dq_acc).  OWL_ATTN_BWD=1 forces the two-pass kernels below (A/B aid).
+    // more than one tile: the single-pass kernel (attn_bwd2.cu; S and dP once per tile pair, dq accumulated in fp32 in
+    // dq_acc: TMA reduce-add at dh = 64, red.global.add at dh = 128).  OWL_ATTN_BWD=1 forces the two-pass kernels below
+    // (A/B aid), OWL_ATTN_BWD=3 keeps dh = 128 on them.
     static const int force = [] { const char* e = getenv("OWL_ATTN_BWD"); return e ? atoi(e) : 0; }();
-    if (dh == 64 && dq_acc != nullptr && force != 1 && (p.n_qtiles > 1 || p.n_ktiles > 1))
+    if (dq_acc != nullptr && force != 1 && !(force == 3 && dh == 128) && (p.n_qtiles > 1 || p.n_ktiles > 1))
       return attn_bwd2_dispatch(dout, o_sb, o_sl, q, q_sb, q_sh, k, k_sb, k_sh, v, v_sb, v_sh, lse, delta, dq_acc, dq,
-                                dq_sb, dq_sh, dk, dk_sb, dk_sh, dv, dv_sb, dv_sh, B, H, Lq, Lk, mask, s);
+                                dq_sb, dq_sh, dk, dk_sb, dk_sh, dv, dv_sb, dv_sh, B, H, Lq, Lk, dh, mask, s);
   }
   CUtensorMap tmQ, tmDO, tmK, tmV;
   if ((rc = make_tmap_4d_bf16(&tmQ, q, dh, Lq, H, B, dh, q_sh, q_sb, 64, kTile)) != OWL_OK) return rc;

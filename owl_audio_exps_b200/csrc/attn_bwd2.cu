@@ -1,4 +1,4 @@
-// Attention backward, second generation (dh = 64, more than one tile): ONE persistent kernel per call instead of a dq pass
+// Attention backward, second generation (more than one tile): ONE persistent kernel per call instead of a dq pass
 // plus a dk/dv pass, so S and dP are computed once per (query tile, key tile) pair - 5 MMAs per pair instead of 7 - and
 // neither P nor dS makes a round trip through shared memory on its way back to the tensor core.
 //
@@ -17,10 +17,15 @@
 //     WG0 / WG1  softmax over query columns [0,64) / [64,128) of the pair (thread = key row), epilogue dV / dK
 //     WG2        warp 8 TMA producer, warp 9 MMA issuer, warps 10 / 11 load lse / delta of the query tile into shared memory
 //     WG3        dQ drain
-//   TMEM: S^T [0,128)  dP^T [128,256)  dV [256,320)  dK [320,384)  dQ partial, double-buffered [384,448) [448,512).
+//   TMEM, dh = 64:  S^T [0,128)  dP^T [128,256)  dV [256,320)  dK [320,384)  dQ partial, double-buffered [384,448) [448,512).
+//   TMEM, dh = 128: S^T [0,128)  dP^T [128,256)  dV [256,384)  dK [384,512) fill all 512 columns.  The dQ partial lives in the
+//     four 32-column gaps the softmax leaves inside S^T / dP^T (P^T and dS^T are bf16: each warpgroup's 64 fp32 columns
+//     shrink to 32), as four N = 32 MMAs; it is issued FIRST in MMA 2 and drained (red.global.add.v4.f32 straight from
+//     registers: no shared memory is left for a staging tile) while dV / dK run, so the next pair's MMA 1 - which overwrites
+//     those columns - finds them free.  Shared memory: K, V, 2 stages of {Q, dO}, dS^T = 226 KB.
 //
-// Replaces the autograd of flex_attention (owl_wms/nn/attn.py:106-109 under rft_trainer.py:189) for dh = 64 training /
-// prefill shapes; dh = 128 and single-tile problems stay on attn_bwd.cu.
+// Replaces the autograd of flex_attention (owl_wms/nn/attn.py:106-109 under rft_trainer.py:189) for training / prefill
+// shapes at dh = 64 and dh = 128; single-tile problems stay on attn_bwd.cu.
 #include <cuda_bf16.h>
 #include <math.h>
 #include <stdlib.h>
@@ -37,27 +42,29 @@ struct AttnBwd2Params {
   float scale_log2, scale;
   const float* lse;
   const float* delta;
+  float* dq_acc;   // fp32 [B*H, Lq_pad, dh]
   bf16 *dk, *dv;
   long long dk_sb, dk_sh, dv_sb, dv_sh;
   MaskParams m;
 };
 
-namespace bwd2 {
-static constexpr int DH = 64;
-static constexpr int kThreads = 512;
-static constexpr int kStages = 3;                        // {Q_i, dO_i, lse_i, delta_i} in flight
-static constexpr int kTileBytes = kTile * DH * 2;        // 16 KB
-static constexpr int kOffK = 0;
-static constexpr int kOffV = kTileBytes;
-static constexpr int kOffRing = 2 * kTileBytes;          // per stage: Q then dO
-static constexpr int kStageBytes = 2 * kTileBytes;
-static constexpr int kOffDS = kOffRing + kStages * kStageBytes;   // dS^T [128 keys][128 q] bf16, two swizzled panels
-static constexpr int kOffDQ = kOffDS + kTile * kTile * 2;         // fp32 staging [128 q][64] as two 128B-swizzled panels
-static constexpr int kOffStat = kOffDQ + kTile * DH * 4;          // per stage: lse2[128], delta[128] fp32
-static constexpr int kOffBar = kOffStat + kStages * 1024;
-static constexpr int kSmemBytes = kOffBar + 512;
-static constexpr uint32_t kColST = 0, kColDPT = 128, kColDV = 256, kColDK = 320, kColDQ = 384;
-}  // namespace bwd2
+template <int DH_>
+struct Bwd2Cfg {
+  static constexpr int DH = DH_;
+  static constexpr int kThreads = 512;
+  static constexpr int kStages = DH == 64 ? 3 : 2;         // {Q_i, dO_i, lse_i, delta_i} in flight
+  static constexpr int kTileBytes = kTile * DH * 2;        // 16 / 32 KB
+  static constexpr int kOffK = 0;
+  static constexpr int kOffV = kTileBytes;
+  static constexpr int kOffRing = 2 * kTileBytes;          // per stage: Q then dO
+  static constexpr int kStageBytes = 2 * kTileBytes;
+  static constexpr int kOffDS = kOffRing + kStages * kStageBytes;   // dS^T [128 keys][128 q] bf16, two swizzled panels
+  static constexpr int kOffDQ = kOffDS + kTile * kTile * 2;         // dh = 64: fp32 staging [128 q][64], two 128B-swizzled panels
+  static constexpr int kOffStat = kOffDQ + (DH == 64 ? kTile * DH * 4 : 0);   // per stage: lse2[128], delta[128] fp32
+  static constexpr int kOffBar = kOffStat + kStages * 1024;
+  static constexpr int kSmemBytes = kOffBar + 512;
+  static constexpr uint32_t kColST = 0, kColDPT = 128, kColDV = 256, kColDK = 256 + DH, kColDQ = 384;
+};
 
 struct Bwd2Item {
   int b, h, j0, t0, n_q;
@@ -76,11 +83,18 @@ __device__ __forceinline__ Bwd2Item bwd2_item(const AttnBwd2Params& p, int w) {
   return it;
 }
 
-__global__ void __launch_bounds__(bwd2::kThreads, 1)
+template <int DH>
+__global__ void __launch_bounds__(512, 1)
 attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
                  const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                  const __grid_constant__ CUtensorMap tmDQ, const AttnBwd2Params p) {
-  using namespace bwd2;
+  using Cfg = Bwd2Cfg<DH>;
+  constexpr int kStages = Cfg::kStages, kTileBytes = Cfg::kTileBytes, kStageBytes = Cfg::kStageBytes;
+  constexpr int kOffK = Cfg::kOffK, kOffV = Cfg::kOffV, kOffRing = Cfg::kOffRing, kOffDS = Cfg::kOffDS;
+  constexpr int kOffDQ = Cfg::kOffDQ, kOffStat = Cfg::kOffStat, kOffBar = Cfg::kOffBar;
+  constexpr uint32_t kColST = Cfg::kColST, kColDPT = Cfg::kColDPT, kColDV = Cfg::kColDV, kColDK = Cfg::kColDK;
+  constexpr uint32_t kColDQ = Cfg::kColDQ;
+  (void)kOffDQ; (void)kColDQ;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
   uint64_t* kv_full = bars;                 // TMA -> MMA
@@ -140,16 +154,23 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         mbar_wait(kv_empty, (item_n & 1) ^ 1);
         ++item_n;
         mbar_arrive_expect_tx(kv_full, 2 * kTileBytes);
-        tma_load_4d(smem + kOffK, &tmK, kv_full, 0, it.j0, it.h, it.b);
-        tma_load_4d(smem + kOffV, &tmV, kv_full, 0, it.j0, it.h, it.b);
+#pragma unroll
+        for (int pn = 0; pn < DH / 64; ++pn) {
+          tma_load_4d(smem + kOffK + pn * kPanelBytes, &tmK, kv_full, pn * 64, it.j0, it.h, it.b);
+          tma_load_4d(smem + kOffV + pn * kPanelBytes, &tmV, kv_full, pn * 64, it.j0, it.h, it.b);
+        }
         for (int q = 0; q < it.n_q; ++q) {
           const uint32_t s = ring_n % kStages;
           mbar_wait(&qdo_empty[s], ((ring_n / kStages) & 1) ^ 1);
           ++ring_n;
           mbar_arrive_expect_tx(&qdo_full[s], kStageBytes);
           const int i0 = (it.t0 + q) * kTile;
-          tma_load_4d(smem + kOffRing + s * kStageBytes, &tmQ, &qdo_full[s], 0, i0, it.h, it.b);
-          tma_load_4d(smem + kOffRing + s * kStageBytes + kTileBytes, &tmDO, &qdo_full[s], 0, i0, it.h, it.b);
+#pragma unroll
+          for (int pn = 0; pn < DH / 64; ++pn) {
+            tma_load_4d(smem + kOffRing + s * kStageBytes + pn * kPanelBytes, &tmQ, &qdo_full[s], pn * 64, i0, it.h, it.b);
+            tma_load_4d(smem + kOffRing + s * kStageBytes + kTileBytes + pn * kPanelBytes, &tmDO, &qdo_full[s], pn * 64, i0,
+                        it.h, it.b);
+          }
         }
       }
     }
@@ -188,6 +209,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);   // S^T, dP^T
       constexpr uint32_t idesc_acc = make_idesc_bf16(kTile, DH, false, true);     // dV, dK: A from TMEM, B MN-major
       constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, true, true);       // dQ: A = dS^T tile read MN-major
+      constexpr uint32_t idesc_dq32 = make_idesc_bf16(kTile, 32, true, true);     // dh = 128: one 32-column piece of dQ
+      (void)idesc_dq; (void)idesc_dq32;
       const uint32_t sK = smem_u32(smem + kOffK), sV = smem_u32(smem + kOffV), sDS = smem_u32(smem + kOffDS);
       const uint32_t tST = tmem_base + kColST, tDPT = tmem_base + kColDPT;
       const uint32_t tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
@@ -201,6 +224,10 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
           ++ring_n;
           const uint32_t sQ = smem_u32(smem + kOffRing + s * kStageBytes), sDO = sQ + kTileBytes;
+          if (DH == 128 && pair_n > 0) {
+            // the previous pair's dQ partial sits inside the S^T / dP^T columns MMA 1 is about to overwrite
+            mbar_wait(&dq_free[0], (pair_n - 1) & 1);
+          }
           tc_fence_after();
           // MMA 1 (in issue order behind MMA 2 of the previous pair, which still reads P^T / dS^T from these columns)
 #pragma unroll
@@ -211,26 +238,53 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           // MMA 2
           mbar_wait(pds_full, pair_n & 1);
           if (q == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);       // the previous item's epilogue has read dV / dK
-          const uint32_t buf = pair_n & 1;
-          mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);       // the drain has read this dQ buffer's previous content
-          tc_fence_after();
           const uint32_t acc = q > 0 ? 1u : 0u;
+          if (DH == 64) {
+            const uint32_t buf = pair_n & 1;
+            mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);     // the drain has read this dQ buffer's previous content
+            tc_fence_after();
 #pragma unroll
-          for (int k = 0; k < kTile / 16; ++k) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
-            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+            for (int k = 0; k < kTile / 16; ++k) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+            }
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k) {
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+            }
+            const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k)
+              umma_bf16_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+            umma_commit(&qdo_empty[s]);
+            umma_commit(&dq_full[buf]);
+          } else {
+            tc_fence_after();
+            // dQ partial first, as four N = 32 pieces into the column gaps [32,64) [96,128) [160,192) [224,256): piece c
+            // holds head-dim columns [32c, 32c + 32); B = K_j read MN-major at a 64-byte offset inside its 64-column panel
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const uint32_t tDQc = tmem_base + 32u + 64u * static_cast<uint32_t>(c);
+              const uint32_t sKc = sK + (c >> 1) * kPanelBytes + (c & 1) * 64;
+#pragma unroll
+              for (int k = 0; k < kTile / 16; ++k)
+                umma_bf16_ss(tDQc, desc_mnmajor(sDS, k), make_smem_desc(sKc + k * 2048, kPanelBytes, 1024), idesc_dq32,
+                             k > 0 ? 1u : 0u);
+            }
+            umma_commit(&dq_full[0]);
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k) {
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+            }
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k) {
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
+            }
+            umma_commit(&qdo_empty[s]);
           }
-#pragma unroll
-          for (int k = 0; k < kTile / 16; ++k) {
-            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
-          }
-          const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
-#pragma unroll
-          for (int k = 0; k < kTile / 16; ++k)
-            umma_bf16_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
-          umma_commit(&qdo_empty[s]);
-          umma_commit(&dq_full[buf]);
           ++pair_n;
         }
         umma_commit(acc_done);
@@ -251,31 +305,56 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       if (it.n_q <= 0) continue;
       const long long row_base = (static_cast<long long>(it.b) * p.H + it.h) * p.Lq_pad;
       for (int q = 0; q < it.n_q; ++q) {
-        const uint32_t buf = pair_n & 1;
-        mbar_wait(&dq_full[buf], (pair_n >> 1) & 1);
-        ++pair_n;
-        tc_fence_after();
-        uint32_t v[2][32];
-        tmem_ld_x32(tmem_base + kColDQ + buf * DH + lane_addr, v[0]);
-        tmem_ld_x32(tmem_base + kColDQ + buf * DH + lane_addr + 32, v[1]);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(&dq_free[buf]);
-        if (leader) tma_store_wait_read0();   // the previous reduce has finished reading the staging panels
-        named_bar_sync(1, 128);
+        if (DH == 64) {
+          const uint32_t buf = pair_n & 1;
+          mbar_wait(&dq_full[buf], (pair_n >> 1) & 1);
+          ++pair_n;
+          tc_fence_after();
+          uint32_t v[2][32];
+          tmem_ld_x32(tmem_base + kColDQ + buf * DH + lane_addr, v[0]);
+          tmem_ld_x32(tmem_base + kColDQ + buf * DH + lane_addr + 32, v[1]);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(&dq_free[buf]);
+          if (leader) tma_store_wait_read0();   // the previous reduce has finished reading the staging panels
+          named_bar_sync(1, 128);
 #pragma unroll
-        for (int pn = 0; pn < 2; ++pn)
+          for (int pn = 0; pn < 2; ++pn)
 #pragma unroll
-          for (int c = 0; c < 8; ++c)
-            *reinterpret_cast<uint4*>(stag + pn * 16384 + r * 128 + ((c ^ (r & 7)) << 4)) =
-                make_uint4(v[pn][4 * c], v[pn][4 * c + 1], v[pn][4 * c + 2], v[pn][4 * c + 3]);
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (leader) {
-          const int row0 = static_cast<int>(row_base + static_cast<long long>(it.t0 + q) * kTile);
-          tma_reduce_add_2d(&tmDQ, stag, 0, row0);
-          tma_reduce_add_2d(&tmDQ, stag + 16384, 32, row0);
-          tma_store_commit();
+            for (int c = 0; c < 8; ++c)
+              *reinterpret_cast<uint4*>(stag + pn * 16384 + r * 128 + ((c ^ (r & 7)) << 4)) =
+                  make_uint4(v[pn][4 * c], v[pn][4 * c + 1], v[pn][4 * c + 2], v[pn][4 * c + 3]);
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (leader) {
+            const int row0 = static_cast<int>(row_base + static_cast<long long>(it.t0 + q) * kTile);
+            tma_reduce_add_2d(&tmDQ, stag, 0, row0);
+            tma_reduce_add_2d(&tmDQ, stag + 16384, 32, row0);
+            tma_store_commit();
+          }
+        } else {
+          // dh = 128: the partial sits in the four 32-column gaps of S^T / dP^T; read it out at once (the next pair's
+          // MMA 1 waits for these columns), then add it to the fp32 accumulator straight from registers
+          mbar_wait(&dq_full[0], pair_n & 1);
+          ++pair_n;
+          tc_fence_after();
+          float* dst = p.dq_acc + (row_base + static_cast<long long>(it.t0 + q) * kTile + r) * DH;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {     // 32 columns at a time (128 registers per thread in this kernel)
+            uint32_t v[32];
+            tmem_ld_x32(tmem_base + 32u + 64u * static_cast<uint32_t>(c) + lane_addr, v);
+            tmem_ld_wait();
+            if (c == 3) {
+              tc_fence_before();
+              mbar_arrive(&dq_free[0]);
+            }
+#pragma unroll
+            for (int g = 0; g < 8; ++g)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c * 32 + g * 4),
+                           "f"(__uint_as_float(v[4 * g])), "f"(__uint_as_float(v[4 * g + 1])),
+                           "f"(__uint_as_float(v[4 * g + 2])), "f"(__uint_as_float(v[4 * g + 3]))
+                           : "memory");
+          }
         }
       }
     }
@@ -403,32 +482,34 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   }
 }
 
-// fp32 dq accumulator [B*H, Lq_pad, 64] -> bf16 dq [B, H, Lq, 64] (strides in elements)
+// fp32 dq accumulator [B*H, Lq_pad, dh] -> bf16 dq [B, H, Lq, dh] (strides in elements); lg8 = log2(dh / 8)
 __global__ void __launch_bounds__(256)
 attn_dq_convert_kernel(const float* __restrict__ acc, bf16* __restrict__ dq, long long dq_sb, long long dq_sh, int H,
-                       int Lq, int Lq_pad, long long total8) {
+                       int Lq, int Lq_pad, long long total8, int lg8) {
   pdl_prologue();
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int dh = 8 << lg8;
   for (long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < total8; t += stride) {
-    const int c = static_cast<int>(t & 7);            // 8-element group inside the 64-wide row
-    const long long row = t >> 3;                     // (b*H + h) * Lq + i
+    const int c = static_cast<int>(t & ((1 << lg8) - 1));   // 8-element group inside the row
+    const long long row = t >> lg8;                   // (b*H + h) * Lq + i
     const int i = static_cast<int>(row % Lq);
     const long long bh = row / Lq;
-    const float4* src = reinterpret_cast<const float4*>(acc + (bh * Lq_pad + i) * 64 + c * 8);
+    const float4* src = reinterpret_cast<const float4*>(acc + (bh * Lq_pad + i) * dh + c * 8);
     const float4 a = __ldg(src), b = __ldg(src + 1);
     uint4 o;
     o.x = pack_bf16(a.x, a.y); o.y = pack_bf16(a.z, a.w); o.z = pack_bf16(b.x, b.y); o.w = pack_bf16(b.z, b.w);
-    *reinterpret_cast<uint4*>(dq + (bh / H) * dq_sb + (bh % H) * dq_sh + static_cast<long long>(i) * 64 + c * 8) = o;
+    *reinterpret_cast<uint4*>(dq + (bh / H) * dq_sb + (bh % H) * dq_sh + static_cast<long long>(i) * dh + c * 8) = o;
   }
 }
 
-// called by owl_attn_bwd (attn_bwd.cu) after the delta pre-pass, for dh = 64 and more than one tile
-int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void* q, int64_t q_sb, int64_t q_sh,
-                       const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb, int64_t v_sh,
-                       const float* lse, const float* delta, float* dq_acc, void* dq, int64_t dq_sb, int64_t dq_sh,
-                       void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh, int64_t B,
-                       int64_t H, int64_t Lq, int64_t Lk, const owl_attn_mask* mask, cudaStream_t s) {
-  using namespace bwd2;
+// called by owl_attn_bwd (attn_bwd.cu) after the delta pre-pass, for more than one tile
+template <int DH>
+static int attn_bwd2_launch(const void* dout, int64_t o_sb, int64_t o_sl, const void* q, int64_t q_sb, int64_t q_sh,
+                            const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb, int64_t v_sh,
+                            const float* lse, const float* delta, float* dq_acc, void* dq, int64_t dq_sb, int64_t dq_sh,
+                            void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh, int64_t B,
+                            int64_t H, int64_t Lq, int64_t Lk, const owl_attn_mask* mask, cudaStream_t s) {
+  using Cfg = Bwd2Cfg<DH>;
   if (dq_acc == nullptr) return OWL_ERR_BAD_ARG;
   AttnBwd2Params p{};
   int rc = fill_mask_params(mask, &p.m);
@@ -443,7 +524,7 @@ int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void*
   p.total_items = static_cast<int>(total);
   p.scale = 1.0f / sqrtf(static_cast<float>(DH));
   p.scale_log2 = 1.4426950408889634f * p.scale;
-  p.lse = lse; p.delta = delta;
+  p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.dk = static_cast<bf16*>(dk); p.dv = static_cast<bf16*>(dv);
   p.dk_sb = dk_sb; p.dk_sh = dk_sh; p.dv_sb = dv_sb; p.dv_sh = dv_sh;
 
@@ -457,7 +538,7 @@ int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void*
   static PerDeviceOnce once;
   rc = once.run([] {
     return static_cast<int>(
-        cudaFuncSetAttribute(attn_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        cudaFuncSetAttribute(attn_bwd2_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   });
   if (rc != OWL_OK) return rc;
   cudaError_t e = cudaMemsetAsync(dq_acc, 0, static_cast<size_t>(acc_rows) * DH * sizeof(float), s);
@@ -465,8 +546,8 @@ int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void*
   LaunchOpts lo;
   lo.pdl = false;  // follows a memset node
   const int grid = min(p.total_items, sm_count());
-  e = launch_kx(lo, attn_bwd2_kernel, dim3(static_cast<unsigned>(grid)), dim3(kThreads), kSmemBytes, s, tmQ, tmDO, tmK,
-                tmV, tmDQ, p);
+  e = launch_kx(lo, attn_bwd2_kernel<DH>, dim3(static_cast<unsigned>(grid)), dim3(Cfg::kThreads), Cfg::kSmemBytes, s, tmQ,
+                tmDO, tmK, tmV, tmDQ, p);
   if (e != cudaSuccess) {
     (void)cudaGetLastError();
     return static_cast<int>(e);
@@ -478,8 +559,20 @@ int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void*
   if (blocks > cap) blocks = cap;
   (void)launch_k(attn_dq_convert_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, s,
                  static_cast<const float*>(dq_acc), static_cast<bf16*>(dq), static_cast<long long>(dq_sb),
-                 static_cast<long long>(dq_sh), p.H, p.Lq, p.Lq_pad, total8);
+                 static_cast<long long>(dq_sh), p.H, p.Lq, p.Lq_pad, total8, DH == 64 ? 3 : 4);
   return launch_status();
+}
+
+int attn_bwd2_dispatch(const void* dout, int64_t o_sb, int64_t o_sl, const void* q, int64_t q_sb, int64_t q_sh,
+                       const void* k, int64_t k_sb, int64_t k_sh, const void* v, int64_t v_sb, int64_t v_sh,
+                       const float* lse, const float* delta, float* dq_acc, void* dq, int64_t dq_sb, int64_t dq_sh,
+                       void* dk, int64_t dk_sb, int64_t dk_sh, void* dv, int64_t dv_sb, int64_t dv_sh, int64_t B,
+                       int64_t H, int64_t Lq, int64_t Lk, int64_t dh, const owl_attn_mask* mask, cudaStream_t s) {
+  if (dh == 64)
+    return attn_bwd2_launch<64>(dout, o_sb, o_sl, q, q_sb, q_sh, k, k_sb, k_sh, v, v_sb, v_sh, lse, delta, dq_acc, dq, dq_sb,
+                                dq_sh, dk, dk_sb, dk_sh, dv, dv_sb, dv_sh, B, H, Lq, Lk, mask, s);
+  return attn_bwd2_launch<128>(dout, o_sb, o_sl, q, q_sb, q_sh, k, k_sb, k_sh, v, v_sb, v_sh, lse, delta, dq_acc, dq, dq_sb,
+                               dq_sh, dk, dk_sb, dk_sh, dv, dv_sb, dv_sh, B, H, Lq, Lk, mask, s);
 }
 
 }  // namespace owl

@@ -1,0 +1,145 @@
+// Rectified-flow training glue either side of the model call: the noising of the clean latents and the
+// MSE against the velocity target, each as one pass.
+//
+//   owl_rf_noise      lerpd = x * (1 - t) + z * t ;  target = z - x        (models/gamerft.py:93-96, audiorft.py:75-79,
+//                     gamerft_audio.py:139-146: three elementwise torch kernels + two temporaries per stream)
+//   owl_mse_fwd / bwd loss = mean((pred - target)^2) in fp32 without the `.float()` copies of models/*.py
+//                     (F.mse_loss(pred.float(), target.float())), and its gradient 2 (pred - target) dloss / n as bf16
+//
+// bf16 tensors, 16-byte vectors, grid-stride; the reduction is warp shuffles -> shared memory -> ONE fp32 atomic per CTA.
+#include <cuda_bf16.h>
+
+#include "host_common.h"
+#include "sm100.cuh"
+
+namespace owl {
+
+__device__ __forceinline__ void fl_unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 fl_pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+// x, z: [rows, inner] bf16 (inner % 8 == 0), t: [rows] (one timestep per (batch, frame) row), bf16
+__global__ void __launch_bounds__(256)
+rf_noise_kernel(const bf16* __restrict__ x, const bf16* __restrict__ z, const bf16* __restrict__ t, bf16* __restrict__ lerpd,
+                bf16* __restrict__ target, int64_t rows, int inner8) {
+  pdl_prologue();
+  const int64_t total = rows * inner8;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t r = i / inner8;
+    const float tt = __bfloat162float(t[r]);
+    float fx[8], fz[8], l[8], tg[8];
+    fl_unpack8(__ldg(reinterpret_cast<const uint4*>(x) + i), fx);
+    fl_unpack8(__ldg(reinterpret_cast<const uint4*>(z) + i), fz);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      // the reference evaluates x * (1 - t) + z * t in the tensors' dtype: each product and the sum round to bf16
+      l[j] = round_bf16(round_bf16(fx[j] * round_bf16(1.f - tt)) + round_bf16(fz[j] * tt));
+      tg[j] = fz[j] - fx[j];
+    }
+    reinterpret_cast<uint4*>(lerpd)[i] = fl_pack8(l);
+    reinterpret_cast<uint4*>(target)[i] = fl_pack8(tg);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+mse_fwd_kernel(const bf16* __restrict__ pred, const bf16* __restrict__ target, float* __restrict__ loss, int64_t n8,
+               float inv_n) {
+  pdl_prologue();
+  __shared__ float s_part[8];
+  float acc = 0.f;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float p[8], t[8];
+    fl_unpack8(__ldg(reinterpret_cast<const uint4*>(pred) + i), p);
+    fl_unpack8(__ldg(reinterpret_cast<const uint4*>(target) + i), t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = p[j] - t[j];
+      acc = fmaf(d, d, acc);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += s_part[w];
+    atomicAdd(loss, s * inv_n);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+mse_bwd_kernel(const bf16* __restrict__ pred, const bf16* __restrict__ target, const float* __restrict__ dloss,
+               bf16* __restrict__ dpred, int64_t n8, float two_over_n) {
+  pdl_prologue();
+  const float g = __ldg(dloss) * two_over_n;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float p[8], t[8];
+    fl_unpack8(__ldg(reinterpret_cast<const uint4*>(pred) + i), p);
+    fl_unpack8(__ldg(reinterpret_cast<const uint4*>(target) + i), t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p[j] = (p[j] - t[j]) * g;
+    reinterpret_cast<uint4*>(dpred)[i] = fl_pack8(p);
+  }
+}
+
+static inline int fl_grid(int64_t items) {
+  int64_t b = (items + 255) / 256;
+  const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+  return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace owl
+
+using namespace owl;
+
+extern "C" {
+
+int owl_rf_noise(const void* x, const void* z, const void* t, void* lerpd, void* target, int64_t rows, int64_t inner,
+                 owl_stream_t stream) {
+  if (!x || !z || !t || !lerpd || !target || rows <= 0 || inner <= 0) return OWL_ERR_BAD_ARG;
+  if (inner % 8 != 0 || inner / 8 > INT32_MAX) return OWL_ERR_UNSUPPORTED;
+  if (!aligned16(x) || !aligned16(z) || !aligned16(lerpd) || !aligned16(target)) return OWL_ERR_ALIGN;
+  (void)launch_k(rf_noise_kernel, dim3(fl_grid(rows * (inner / 8))), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                 static_cast<const bf16*>(x), static_cast<const bf16*>(z), static_cast<const bf16*>(t),
+                 static_cast<bf16*>(lerpd), static_cast<bf16*>(target), rows, static_cast<int>(inner / 8));
+  return launch_status();
+}
+
+int owl_mse_fwd(const void* pred, const void* target, float* loss, int64_t n, owl_stream_t stream) {
+  if (!pred || !target || !loss || n <= 0) return OWL_ERR_BAD_ARG;
+  if (n % 8 != 0) return OWL_ERR_UNSUPPORTED;
+  if (!aligned16(pred) || !aligned16(target)) return OWL_ERR_ALIGN;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemsetAsync(loss, 0, sizeof(float), s);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  LaunchOpts lo;
+  lo.pdl = false;   // follows a memset node
+  e = launch_kx(lo, mse_fwd_kernel, dim3(fl_grid(n / 8)), dim3(256), 0, s, static_cast<const bf16*>(pred),
+                static_cast<const bf16*>(target), loss, n / 8, 1.0f / static_cast<float>(n));
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return static_cast<int>(e);
+  }
+  return launch_status();
+}
+
+int owl_mse_bwd(const void* pred, const void* target, const float* dloss, void* dpred, int64_t n, owl_stream_t stream) {
+  if (!pred || !target || !dloss || !dpred || n <= 0) return OWL_ERR_BAD_ARG;
+  if (n % 8 != 0) return OWL_ERR_UNSUPPORTED;
+  if (!aligned16(pred) || !aligned16(target) || !aligned16(dpred)) return OWL_ERR_ALIGN;
+  (void)launch_k(mse_bwd_kernel, dim3(fl_grid(n / 8)), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                 static_cast<const bf16*>(pred), static_cast<const bf16*>(target), dloss, static_cast<bf16*>(dpred), n / 8,
+                 2.0f / static_cast<float>(n));
+  return launch_status();
+}
+
+}  // extern "C"

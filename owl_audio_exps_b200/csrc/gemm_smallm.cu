@@ -29,7 +29,11 @@ static constexpr int kSmBK = 64;
 static constexpr int kSmABytes = 128 * kSmBK * 2;
 static constexpr int kSmMaxStages = 8;
 static constexpr int kSmSmemLimit = 232448;
-static constexpr int kSmSmemPerCta = 113 * 1024;   // two CTAs (of consecutive kernels) per SM
+// Measured (tools/smallm_bench.py, B200): a ring of 8 stages and one CTA per SM beats 3-4 stages with two CTAs per SM
+// (qkv 13.3 vs 14.0 us, conditioning bank 29.5 vs 40.6 us): all k-blocks of a chunk in flight at once means 1 KB of
+// consecutive bytes per weight row at the DRAM, and the next kernel's CTA still starts (and prefetches) as soon as this
+// kernel's CTA on the same SM has exited.
+static constexpr int kSmSmemPerCta = kSmSmemLimit;
 
 struct SmallMParams {
   int M, N, K;
@@ -44,7 +48,14 @@ struct SmallMParams {
   long long ldgate;
   float* ws;            // [tiles_n][128][BN] fp32, zero between launches
   unsigned* counters;   // [tiles_n], zero between launches
+  const char* next_w;   // weights of the NEXT Linear of the schedule (or nullptr): pulled into L2 while this one reduces
+  long long next_bytes;
 };
+
+// L2 prefetch of [addr, addr + bytes): one bulk request per 16 KB (cp.async.bulk.prefetch.L2; no destination, no barrier)
+__device__ __forceinline__ void l2_prefetch_bulk(const char* addr, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(addr), "r"(bytes) : "memory");
+}
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -114,7 +125,7 @@ __device__ __forceinline__ void finish32(const SmallMParams& p, const float* s_b
 }
 
 template <int BN>
-__global__ void __launch_bounds__(kSmThreads, 2)
+__global__ void __launch_bounds__(kSmThreads, 1)
 gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const SmallMParams p) {
   constexpr int kBBytes = BN * kSmBK * 2;
   constexpr int kStageBytes = kSmABytes + kBBytes;
@@ -155,9 +166,9 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
   const int total = p.tiles_n * p.splits;
   // WEIGHT PREFETCH AHEAD OF THE GRID DEPENDENCY.  The weights do not depend on the previous kernel, only the activations
-  // do: under programmatic dependent launch this CTA is resident while the previous kernel still runs (two CTAs fit an SM:
-  // <= 113 KB of shared memory each), so the producer fills the ring with the first weight tiles BEFORE
-  // griddepcontrol.wait and HBM keeps streaming across the kernel boundary (reduction round trips, launch, flush).
+  // do: under programmatic dependent launch this CTA becomes resident while the previous kernel is still draining (its
+  // CTA on this SM has exited, others are in their reduction round trips), so the producer fills the ring with the first
+  // weight tiles BEFORE griddepcontrol.wait and HBM keeps streaming across the kernel boundary.
   int pre = 0;
   if (warp == 0 && lane == 0 && static_cast<int>(blockIdx.x) < total) {
     const int t = blockIdx.x;
@@ -227,6 +238,18 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     float* s_bias = reinterpret_cast<float*>(smem + 512);   // this tile's BN bias values
     int as = 0;
     uint32_t aphase = 0;
+    if (elected && p.next_w != nullptr) {
+      // this CTA's share of the next Linear's weights -> L2.  The decode step is a chain of short dependent kernels;
+      // between two GEMMs HBM would idle through reduction round trips, launches and the small kernels in between.  The
+      // requests ride behind this kernel's own (already issued) ring fill; the next GEMM then streams from the 126 MB L2.
+      const long long chunk = 16384;
+      const long long n_chunks = (p.next_bytes + chunk - 1) / chunk;
+      for (long long c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        const long long off = c * chunk;
+        const long long left = p.next_bytes - off;
+        l2_prefetch_bulk(p.next_w + off, static_cast<unsigned>((left < chunk ? left : chunk) & ~15LL));
+      }
+    }
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
       const int tn = t % p.tiles_n;
       const int n0 = tn * BN;
@@ -368,7 +391,8 @@ int64_t owl_gemm_smallm_workspace_bytes(int64_t N) {
 }
 
 int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
-                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, owl_stream_t stream) {
+                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, const void* next_w,
+                    int64_t next_bytes, owl_stream_t stream) {
   if (!A || !W || !epi || !epi->out0 || M <= 0 || N <= 0 || K <= 0) return OWL_ERR_BAD_ARG;
   if (M > 128) return OWL_ERR_UNSUPPORTED;
   if (N % 8 != 0 || K % 8 != 0) return OWL_ERR_UNSUPPORTED;
@@ -382,6 +406,10 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
   p.bias = epi->bias;
   p.out = static_cast<bf16*>(epi->out0);
   p.ldo = epi->ld0;
+  if (next_w != nullptr && next_bytes > 0 && aligned16(next_w)) {
+    p.next_w = static_cast<const char*>(next_w);
+    p.next_bytes = next_bytes;
+  }
   switch (p.mode) {
     case OWL_EPI_STORE:
     case OWL_EPI_BIAS_SILU:   // single output here: silu(bf16(x W^T + b)); the pre-activation is not kept (no backward)

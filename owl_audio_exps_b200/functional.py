@@ -1046,6 +1046,41 @@ class DiTBlockFn(torch.autograd.Function):
                 g_wa1, g_ba1, g_wg1, g_bg1, g_wa2, g_ba2, g_wg2, g_bg2)
 
 
+class _MSE(torch.autograd.Function):
+    """mean((pred - target)^2) in fp32 from bf16 operands, one pass each way (models/*.py: F.mse_loss(pred.float(),
+    target.float()))."""
+
+    @staticmethod
+    def forward(ctx, pred, target):
+        p16, t16 = _as_bf16(pred), _as_bf16(target)
+        ctx.save_for_backward(p16, t16)
+        ctx.meta = (pred.dtype, pred.shape)
+        return ops.mse_fwd(p16, t16)
+
+    @staticmethod
+    def backward(ctx, dloss):
+        p16, t16 = ctx.saved_tensors
+        dtype, shape = ctx.meta
+        d = ops.mse_bwd(p16, t16, dloss.to(f32).contiguous())
+        return d.view(shape).to(dtype), None
+
+
+def mse_loss(pred, target):
+    """Fused MSE for bf16 predictions whose element count is a multiple of 8; anything else takes torch's kernel."""
+    if pred.is_cuda and pred.dtype == bf16 and target.dtype == bf16 and pred.numel() % 8 == 0 and pred.shape == target.shape:
+        return _MSE.apply(pred.contiguous(), target.detach().contiguous())
+    return torch.nn.functional.mse_loss(pred.float(), target.float())
+
+
+def rf_noise(x, z, t):
+    """(lerpd, target) = (x (1 - t) + z t, z - x) with t broadcast over the trailing dims of x (one launch for bf16)."""
+    inner = x.numel() // max(t.numel(), 1)
+    if x.is_cuda and x.dtype == bf16 and z.dtype == bf16 and inner % 8 == 0 and x.shape[:t.dim()] == t.shape:
+        return ops.rf_noise(x.contiguous(), z.contiguous(), t.to(bf16).contiguous())
+    tt = t.view(*t.shape, *([1] * (x.dim() - t.dim())))
+    return x * (1 - tt) + z * tt, z - x
+
+
 def _fresh_or_sink(p: torch.Tensor, needed: bool):
     """(fp32 destination for a fused bias column-sum, accumulate flag, destination is a bucket sink)."""
     if not needed:

@@ -43,7 +43,8 @@ class AudioRFT(nn.Module):
 
     def noise(self, tensor, ts):
         z = torch.randn_like(tensor)
-        return tensor * (1 - ts) + z * ts, z - tensor, z
+        lerpd, target = OF.rf_noise(tensor, z, ts.reshape(ts.shape[:2]))     # one pass for both (bf16 latents)
+        return lerpd, target, z
 
     def forward(self, x, doc_id=None, return_dict=False):
         B, n_latents, _ = x.shape
@@ -51,7 +52,7 @@ class AudioRFT(nn.Module):
             ts = torch.randn(B, n_latents, device=x.device, dtype=x.dtype).sigmoid()
             lerpd_audio, target_audio, z_audio = self.noise(x, ts[:, :, None])
         pred_audio = self.core(lerpd_audio, ts, doc_id)
-        loss = F.mse_loss(pred_audio.float(), target_audio.float())
+        loss = OF.mse_loss(pred_audio, target_audio)
         if not return_dict:
             return loss
         return {"diffusion_loss": loss, "audio_loss": loss, "lerpd_audio": lerpd_audio, "pred_audio": pred_audio,

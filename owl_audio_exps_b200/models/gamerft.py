@@ -72,7 +72,8 @@ class GameRFT(nn.Module):
 
     def noise(self, tensor, ts):
         z = torch.randn_like(tensor)
-        return tensor * (1 - ts) + z * ts, z - tensor, z
+        lerpd, target = OF.rf_noise(tensor, z, ts.reshape(ts.shape[:2]))     # one pass for both (bf16 latents)
+        return lerpd, target, z
 
     def forward(self, x, mouse=None, btn=None, doc_id=None, return_dict=False, cfg_prob=None, has_controls=None):
         B, S = x.size(0), x.size(1)
@@ -85,7 +86,7 @@ class GameRFT(nn.Module):
             ts = torch.randn(B, S, device=x.device, dtype=x.dtype).sigmoid()
             lerpd_video, target_video, z_video = self.noise(x, ts[:, :, None, None, None])
         pred_video = self.core(lerpd_video, ts, mouse, btn, doc_id, has_controls)
-        loss = F.mse_loss(pred_video.float(), target_video.float())
+        loss = OF.mse_loss(pred_video, target_video)
         if not return_dict:
             return loss
         return {"diffusion_loss": loss, "video_loss": loss, "lerpd_video": lerpd_video, "pred_video": pred_video,

@@ -111,11 +111,11 @@ class GameRFTAudio(nn.Module):
             ts = torch.randn(b, n, device=x.device, dtype=x.dtype).sigmoid()
             tv, ta = ts[:, :, None, None, None], ts.unsqueeze(-1)
             z_video, z_audio = torch.randn_like(x), torch.randn_like(audio)
-            lerpd_video, target_video = x * (1.0 - tv) + z_video * tv, z_video - x
-            lerpd_audio, target_audio = audio * (1.0 - ta) + z_audio * ta, z_audio - audio
+            lerpd_video, target_video = OF.rf_noise(x, z_video, ts)
+            lerpd_audio, target_audio = OF.rf_noise(audio, z_audio, ts)
         pred_video, pred_audio = self.core(lerpd_video, lerpd_audio, ts, mouse, btn, has_controls)
-        video_loss = F.mse_loss(pred_video.float(), target_video.float())
-        audio_loss = F.mse_loss(pred_audio.float(), target_audio.float())
+        video_loss = OF.mse_loss(pred_video, target_video)
+        audio_loss = OF.mse_loss(pred_audio, target_audio)
         diff_loss = video_loss + audio_loss
         if not return_dict:
             return diff_loss, video_loss, audio_loss

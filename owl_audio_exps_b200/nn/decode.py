@@ -151,7 +151,7 @@ def dit_decode_forward(dit, x, cond, ring: RingKVCache):
     per_layer, wc, bc = _stack_operands(dit)
     n_layers = len(dit.blocks)
     mod_all = torch.empty(R, 6 * d * n_layers, device=dev, dtype=bf16)
-    ops.gemm_smallm(scond, wc, R, 6 * d * n_layers, d, bias=bc, out0=mod_all)
+    ops.gemm_smallm(scond, wc, R, 6 * d * n_layers, d, bias=bc, out0=mod_all, next_w=per_layer[0]["wqkv"])
     q = torch.empty(B, H, L, dh, device=dev, dtype=bf16)
     qkv = torch.empty(B, L, 3 * d, device=dev, dtype=bf16)
     o = torch.empty(B, L, d, device=dev, dtype=bf16)
@@ -163,18 +163,19 @@ def dit_decode_forward(dit, x, cond, ring: RingKVCache):
         a2, b2, c2 = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], mod[:, 5 * d:6 * d]
         attn = blk.attn
         h1, _ = ops.adaln_modulate_fwd(x2, a1, b1, T, OF.RMS_EPS, want_rstd=False)
-        ops.gemm_smallm(h1, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d))
+        nxt = per_layer[i + 1]["wqkv"] if i + 1 < n_layers else None
+        ops.gemm_smallm(h1, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d), next_w=W["wout"])
         ops.qk_norm_rope_decode(qkv, attn.rope.cos, attn.rope.sin, ring.state, q, ring.k[i], ring.v[i], H, OF.RMS_EPS)
         vis = attn.local_offset if attn.local else 0
         ops.attn_decode(q, ring.k[i], ring.v[i], ring.state, vis, out=o)
         x1 = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm_smallm(o.view(M, d), W["wout"], M, d, d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["bout"], out0=x1, aux0=x2,
-                        aux1=c1, rows_per_frame=T)
+                        aux1=c1, rows_per_frame=T, next_w=W["w1"])
         h2, _ = ops.adaln_modulate_fwd(x1, a2, b2, T, OF.RMS_EPS, want_rstd=False)
-        ops.gemm_smallm(h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s)
+        ops.gemm_smallm(h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"])
         x2n = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm_smallm(s, W["w2"], M, d, 4 * d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["b2"], out0=x2n, aux0=x1, aux1=c2,
-                        rows_per_frame=T)
+                        rows_per_frame=T, next_w=nxt)
         x2 = x2n
     out = x2.view(B, L, d)
     return out if x.dtype == bf16 else out.to(x.dtype)

@@ -190,8 +190,10 @@ def _smallm_workspace(dev: torch.device, N: int) -> torch.Tensor:
 @_prof("gemm_smallm", lambda a, w, M, N, K, **k: 2.0 * M * N * K)
 def gemm_smallm(a: torch.Tensor, w: torch.Tensor, M: int, N: int, K: int, *, mode: int = OWL_EPI_STORE,
                 bias: Optional[torch.Tensor] = None, out0: Optional[torch.Tensor] = None,
-                aux0: Optional[torch.Tensor] = None, aux1: Optional[torch.Tensor] = None, rows_per_frame: int = 1) -> None:
-    """out0[M <= 128, N] = epi(a[M, K] . w[N, K]^T + bias): the decode regime's weight-streaming GEMM (owl_gemm_smallm)."""
+                aux0: Optional[torch.Tensor] = None, aux1: Optional[torch.Tensor] = None, rows_per_frame: int = 1,
+                next_w: Optional[torch.Tensor] = None) -> None:
+    """out0[M <= 128, N] = epi(a[M, K] . w[N, K]^T + bias): the decode regime's weight-streaming GEMM (owl_gemm_smallm).
+    `next_w`: the (contiguous) weight matrix the next Linear of the schedule reads, prefetched into L2 meanwhile."""
     _req(a), _req(w), _req(out0)
     e = GemmEpilogue()
     e.mode, e.rows_per_frame = mode, rows_per_frame
@@ -204,8 +206,9 @@ def gemm_smallm(a: torch.Tensor, w: torch.Tensor, M: int, N: int, K: int, *, mod
     if aux1 is not None:
         e.aux1, e.lda1 = aux1.data_ptr(), _ld(aux1)
     ws = _smallm_workspace(a.device, N)
+    nw, nb = (next_w.data_ptr(), next_w.numel() * next_w.element_size()) if next_w is not None else (None, 0)
     rc = _lib.load().owl_gemm_smallm(M, N, K, a.data_ptr(), _ld(a), w.data_ptr(), _ld(w), C.byref(e), ws.data_ptr(),
-                                     ws.numel(), _stream())
+                                     ws.numel(), nw, nb, _stream())
     if rc != 0:
         _lib.check(rc, "owl_gemm_smallm")
 
@@ -591,3 +594,36 @@ def attn_decode(q, k_cache, v_cache, state, vis_rows: int = 0, out=None):
 def decode_state_advance(state, commit_rows: int, drop_rows: int, cap: int) -> None:
     _lib.check(_lib.load().owl_decode_state_advance(state.data_ptr(), commit_rows, drop_rows, cap, _stream()),
                "owl_decode_state_advance")
+
+
+# ------------------------------------------------------------------------------------------------
+# rectified-flow glue (owl_rf_noise / owl_mse_fwd / owl_mse_bwd)
+# ------------------------------------------------------------------------------------------------
+@_prof("rf_noise")
+def rf_noise(x, z, t):
+    """x, z bf16 [rows..., inner...] contiguous, t bf16 with one value per leading row -> (lerpd, target) bf16."""
+    _req(x), _req(z), _req(t)
+    rows = t.numel()
+    inner = x.numel() // rows
+    lerpd, target = torch.empty_like(x), torch.empty_like(x)
+    rc = _lib.load().owl_rf_noise(x.data_ptr(), z.data_ptr(), t.data_ptr(), lerpd.data_ptr(), target.data_ptr(), rows, inner,
+                                  _stream())
+    _lib.check(rc, "owl_rf_noise")
+    return lerpd, target
+
+
+@_prof("mse_fwd")
+def mse_fwd(pred, target):
+    _req(pred), _req(target)
+    loss = torch.empty((), device=pred.device, dtype=torch.float32)
+    _lib.check(_lib.load().owl_mse_fwd(pred.data_ptr(), target.data_ptr(), loss.data_ptr(), pred.numel(), _stream()),
+               "owl_mse_fwd")
+    return loss
+
+
+@_prof("mse_bwd")
+def mse_bwd(pred, target, dloss):
+    dpred = torch.empty_like(pred)
+    _lib.check(_lib.load().owl_mse_bwd(pred.data_ptr(), target.data_ptr(), dloss.data_ptr(), dpred.data_ptr(), pred.numel(),
+                                       _stream()), "owl_mse_bwd")
+    return dpred

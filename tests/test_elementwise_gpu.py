@@ -158,3 +158,29 @@ def test_layer_norm_fwd_bwd_vs_torch(M, d):
     assert y.dtype == torch.bfloat16
     assert (y.float() - yr).abs().max() <= 2 ** -7 * yr.abs().max()
     assert (xa.grad.float() - xr.grad).abs().max() <= 2 ** -7 * xr.grad.abs().max()
+
+
+def test_rf_noise_and_fused_mse_vs_torch():
+    """owl_rf_noise / owl_mse_fwd / owl_mse_bwd against the reference's torch expressions (models/gamerft.py:93-96,
+    F.mse_loss(pred.float(), target.float())) on bf16 latents."""
+    from owl_audio_exps_b200 import functional as OF
+    dev = "cuda:0"
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(2, 5, 16, 8, 8, generator=g).to(torch.bfloat16).to(dev)
+    z = torch.randn(2, 5, 16, 8, 8, generator=g).to(torch.bfloat16).to(dev)
+    t = torch.rand(2, 5, generator=g).to(torch.bfloat16).to(dev)
+    lerpd, target = OF.rf_noise(x, z, t)
+    tv = t[:, :, None, None, None]
+    assert torch.equal(lerpd, x * (1 - tv) + z * tv) and torch.equal(target, z - x)
+    pred = torch.randn(2, 5, 16, 8, 8, generator=g).to(torch.bfloat16).to(dev).requires_grad_(True)
+    loss = OF.mse_loss(pred, target)
+    ref_in = pred.detach().clone().requires_grad_(True)
+    ref = torch.nn.functional.mse_loss(ref_in.float(), target.float())
+    assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
+    (loss * 3.0).backward()
+    (ref * 3.0).backward()
+    assert relerr(pred.grad, ref_in.grad) <= 1e-2
+    # shapes the fused kernels do not take fall back to the torch expressions
+    xo = torch.randn(3, 7, 5, device=dev)
+    l2, t2 = OF.rf_noise(xo, torch.ones_like(xo), torch.full((3, 7), 0.25, device=dev))
+    assert torch.allclose(l2, xo * 0.75 + 0.25) and torch.allclose(t2, 1 - xo)

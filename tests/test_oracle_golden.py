@@ -215,3 +215,14 @@ def test_av_cached_rollout_matches_reference_sampler():
                                   fx["cfg_scale"], fx["noise_prev"], fx["max_window"], noise)
     assert next(draws, None) is None
     assert relerr(out, fx["out"]) < 5 * TOL
+
+
+def test_oracle_newton_schulz_matches_reference_muon():
+    """oracle.newton_schulz5 (bf16 iteration) == owl_wms/muon.py:11-38 run by tests/golden/make_golden_muon.py, bit for bit;
+    the fp32 iteration of the same recurrence stays within bf16 iteration noise of it."""
+    import os
+    from helpers import GOLDEN
+    fx = torch.load(os.path.join(GOLDEN, "muon_ns5.pt"), map_location="cpu", weights_only=False)
+    for G, ref in zip(fx["G"], fx["out"]):
+        assert torch.equal(O.newton_schulz5(G, fx["steps"], torch.bfloat16).float(), ref)
+        assert relerr(O.newton_schulz5(G, fx["steps"]), ref) <= 6e-2
