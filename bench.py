@@ -360,8 +360,11 @@ def run_owl(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": w["name"], "per_gpu_batch": B, "tokens_per_sample": L, "d_model": d,
                        "n_layers": cfg.n_layers, "n_heads": cfg.n_heads, "params": n_params, "parallelism": f"dp{world}",
-                       "step": "DiT stack fwd + bwd + grad all-reduce (bucket per block, overlapped; wire dtype "
-                               + ("bf16" if buckets.comm_dtype == torch.bfloat16 else "fp32") + "); optimizer excluded",
+                       "step": "DiT stack fwd + bwd + grad all-reduce (bucket per block, overlapped; "
+                               + ("copy-engine peer copies over symmetric memory + shard-reduce kernel, fp32"
+                                  if getattr(buckets, "exchange", None) is not None else
+                                  "ncclAllReduce, wire dtype " + ("bf16" if buckets.comm_dtype == torch.bfloat16 else "fp32"))
+                               + "); optimizer excluded",
                        "cuda_graph": not args.no_graph,
                        "l2": "per-step working set (weights+grads+activations, >4 GB) exceeds the 126 MB L2; no flush"},
             "tokens_per_s_per_gpu": value / world,

@@ -45,6 +45,10 @@ uint64_t owl_launch_count(void);
  * NCCL CTAs when gradients are exchanged concurrently with backward (DDP overlap, rft_trainer.py:96): a persistent
  * grid sized to ALL SMs would queue one CTA behind the communication kernel and stretch that GEMM to two waves. */
 int owl_set_reserved_sms(int n);
+/* Bytes of shared memory per SM the persistent GEMM leaves unallocated from now on (host-side launch state, like
+ * owl_set_reserved_sms), so that a small CTA of a concurrently running kernel - the shard reduction of the copy-engine
+ * gradient exchange - can become resident next to a GEMM CTA instead of waiting for a kernel boundary.  0 = none. */
+int owl_set_coresident_reserve(int bytes);
 /* Debug aid: enqueue a one-thread kernel that stores the GPU's %globaltimer (ns) to *dst.  Used by
  * tools/step_trace.py to time phases INSIDE a replayed CUDA graph; never called on the product path. */
 int owl_debug_timestamp(uint64_t* dst, owl_stream_t stream);
@@ -111,11 +115,22 @@ int owl_gemm_bf16(int layout, int64_t M, int64_t N, int64_t K, const void* A, in
  * `workspace`: owl_gemm_smallm_workspace_bytes(N) bytes, ZERO before the first call; every call leaves it zero again.
  * Calls sharing a workspace must be ordered on one stream.
  * `next_w` / `next_bytes` (optional, NULL / 0): the weight matrix the NEXT Linear of the schedule will read; its bytes are
- * requested into L2 (cp.async.bulk.prefetch.L2) while this call reduces, so HBM keeps streaming across kernel boundaries. */
+ * requested into L2 (cp.async.bulk.prefetch.L2) while this call reduces, so HBM keeps streaming across kernel boundaries.
+ * `ln` (optional, NULL): adaLN as the A-operand transform (modulation.py:20-25; north_star: adaLN scale/shift fused into
+ * the GEMM prologue): A is the RAW residual stream and the kernel multiplies rms_norm(A) * (1 + a[m / T]) + b[m / T], built
+ * tile by tile in shared memory (the arithmetic of owl_adaln_modulate_fwd; the row statistic is summed per thread). */
+typedef struct owl_adaln_prologue {
+  const void* a;          /* bf16 [M / rows_per_frame, ld_ab]: scale                               */
+  const void* b;          /* bf16 [M / rows_per_frame, ld_ab]: shift                               */
+  int64_t ld_ab;
+  int32_t rows_per_frame; /* tokens per frame T                                                    */
+  float eps;              /* F.rms_norm epsilon                                                    */
+} owl_adaln_prologue;
+
 int64_t owl_gemm_smallm_workspace_bytes(int64_t N);
 int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
-                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, const void* next_w,
-                    int64_t next_bytes, owl_stream_t stream);
+                    const owl_gemm_epilogue* epi, const owl_adaln_prologue* ln, void* workspace, int64_t workspace_bytes,
+                    const void* next_w, int64_t next_bytes, owl_stream_t stream);
 
 /* Plain CUDA-core GEMM with the same contract (OWL_EPI_STORE / OWL_EPI_F32 only, no bias).
  * Verification aid for tests: an independent on-device answer at sizes where the CPU oracle is
@@ -329,6 +344,14 @@ int owl_attn_decode(const void* q, int64_t q_sb, int64_t q_sh, const void* k_cac
                     int64_t c_sh, int64_t cap, const int32_t* state, int64_t vis_rows, void* o, int64_t o_sb, int64_t o_sl,
                     int64_t B, int64_t H, int64_t Lq, int64_t dh, void* workspace, int64_t workspace_bytes,
                     owl_stream_t stream);
+/* owl_attn_decode_fused = owl_qk_norm_rope_decode + owl_attn_decode in ONE launch (north_star: RoPE fused into the Q/K
+ * load): every CTA builds its Q tile from qkv [B, Lq, 3*H*dh] with QK-RMSNorm + RoPE applied on the way into shared
+ * memory; the last KV split of each head builds the K / V tile of the new rows the same way, attends to it as one more
+ * tile and writes the rows into their ring slots for the calls that follow. */
+int owl_attn_decode_fused(const void* qkv, const float* cos_tab, const float* sin_tab, int64_t table_rows, void* k_cache,
+                          void* v_cache, int64_t c_sb, int64_t c_sh, int64_t cap, const int32_t* state, int64_t vis_rows,
+                          void* o, int64_t o_sb, int64_t o_sl, int64_t B, int64_t H, int64_t Lq, int64_t dh, float eps,
+                          void* workspace, int64_t workspace_bytes, owl_stream_t stream);
 int owl_qk_norm_rope_decode(const void* qkv, const float* cos_tab, const float* sin_tab, int64_t table_rows,
                             const int32_t* state, void* q, int64_t q_sb, int64_t q_sh, void* k_cache, void* v_cache,
                             int64_t c_sb, int64_t c_sh, int64_t cap, int64_t B, int64_t L, int64_t H, int64_t dh, float eps,
@@ -345,6 +368,12 @@ int owl_rf_noise(const void* x, const void* z, const void* t, void* lerpd, void*
                  owl_stream_t stream);
 int owl_mse_fwd(const void* pred, const void* target, float* loss, int64_t n, owl_stream_t stream);
 int owl_mse_bwd(const void* pred, const void* target, const float* dloss, void* dpred, int64_t n, owl_stream_t stream);
+
+/* Shard reduction of the copy-engine gradient exchange (engine.PeerExchange; replaces the reduction half of DDP's
+ * ncclAllReduce, rft_trainer.py:96): dst[i] = (dst[i] + sum_{j < n_src} srcs[j * src_stride + i]) * scale, fp32.  The peers'
+ * shards arrive by copy-engine peer copies; `max_ctas` bounds the grid (the kernel runs next to the backward GEMMs). */
+int owl_shard_reduce(float* dst, const float* srcs, int64_t src_stride, int n_src, int64_t n, float scale, int max_ctas,
+                     owl_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -26,6 +26,12 @@ class GemmEpilogue(C.Structure):
     ]
 
 
+class AdaLNPrologue(C.Structure):
+    """struct owl_adaln_prologue (include/owl_dit.h)."""
+
+    _fields_ = [("a", vp), ("b", vp), ("ld_ab", i64), ("rows_per_frame", i32), ("eps", f32)]
+
+
 class AttnMask(C.Structure):
     """struct owl_attn_mask (include/owl_dit.h)."""
 
@@ -46,11 +52,13 @@ SIGNATURES = {
     "owl_error_string": ([C.c_int], C.c_char_p),
     "owl_launch_count": ([], C.c_uint64),
     "owl_set_reserved_sms": ([C.c_int], C.c_int),
+    "owl_set_coresident_reserve": ([C.c_int], C.c_int),
     "owl_cast_f32_bf16_multi": ([vp, vp, vp, C.c_int, vp], C.c_int),
     "owl_debug_timestamp": ([vp, vp], C.c_int),
     "owl_gemm_bf16": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp], C.c_int),
     "owl_gemm_smallm_workspace_bytes": ([i64], i64),
-    "owl_gemm_smallm": ([i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp, i64, vp, i64, vp], C.c_int),
+    "owl_gemm_smallm": ([i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), C.POINTER(AdaLNPrologue), vp, i64, vp,
+                         i64, vp], C.c_int),
     "owl_gemm_bf16_check": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, vp, i64, vp], C.c_int),
     "owl_cast_f32_bf16": ([vp, vp, i64, vp], C.c_int),
     "owl_silu_bf16": ([vp, vp, i64, vp], C.c_int),
@@ -77,9 +85,12 @@ SIGNATURES = {
     "owl_attn_decode_workspace_bytes": ([i64, i64, i64, i64], i64),
     "owl_attn_decode": ([vp, i64, i64, vp, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, vp, i64, vp],
                         C.c_int),
+    "owl_attn_decode_fused": ([vp, vp, vp, i64, vp, vp, i64, i64, i64, vp, i64, vp, i64, i64, i64, i64, i64, i64, f32, vp, i64,
+                               vp], C.c_int),
     "owl_qk_norm_rope_decode": ([vp, vp, vp, i64, vp, vp, i64, i64, vp, vp, i64, i64, i64, i64, i64, i64, i64, f32, vp],
                                 C.c_int),
     "owl_decode_state_advance": ([vp, i64, i64, i64, vp], C.c_int),
+    "owl_shard_reduce": ([vp, vp, i64, C.c_int, i64, f32, C.c_int, vp], C.c_int),
     "owl_rf_noise": ([vp, vp, vp, vp, vp, i64, i64, vp], C.c_int),
     "owl_mse_fwd": ([vp, vp, vp, i64, vp], C.c_int),
     "owl_mse_bwd": ([vp, vp, vp, vp, i64, vp], C.c_int),

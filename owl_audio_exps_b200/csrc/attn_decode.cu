@@ -64,7 +64,67 @@ struct AttnDecodeParams {
   float* part_o;       // [B*H][n_splits][128][DH]
   float* part_ml;      // [B*H][n_splits][128][2]
   unsigned* counters;  // [B*H], zero between launches
+  // FUSED variant (owl_attn_decode_fused): Q / K / V of the new rows come straight from the qkv GEMM output
+  const bf16* qkv;     // [B, Lq, 3, H, DH]
+  const float* cos_tab;
+  const float* sin_tab;
+  long long table_rows;
+  bf16* k_cache;       // ring buffers [B, H, cap, DH] (strides c_sb, c_sh): the new rows are written here too
+  bf16* v_cache;
+  long long c_sb, c_sh;
+  float eps;
 };
+
+// One head row of qkv (DH bf16 at `src`) -> QK-RMSNorm + RoPE (attn.py:83-89, rope.py:43-51; the arithmetic of
+// qk_norm_rope_fwd_kernel) as DH/8 16-byte chunks in the output order [y_even | y_odd]; `rotate` false: raw copy (V).
+template <int DH>
+__device__ __forceinline__ void norm_rope_row(const bf16* __restrict__ src, const float* __restrict__ cos_row,
+                                              const float* __restrict__ sin_row, float eps, bool rotate, uint4 (&out)[DH / 8]) {
+  uint4 raw[DH / 8];
+#pragma unroll
+  for (int c = 0; c < DH / 8; ++c) raw[c] = __ldg(reinterpret_cast<const uint4*>(src) + c);
+  if (!rotate) {
+#pragma unroll
+    for (int c = 0; c < DH / 8; ++c) out[c] = raw[c];
+    return;
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int c = 0; c < DH / 8; ++c) {
+    const uint32_t w[4] = {raw[c].x, raw[c].y, raw[c].z, raw[c].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float lo = bf16_lo(w[j]), hi = bf16_hi(w[j]);
+      ss += lo * lo;
+      ss += hi * hi;
+    }
+  }
+  const float rstd = rsqrtf(ss * (1.f / static_cast<float>(DH)) + eps);
+  // chunk c of the raw row holds pairs 4c .. 4c+3; their rotated values go to positions 4c.. of each half
+  uint32_t y0[DH / 4], y1[DH / 4];   // packed pairs of the even / odd half: index p/2 holds pairs (p, p+1)
+#pragma unroll
+  for (int c = 0; c < DH / 8; ++c) {
+    const float4 c4 = __ldg(reinterpret_cast<const float4*>(cos_row) + c);
+    const float4 s4 = __ldg(reinterpret_cast<const float4*>(sin_row) + c);
+    const float cs[4] = {c4.x, c4.y, c4.z, c4.w}, sn[4] = {s4.x, s4.y, s4.z, s4.w};
+    const uint32_t w[4] = {raw[c].x, raw[c].y, raw[c].z, raw[c].w};
+    float e[4], o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float x0 = round_bf16(bf16_lo(w[j]) * rstd), x1 = round_bf16(bf16_hi(w[j]) * rstd);
+      e[j] = x0 * cs[j] - x1 * sn[j];
+      o[j] = x1 * cs[j] + x0 * sn[j];
+    }
+    y0[2 * c] = pack_bf16(e[0], e[1]); y0[2 * c + 1] = pack_bf16(e[2], e[3]);
+    y1[2 * c] = pack_bf16(o[0], o[1]); y1[2 * c + 1] = pack_bf16(o[2], o[3]);
+  }
+  // halves: [y0 (DH/2 values = DH/16 chunks) | y1]
+#pragma unroll
+  for (int c = 0; c < DH / 16; ++c) {
+    out[c] = make_uint4(y0[4 * c], y0[4 * c + 1], y0[4 * c + 2], y0[4 * c + 3]);
+    out[DH / 16 + c] = make_uint4(y1[4 * c], y1[4 * c + 1], y1[4 * c + 2], y1[4 * c + 3]);
+  }
+}
 
 template <int DH>
 struct DecCfg {
@@ -81,7 +141,7 @@ struct DecCfg {
 
 static constexpr int kDecThreads = 192;
 
-template <int DH>
+template <int DH, bool FUSED>
 __global__ void __launch_bounds__(kDecThreads, DH == 64 ? 2 : 1)
 attn_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const AttnDecodeParams p) {
@@ -130,18 +190,24 @@ attn_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   pdl_launch();
   const uint32_t tS = tmem_base, tO = tmem_base + 128;
 
-  const RingView ring = ring_view(p.state, p.Lq, p.vis_rows, p.cap);
+  RingView ring = ring_view(p.state, p.Lq, p.vis_rows, p.cap);
+  // FUSED: the new rows are not read back from their ring slots; the LAST split of a head builds them in shared memory
+  // as one extra KV tile (it = 0, ring stage 0) and writes them to the ring for the calls that follow
+  const bool has_new = FUSED && split == p.n_splits - 1;
+  if (FUSED) ring.len -= p.Lq;   // cache tiles: cached rows only (vis_lo was taken over [cache, new]: len >= Lq here or < 0)
   const int tile_lo = split * p.tiles_per_split;
   const int tile_hi = min(tile_lo + p.tiles_per_split, p.tiles_total);
-  int n_kv = 0;  // tiles of this split that hold at least one visible row (every role walks the same list)
+  int n_kv = has_new ? 1 : 0;  // tiles of this split that hold at least one visible row (every role walks the same list)
   for (int t = tile_lo; t < tile_hi; ++t) n_kv += ring.tile_any(t * kTile) ? 1 : 0;
 
   if (warp == 0) {
     if (lane == 0 && n_kv > 0) {
-      mbar_arrive_expect_tx(q_full, Cfg::kTileBytes);
+      if (!FUSED) {
+        mbar_arrive_expect_tx(q_full, Cfg::kTileBytes);
 #pragma unroll
-      for (int pn = 0; pn < DH / 64; ++pn) tma_load_4d(smem + pn * kPanelBytes, &tmQ, q_full, pn * 64, 0, h, b);
-      int it = 0;
+        for (int pn = 0; pn < DH / 64; ++pn) tma_load_4d(smem + pn * kPanelBytes, &tmQ, q_full, pn * 64, 0, h, b);
+      }
+      int it = has_new ? 1 : 0;    // stage 0 of the first round belongs to the tile of new rows
       for (int t = tile_lo; t < tile_hi; ++t) {
         if (!ring.tile_any(t * kTile)) continue;
         const int s = it & 1;
@@ -192,14 +258,56 @@ attn_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const bool row_ok = row < p.Lq;
     float m_run = -INFINITY, l_run = 0.f;
     uint8_t* sP = smem + Cfg::kOffP;
+    if (FUSED && n_kv > 0) {
+      // ---- Q tile (and, in the last split, the K / V tile of the new rows) straight from the qkv GEMM output:
+      // QK-RMSNorm + RoPE applied on the way into shared memory (thread = row), swizzled as TMA would have written it
+      const long long pos = min(static_cast<long long>(p.state[2]) + row, p.table_rows - 1);
+      const float* cr = p.cos_tab + pos * (DH / 2);
+      const float* sr = p.sin_tab + pos * (DH / 2);
+      const bf16* tok = p.qkv + (static_cast<long long>(b) * p.Lq + row) * (3LL * p.H * DH) + static_cast<long long>(h) * DH;
+      uint4 chunk[DH / 8];
+      if (row_ok) {
+        norm_rope_row<DH>(tok, cr, sr, p.eps, true, chunk);
+      } else {
+#pragma unroll
+        for (int c = 0; c < DH / 8; ++c) chunk[c] = make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int c = 0; c < DH / 8; ++c) *reinterpret_cast<uint4*>(smem + tile_chunk_offset(row, c)) = chunk[c];
+      if (has_new) {
+        const int slot = static_cast<int>((static_cast<long long>(p.state[1]) + p.state[0] + row) % p.cap);
+        bf16* kdst = p.k_cache + b * p.c_sb + h * p.c_sh + static_cast<long long>(slot) * DH;
+        bf16* vdst = p.v_cache + b * p.c_sb + h * p.c_sh + static_cast<long long>(slot) * DH;
+        if (row_ok) norm_rope_row<DH>(tok + static_cast<long long>(p.H) * DH, cr, sr, p.eps, true, chunk);
+#pragma unroll
+        for (int c = 0; c < DH / 8; ++c) {
+          *reinterpret_cast<uint4*>(smem + Cfg::kOffK + tile_chunk_offset(row, c)) = chunk[c];   // rows >= Lq: zeros
+          if (row_ok) reinterpret_cast<uint4*>(kdst)[c] = chunk[c];
+        }
+        if (row_ok) norm_rope_row<DH>(tok + 2LL * p.H * DH, cr, sr, p.eps, false, chunk);
+#pragma unroll
+        for (int c = 0; c < DH / 8; ++c) {
+          *reinterpret_cast<uint4*>(smem + Cfg::kOffV + tile_chunk_offset(row, c)) = chunk[c];
+          if (row_ok) reinterpret_cast<uint4*>(vdst)[c] = chunk[c];
+        }
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+      if (threadIdx.x == 64) {
+        mbar_arrive(q_full);
+        if (has_new) mbar_arrive(&kv_full[0]);
+      }
+    }
     int it = 0;
-    for (int t = tile_lo; t < tile_hi; ++t) {
+    for (int t = has_new ? tile_lo - 1 : tile_lo; t < tile_hi; ++t) {
+      const bool new_tile = has_new && t == tile_lo - 1;
       const int j0 = t * kTile;
-      if (!ring.tile_any(j0)) continue;
+      if (!new_tile && !ring.tile_any(j0)) continue;
       // every query row sees the same keys: one ballot per 32 keys gives the whole warp the validity word
       uint32_t valid[4];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) valid[c] = __ballot_sync(0xffffffffu, ring.has(j0 + c * 32 + lane));
+      for (int c = 0; c < 4; ++c)
+        valid[c] = __ballot_sync(0xffffffffu, new_tile ? (c * 32 + lane < p.Lq) : ring.has(j0 + c * 32 + lane));
       mbar_wait(s_full, it & 1);
       tc_fence_after();
       uint32_t r[4][32];
@@ -448,18 +556,19 @@ __global__ void decode_state_advance_kernel(int* state, int commit_rows, int dro
   state[2] = pos;
 }
 
-template <int DH>
+template <int DH, bool FUSED>
 static int launch_attn_decode(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV,
                               const AttnDecodeParams& p, cudaStream_t s) {
   using Cfg = DecCfg<DH>;
   static PerDeviceOnce once;
   const int rc0 = once.run([] {
-    return static_cast<int>(
-        cudaFuncSetAttribute(attn_decode_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    return static_cast<int>(cudaFuncSetAttribute(attn_decode_kernel<DH, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 Cfg::kSmemBytes));
   });
   if (rc0 != OWL_OK) return rc0;
   const long long grid = static_cast<long long>(p.B) * p.H * p.n_splits;
-  (void)launch_k(attn_decode_kernel<DH>, dim3(static_cast<unsigned>(grid)), dim3(kDecThreads), Cfg::kSmemBytes, s, tmQ, tmK, tmV, p);
+  (void)launch_k(attn_decode_kernel<DH, FUSED>, dim3(static_cast<unsigned>(grid)), dim3(kDecThreads), Cfg::kSmemBytes, s, tmQ,
+                 tmK, tmV, p);
   return launch_status();
 }
 
@@ -520,7 +629,49 @@ int owl_attn_decode(const void* q, int64_t q_sb, int64_t q_sh, const void* k_cac
   if ((rc = make_tmap_4d_bf16(&tmK, k_cache, dh, cap, H, B, dh, c_sh, c_sb, 64, kTile)) != OWL_OK) return rc;
   if ((rc = make_tmap_4d_bf16(&tmV, v_cache, dh, cap, H, B, dh, c_sh, c_sb, 64, kTile)) != OWL_OK) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  return dh == 64 ? launch_attn_decode<64>(tmQ, tmK, tmV, p, s) : launch_attn_decode<128>(tmQ, tmK, tmV, p, s);
+  return dh == 64 ? launch_attn_decode<64, false>(tmQ, tmK, tmV, p, s) : launch_attn_decode<128, false>(tmQ, tmK, tmV, p, s);
+}
+
+int owl_attn_decode_fused(const void* qkv, const float* cos_tab, const float* sin_tab, int64_t table_rows, void* k_cache,
+                          void* v_cache, int64_t c_sb, int64_t c_sh, int64_t cap, const int32_t* state, int64_t vis_rows,
+                          void* o, int64_t o_sb, int64_t o_sl, int64_t B, int64_t H, int64_t Lq, int64_t dh, float eps,
+                          void* workspace, int64_t workspace_bytes, owl_stream_t stream) {
+  if (!qkv || !cos_tab || !sin_tab || !k_cache || !v_cache || !state || !o || B <= 0 || H <= 0 || Lq <= 0 || cap < Lq ||
+      vis_rows < 0 || table_rows <= 0)
+    return OWL_ERR_BAD_ARG;
+  if (dh != 64 && dh != 128) return OWL_ERR_UNSUPPORTED;
+  if (Lq > kTile || cap > (1 << 30) || B * H > (1 << 20)) return OWL_ERR_UNSUPPORTED;
+  if (!aligned16(qkv) || !aligned16(o) || !aligned16(k_cache) || !aligned16(v_cache) || !aligned16(cos_tab) ||
+      !aligned16(sin_tab) || o_sb % 8 || o_sl % 8 || c_sb % 8 || c_sh % 8)
+    return OWL_ERR_ALIGN;
+  AttnDecodeParams p{};
+  p.B = static_cast<int>(B); p.H = static_cast<int>(H); p.Lq = static_cast<int>(Lq); p.cap = static_cast<int>(cap);
+  p.tiles_total = static_cast<int>((cap + kTile - 1) / kTile);
+  p.n_splits = decode_splits(B, H, p.tiles_total);
+  p.tiles_per_split = (p.tiles_total + p.n_splits - 1) / p.n_splits;
+  p.n_splits = (p.tiles_total + p.tiles_per_split - 1) / p.tiles_per_split;
+  p.vis_rows = static_cast<int>(vis_rows);
+  p.scale_log2 = 1.4426950408889634f / sqrtf(static_cast<float>(dh));
+  p.o = static_cast<bf16*>(o); p.o_sb = o_sb; p.o_sl = o_sl;
+  p.state = state;
+  p.qkv = static_cast<const bf16*>(qkv); p.cos_tab = cos_tab; p.sin_tab = sin_tab; p.table_rows = table_rows;
+  p.k_cache = static_cast<bf16*>(k_cache); p.v_cache = static_cast<bf16*>(v_cache); p.c_sb = c_sb; p.c_sh = c_sh;
+  p.eps = eps;
+  if (p.n_splits > 1) {
+    if (!workspace || !aligned16(workspace) || workspace_bytes < owl_attn_decode_workspace_bytes(B, H, cap, dh))
+      return OWL_ERR_BAD_ARG;
+    if (B * H * 4 > kDecCounterBytes) return OWL_ERR_UNSUPPORTED;
+    const int64_t n_part = B * H * p.n_splits * kTile;
+    p.counters = static_cast<unsigned*>(workspace);
+    p.part_o = reinterpret_cast<float*>(static_cast<char*>(workspace) + kDecCounterBytes);
+    p.part_ml = p.part_o + n_part * dh;
+  }
+  CUtensorMap tmK, tmV;
+  int rc;
+  if ((rc = make_tmap_4d_bf16(&tmK, k_cache, dh, cap, H, B, dh, c_sh, c_sb, 64, kTile)) != OWL_OK) return rc;
+  if ((rc = make_tmap_4d_bf16(&tmV, v_cache, dh, cap, H, B, dh, c_sh, c_sb, 64, kTile)) != OWL_OK) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  return dh == 64 ? launch_attn_decode<64, true>(tmK, tmK, tmV, p, s) : launch_attn_decode<128, true>(tmK, tmK, tmV, p, s);
 }
 
 int owl_qk_norm_rope_decode(const void* qkv, const float* cos_tab, const float* sin_tab, int64_t table_rows,

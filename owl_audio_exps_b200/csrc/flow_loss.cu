@@ -143,3 +143,66 @@ int owl_mse_bwd(const void* pred, const void* target, const float* dloss, void* 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Shard reduction of the copy-engine gradient exchange (engine.PeerExchange): dst[i] = (dst[i] + sum_j src_j[i]) * scale
+// with src_j = srcs + j * src_stride, fp32, 16-byte vectors.  The peers' shards arrive by copy-engine peer copies; this
+// kernel is the only SM work of a gradient all-reduce (memory-bound, a few CTAs, runs next to the backward GEMMs).
+// ------------------------------------------------------------------------------------------------
+namespace owl {
+
+// 128 threads x <= 32 registers: one such CTA fits NEXT TO a resident 384-thread x 160-register GEMM CTA (4096 registers of the
+// SM's 65536 are left), so the reduction of a bucket shard runs on the SMs the backward GEMMs occupy instead of waiting for
+// a kernel boundary; it is bandwidth-bound and short (a 37 MB shard at N = 2).
+__global__ void __launch_bounds__(128, 16)
+shard_reduce_kernel(float* __restrict__ dst, const float* __restrict__ srcs, long long src_stride, int n_src, long long n4,
+                    long long n, float scale) {
+  pdl_prologue();
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; i + stride < n4; i += 2 * stride) {   // two independent 16-byte streams per thread
+    float4 a = reinterpret_cast<const float4*>(dst)[i];
+    float4 c = reinterpret_cast<const float4*>(dst)[i + stride];
+    for (int j = 0; j < n_src; ++j) {
+      const float4* sp = reinterpret_cast<const float4*>(srcs + j * src_stride);
+      const float4 b = __ldg(sp + i), d = __ldg(sp + i + stride);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+      c.x += d.x; c.y += d.y; c.z += d.z; c.w += d.w;
+    }
+    a.x *= scale; a.y *= scale; a.z *= scale; a.w *= scale;
+    c.x *= scale; c.y *= scale; c.z *= scale; c.w *= scale;
+    reinterpret_cast<float4*>(dst)[i] = a;
+    reinterpret_cast<float4*>(dst)[i + stride] = c;
+  }
+  for (; i < n4; i += stride) {
+    float4 a = reinterpret_cast<const float4*>(dst)[i];
+    for (int j = 0; j < n_src; ++j) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(srcs + j * src_stride) + i);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    a.x *= scale; a.y *= scale; a.z *= scale; a.w *= scale;
+    reinterpret_cast<float4*>(dst)[i] = a;
+  }
+  // tail (n not a multiple of 4)
+  for (long long t = n4 * 4 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += stride) {
+    float a = dst[t];
+    for (int j = 0; j < n_src; ++j) a += srcs[j * src_stride + t];
+    dst[t] = a * scale;
+  }
+}
+
+}  // namespace owl
+
+extern "C" int owl_shard_reduce(float* dst, const float* srcs, int64_t src_stride, int n_src, int64_t n, float scale,
+                                int max_ctas, owl_stream_t stream) {
+  if (!dst || n <= 0 || n_src < 0 || (n_src > 0 && !srcs)) return OWL_ERR_BAD_ARG;
+  if (!owl::aligned16(dst) || (n_src > 0 && (!owl::aligned16(srcs) || src_stride % 4))) return OWL_ERR_ALIGN;
+  long long blocks = (n / 4 + 255) / 256;     // two 16-byte groups per thread
+  const long long cap = max_ctas > 0 ? max_ctas : owl::sm_count();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  (void)owl::launch_k(owl::shard_reduce_kernel, dim3(static_cast<unsigned>(blocks)), dim3(128), 0,
+                      static_cast<cudaStream_t>(stream), dst, srcs, static_cast<long long>(src_stride), n_src,
+                      static_cast<long long>(n / 4), static_cast<long long>(n), scale);
+  return owl::launch_status();
+}

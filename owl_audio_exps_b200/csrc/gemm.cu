@@ -491,7 +491,9 @@ static int slots_for(const GemmParams& p) { return 2 * (1 + p.has_out1) + 2 * p.
 
 static int stages_for(int bn, int n_slots, int ctas = 1) {
   const int stage_bytes = BM * BK * 2 + (bn / ctas) * BK * 2;
-  int st = (kSmemLimit - 1024 - kBarRegion - n_slots * kSlotBytes) / stage_bytes;
+  // coresident_smem_reserve(): shared memory left for a small CTA of ANOTHER kernel on the same SM (the shard reduction of
+  // the copy-engine gradient exchange runs next to the backward GEMMs; every CTA costs 1 KB of reserved shared memory)
+  int st = (kSmemLimit - coresident_smem_reserve() - 1024 - kBarRegion - n_slots * kSlotBytes) / stage_bytes;
   return st > kMaxStages ? kMaxStages : st;
 }
 

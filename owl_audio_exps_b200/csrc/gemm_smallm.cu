@@ -11,10 +11,12 @@
 //     ~1/148th of the weight matrix through a deep TMA ring (up to 8 x 24 KB in flight per SM);
 //   * each chunk is a 128 x BN x (64 * kb) tcgen05 MMA with the fp32 accumulator in TMEM (the token rows are padded
 //     to 128 by TMA zero fill: no traffic for them, and the tensor pipe is idle anyway);
-//   * split-K partials meet in an fp32 workspace tile with red.global.add.v4.f32 (L2 atomics); a per-tile arrival
-//     counter elects the LAST chunk's CTA, which reads the sum back, applies the epilogue (bias, bias+SiLU,
-//     bias+gate*y+residual) and writes bf16.  That CTA also zeroes the tile and the counter again, so the workspace
-//     is zero between launches and no memset node precedes the kernel (one launch per Linear, graph-friendly);
+//   * split-K partials of a tile meet on chip: the <= 8 CTAs that share an n-tile are ONE thread-block cluster, each parks
+//     its fp32 partial in its own shared memory and, after a cluster barrier, sums a slice of the rows over all partials
+//     through distributed shared memory (ld.shared::cluster), applies the epilogue (bias, bias+SiLU, bias+gate*y+residual)
+//     and writes bf16.  More than 8 splits (or OWL_SMALLM_CLUSTER=0) fall back to an fp32 workspace tile with
+//     red.global.add.v4.f32 (L2 atomics) and a per-tile arrival counter that elects the LAST chunk's CTA; that CTA
+//     re-zeroes tile and counter, so no memset node precedes the kernel (one launch per Linear, graph-friendly);
 //   * persistent over chunks (conditioning bank at decode: M = 1 row, N = 6d * n_layers -> 1728 tiles).
 #include <cuda_bf16.h>
 #include <stdlib.h>
@@ -46,10 +48,19 @@ struct SmallMParams {
   long long ldres;
   const bf16* gate;
   long long ldgate;
+  int cluster;          // 1: the splits of a tile form a thread-block cluster and reduce through distributed shared memory
   float* ws;            // [tiles_n][128][BN] fp32, zero between launches
   unsigned* counters;   // [tiles_n], zero between launches
   const char* next_w;   // weights of the NEXT Linear of the schedule (or nullptr): pulled into L2 while this one reduces
   long long next_bytes;
+  // adaLN prologue (modulation.py:20-25 as the A-operand transform): A = rms_norm(x) * (1 + a[frame]) + b[frame]
+  const bf16* ln_x;     // raw residual rows [M, K] (nullptr: A arrives by TMA as is)
+  long long ln_ldx;
+  const bf16* ln_a;
+  const bf16* ln_b;
+  long long ln_ldab;
+  int ln_T;
+  float ln_eps;
 };
 
 // L2 prefetch of [addr, addr + bytes): one bulk request per 16 KB (cp.async.bulk.prefetch.L2; no destination, no barrier)
@@ -124,6 +135,55 @@ __device__ __forceinline__ void finish32(const SmallMParams& p, const float* s_b
   }
 }
 
+// 8 consecutive output columns (one 16-byte bf16 store): the granule of the cluster reduction
+__device__ __forceinline__ void finish8(const SmallMParams& p, const float* s_bias, int row, int col_in_tile, int n0,
+                                        float (&v)[8]) {
+  const int col = n0 + col_in_tile;
+  if (col >= p.N) return;
+  uint4 rv = make_uint4(0, 0, 0, 0), gv = rv;
+  if (p.mode == OWL_EPI_GATE_RESIDUAL) {
+    rv = __ldg(reinterpret_cast<const uint4*>(p.res + static_cast<long long>(row) * p.ldres + col));
+    gv = __ldg(reinterpret_cast<const uint4*>(p.gate + static_cast<long long>(row / p.rows_per_frame) * p.ldgate + col));
+  }
+  if (p.bias != nullptr) {
+    const float4 b0 = *reinterpret_cast<const float4*>(s_bias + col_in_tile);
+    const float4 b1 = *reinterpret_cast<const float4*>(s_bias + col_in_tile + 4);
+    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+  }
+  if (p.mode != OWL_EPI_STORE) {
+#pragma unroll
+    for (int jj = 0; jj < 8; ++jj) v[jj] = round_bf16(v[jj]);
+    if (p.mode == OWL_EPI_BIAS_SILU) {
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) v[jj] = sm_silu(v[jj]);
+    } else {
+      const uint32_t rr[4] = {rv.x, rv.y, rv.z, rv.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) {
+        v[2 * jj] = fmaf(bf16_lo(gg[jj]), v[2 * jj], bf16_lo(rr[jj]));
+        v[2 * jj + 1] = fmaf(bf16_hi(gg[jj]), v[2 * jj + 1], bf16_hi(rr[jj]));
+      }
+    }
+  }
+  *reinterpret_cast<uint4*>(p.out + static_cast<long long>(row) * p.ldo + col) =
+      make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+}
+
+__device__ __forceinline__ float4 ld_dsmem_v4(uint32_t local_saddr, uint32_t rank) {
+  float4 v;
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %4, %5;\n\t"
+      "ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [ra];\n\t"
+      "}\n"
+      : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+      : "r"(local_saddr), "r"(rank)
+      : "memory");
+  return v;
+}
+
 template <int BN>
 __global__ void __launch_bounds__(kSmThreads, 1)
 gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const SmallMParams p) {
@@ -147,7 +207,7 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(&full_bar[s], 1);
+      mbar_init(&full_bar[s], p.ln_x != nullptr ? 129 : 1);   // prologue: + the 128 threads that write the A tile
       mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -172,10 +232,10 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   int pre = 0;
   if (warp == 0 && lane == 0 && static_cast<int>(blockIdx.x) < total) {
     const int t = blockIdx.x;
-    const int tn = t % p.tiles_n, ks = t / p.tiles_n;
+    const int tn = p.cluster ? t / p.splits : t % p.tiles_n, ks = p.cluster ? t % p.splits : t / p.tiles_n;
     const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
     for (int kb = kb0; kb < kb1 && pre < kStages; ++kb, ++pre) {
-      mbar_arrive_expect_tx(&full_bar[pre], kStageBytes);
+      mbar_arrive_expect_tx(&full_bar[pre], p.ln_x != nullptr ? kBBytes : kStageBytes);
       tma_load_2d(smem_b + pre * kBBytes, &tmB, &full_bar[pre], kb * kSmBK, tn * BN);
     }
   }
@@ -187,17 +247,18 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int tn = t % p.tiles_n, ks = t / p.tiles_n;
+        const int tn = p.cluster ? t / p.splits : t % p.tiles_n, ks = p.cluster ? t % p.splits : t / p.tiles_n;
         const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         for (int kb = kb0; kb < kb1; ++kb) {
+          const bool tma_a = p.ln_x == nullptr;   // adaLN prologue: the epilogue warps write the A tile instead
           if (pre > 0) {   // this stage's weights are already on their way: add the activations
             --pre;
-            tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);
+            if (tma_a) tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);
           } else {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+            mbar_arrive_expect_tx(&full_bar[stage], tma_a ? kStageBytes : kBBytes);
             tma_load_2d(smem_b + stage * kBBytes, &tmB, &full_bar[stage], kb * kSmBK, tn * BN);   // weights: HBM
-            tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);       // activations: L2
+            if (tma_a) tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);   // activations: L2
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -209,7 +270,7 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int ks = t / p.tiles_n;
+        const int ks = p.cluster ? t % p.splits : t / p.tiles_n;
         const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         mbar_wait(&tempty_bar[as], aphase ^ 1);
         tc_fence_after();
@@ -250,9 +311,73 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         l2_prefetch_bulk(p.next_w + off, static_cast<unsigned>((left < chunk ? left : chunk) & ~15LL));
       }
     }
+    // ---- adaLN prologue: this thread's row statistic once, then the A tile of every k-block of the chunk -------------
+    float ln_rstd = 0.f;
+    int ln_stage = 0;
+    uint32_t ln_phase = 0;
+    if (p.ln_x != nullptr && row_ok) {
+      // rstd over the WHOLE row (all of K), whatever K-range this CTA multiplies: 16 independent 16-byte loads in flight
+      const bf16* xr = p.ln_x + static_cast<long long>(r) * p.ln_ldx;
+      float ss = 0.f;
+      for (int c0 = 0; c0 < p.K; c0 += 128) {
+        uint4 v[16];
+#pragma unroll
+        for (int g = 0; g < 16; ++g)
+          v[g] = c0 + g * 8 < p.K ? __ldg(reinterpret_cast<const uint4*>(xr + c0 + g * 8)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int g = 0; g < 16; ++g) {
+          const uint32_t w[4] = {v[g].x, v[g].y, v[g].z, v[g].w};
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const float lo = bf16_lo(w[jj]), hi = bf16_hi(w[jj]);
+            ss = fmaf(lo, lo, fmaf(hi, hi, ss));
+          }
+        }
+      }
+      ln_rstd = rsqrtf(ss / static_cast<float>(p.K) + p.ln_eps);
+    }
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
-      const int tn = t % p.tiles_n;
+      const int tn = p.cluster ? t / p.splits : t % p.tiles_n;
       const int n0 = tn * BN;
+      if (p.ln_x != nullptr) {
+        const int ks = p.cluster ? t % p.splits : t / p.tiles_n;
+        const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const long long frow = r / p.ln_T;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[ln_stage], ln_phase ^ 1);
+          if (row_ok) {
+            const int k0 = kb * kSmBK;
+            uint8_t* dstrow = smem_a + ln_stage * kSmABytes + r * 128;
+            uint4 xv[8], av[8], bv[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const bool in = k0 + c * 8 < p.K;
+              xv[c] = in ? __ldg(reinterpret_cast<const uint4*>(p.ln_x + static_cast<long long>(r) * p.ln_ldx + k0 + c * 8))
+                         : make_uint4(0, 0, 0, 0);
+              av[c] = in ? __ldg(reinterpret_cast<const uint4*>(p.ln_a + frow * p.ln_ldab + k0 + c * 8)) : make_uint4(0, 0, 0, 0);
+              bv[c] = in ? __ldg(reinterpret_cast<const uint4*>(p.ln_b + frow * p.ln_ldab + k0 + c * 8)) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const uint32_t xw[4] = {xv[c].x, xv[c].y, xv[c].z, xv[c].w};
+              const uint32_t aw[4] = {av[c].x, av[c].y, av[c].z, av[c].w};
+              const uint32_t bw[4] = {bv[c].x, bv[c].y, bv[c].z, bv[c].w};
+              uint32_t o[4];
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) {
+                // same arithmetic as adaln_fwd_kernel (elementwise.cu): f * rstd * (1 + a) + b, one bf16 rounding
+                const float lo = bf16_lo(xw[jj]) * ln_rstd * (1.f + bf16_lo(aw[jj])) + bf16_lo(bw[jj]);
+                const float hi = bf16_hi(xw[jj]) * ln_rstd * (1.f + bf16_hi(aw[jj])) + bf16_hi(bw[jj]);
+                o[jj] = (k0 + c * 8 < p.K) ? pack_bf16(lo, hi) : 0u;
+              }
+              *reinterpret_cast<uint4*>(dstrow + ((c ^ (r & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+          }
+          fence_proxy_async_smem();      // generic-proxy writes of the A tile -> visible to tcgen05.mma
+          mbar_arrive(&full_bar[ln_stage]);
+          if (++ln_stage == kStages) { ln_stage = 0; ln_phase ^= 1; }
+        }
+      }
       if (p.bias != nullptr) {
         named_bar_sync(1, 128);        // the previous tile's epilogue has read its bias row
         if (et < BN) s_bias[et] = n0 + et < p.N ? __ldg(p.bias + n0 + et) : 0.f;
@@ -267,6 +392,16 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         uint32_t acc[32];
         tmem_ld_x32(taddr + c * 32, acc);
         tmem_ld_wait();
+        if (p.cluster && p.splits > 1) {
+          // partial sums of this K-range -> own shared memory, chunk-major [BN/4][128 rows] x 16 B (conflict-free for
+          // thread = row); the ring is free: every MMA that read it has completed (tfull)
+          float4* P = reinterpret_cast<float4*>(smem_a);
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            P[(c * 8 + g) * 128 + r] = make_float4(__uint_as_float(acc[4 * g]), __uint_as_float(acc[4 * g + 1]),
+                                                   __uint_as_float(acc[4 * g + 2]), __uint_as_float(acc[4 * g + 3]));
+          continue;
+        }
         if (!row_ok) continue;
         if (p.splits == 1) {
           float a[32];
@@ -283,7 +418,7 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       tc_fence_before();
       mbar_arrive(&tempty_bar[as]);    // accumulator buffer back to the MMA warp
       if (++as == 2) { as = 0; aphase ^= 1; }
-      if (p.splits > 1) {
+      if (p.splits > 1 && !p.cluster) {
         __threadfence();               // this thread's partial sums are at L2 before the arrival is counted
         named_bar_sync(1, 128);
         if (elected) {
@@ -324,6 +459,39 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     }
   }
 
+  if (p.cluster && p.splits > 1) {
+    // ---- split-K reduction through DISTRIBUTED SHARED MEMORY: the `splits` CTAs of a tile are one thread-block cluster.
+    // Every CTA has parked its fp32 partial in its own shared memory; after the cluster barrier CTA `rank` sums rows
+    // rank, rank + S, ... over all S partials (ld.shared::cluster), applies the epilogue and stores bf16.  No global
+    // atomics, no fences, no arrival counter, no workspace: ~1 us instead of the ~4 us L2 round-trip chain.
+    __syncwarp();
+    cluster_sync_all();
+    if (warp >= 2) {
+      const int et = static_cast<int>(threadIdx.x) - 64;
+      const int S = p.splits;
+      const int rank = static_cast<int>(cluster_ctarank());
+      const int tn = static_cast<int>(blockIdx.x) / S;
+      const int n0 = tn * BN;
+      const float* s_bias = reinterpret_cast<const float*>(smem + 512);
+      const int rows_r = p.M > rank ? (p.M - rank + S - 1) / S : 0;
+      const int items = rows_r * (BN / 8);
+      const uint32_t p_base = smem_u32(smem_a);
+      for (int i = et; i < items; i += 128) {
+        const int lr = i % rows_r, g = i / rows_r;
+        const int row = rank + lr * S;
+        float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int sct = 0; sct < S; ++sct) {
+          const float4 a0 = ld_dsmem_v4(p_base + static_cast<uint32_t>(((2 * g) * 128 + row) * 16), static_cast<uint32_t>(sct));
+          const float4 a1 = ld_dsmem_v4(p_base + static_cast<uint32_t>(((2 * g + 1) * 128 + row) * 16), static_cast<uint32_t>(sct));
+          v[0] += a0.x; v[1] += a0.y; v[2] += a0.z; v[3] += a0.w;
+          v[4] += a1.x; v[5] += a1.y; v[6] += a1.z; v[7] += a1.w;
+        }
+        finish8(p, s_bias, row, g * 8, n0, v);
+      }
+    }
+    __syncwarp();
+    cluster_sync_all();   // nobody leaves while a peer still reads its partial
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -341,8 +509,10 @@ static int launch_smallm(const CUtensorMap& tmA, const CUtensorMap& tmB, const S
         cudaFuncSetAttribute(gemm_smallm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmSmemLimit));
   });
   if (rc0 != OWL_OK) return rc0;
-  cudaError_t e = launch_k(gemm_smallm_kernel<BN>, dim3(static_cast<unsigned>(grid)), dim3(kSmThreads),
-                           static_cast<size_t>(smem_bytes), s, tmA, tmB, p);
+  LaunchOpts lo;
+  lo.cluster_x = p.cluster ? p.splits : 1;
+  cudaError_t e = launch_kx(lo, gemm_smallm_kernel<BN>, dim3(static_cast<unsigned>(grid)), dim3(kSmThreads),
+                            static_cast<size_t>(smem_bytes), s, tmA, tmB, p);
   if (e != cudaSuccess) {
     (void)cudaGetLastError();
     return static_cast<int>(e);
@@ -370,7 +540,8 @@ static SmallMPlan plan_smallm(long long M, long long N, int kb_total, int sms) {
       const long long ctas = tiles * sp;
       const long long waves = (ctas + sms - 1) / sms;
       const double bytes = static_cast<double>(kbps) * (bn * 128.0 + static_cast<double>(M) * 128.0);
-      const double cost = static_cast<double>(waves) * (1500.0 + bytes / 45.0) + (sp > 1 ? 700.0 : 0.0);  // ns
+      // reduction: ~0.4 us through distributed shared memory (<= 8 splits = one cluster), ~3 us through L2 atomics
+      const double cost = static_cast<double>(waves) * (1500.0 + bytes / 45.0) + (sp > 8 ? 3000.0 : (sp > 1 ? 400.0 : 0.0));
       if (cost < best_cost) { best_cost = cost; best = SmallMPlan{bn, sp}; }
       if (ctas >= 2LL * sms) break;
     }
@@ -391,8 +562,8 @@ int64_t owl_gemm_smallm_workspace_bytes(int64_t N) {
 }
 
 int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
-                    const owl_gemm_epilogue* epi, void* workspace, int64_t workspace_bytes, const void* next_w,
-                    int64_t next_bytes, owl_stream_t stream) {
+                    const owl_gemm_epilogue* epi, const owl_adaln_prologue* ln, void* workspace, int64_t workspace_bytes,
+                    const void* next_w, int64_t next_bytes, owl_stream_t stream) {
   if (!A || !W || !epi || !epi->out0 || M <= 0 || N <= 0 || K <= 0) return OWL_ERR_BAD_ARG;
   if (M > 128) return OWL_ERR_UNSUPPORTED;
   if (N % 8 != 0 || K % 8 != 0) return OWL_ERR_UNSUPPORTED;
@@ -406,6 +577,17 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
   p.bias = epi->bias;
   p.out = static_cast<bf16*>(epi->out0);
   p.ldo = epi->ld0;
+  if (ln != nullptr) {
+    if (!ln->a || !ln->b || ln->rows_per_frame <= 0 || M % ln->rows_per_frame) return OWL_ERR_BAD_ARG;
+    if (ln->ld_ab % 8 || !aligned16(ln->a) || !aligned16(ln->b)) return OWL_ERR_ALIGN;
+    p.ln_x = static_cast<const bf16*>(A);
+    p.ln_ldx = lda;
+    p.ln_a = static_cast<const bf16*>(ln->a);
+    p.ln_b = static_cast<const bf16*>(ln->b);
+    p.ln_ldab = ln->ld_ab;
+    p.ln_T = ln->rows_per_frame;
+    p.ln_eps = ln->eps;
+  }
   if (next_w != nullptr && next_bytes > 0 && aligned16(next_w)) {
     p.next_w = static_cast<const char*>(next_w);
     p.next_bytes = next_bytes;
@@ -439,7 +621,10 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
   p.kb_total = kb_total;
   p.kb_per_split = (kb_total + plan.splits - 1) / plan.splits;
   p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
-  if (p.splits > 1) {
+  // the splits of a tile as one thread-block cluster (<= 8 CTAs, one tile per CTA): reduction through distributed shared memory
+  static const int no_cluster = [] { const char* e = getenv("OWL_SMALLM_CLUSTER"); return e && e[0] == '0' ? 1 : 0; }();
+  p.cluster = (!no_cluster && p.splits > 1 && p.splits <= 8 && static_cast<long long>(p.tiles_n) * p.splits <= 2LL * sms) ? 1 : 0;
+  if (p.splits > 1 && !p.cluster) {
     if (!workspace || !aligned16(workspace)) return OWL_ERR_BAD_ARG;
     const int64_t ws_floats = static_cast<int64_t>(p.tiles_n) * 128 * bn;
     if (workspace_bytes < ws_floats * 4 + static_cast<int64_t>(p.tiles_n) * 4) return OWL_ERR_BAD_ARG;
@@ -459,7 +644,7 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
   if ((rc = make_tmap_2d_bf16(&tmA, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), lda, 64, 128)) != OWL_OK) return rc;
   if ((rc = make_tmap_2d_bf16(&tmB, W, static_cast<uint64_t>(N), static_cast<uint64_t>(K), ldw, 64, bn)) != OWL_OK) return rc;
   const long long total = static_cast<long long>(p.tiles_n) * p.splits;
-  const int grid = static_cast<int>(total < sms ? total : sms);
+  const int grid = p.cluster ? static_cast<int>(total) : static_cast<int>(total < sms ? total : sms);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   return bn == 128 ? launch_smallm<128>(tmA, tmB, p, grid, smem_bytes, s) : launch_smallm<64>(tmA, tmB, p, grid, smem_bytes, s);
 }

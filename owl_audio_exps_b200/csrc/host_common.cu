@@ -126,6 +126,9 @@ int sm_count() {
   return n;
 }
 
+static std::atomic<int> g_smem_reserve{0};
+int coresident_smem_reserve() { return g_smem_reserve.load(std::memory_order_relaxed); }
+
 static std::atomic<int> g_reserved_sms{0};
 int gemm_sm_count() {
   const int n = sm_count() - g_reserved_sms.load(std::memory_order_relaxed);
@@ -161,6 +164,12 @@ const char* owl_error_string(int code) {
 }
 
 uint64_t owl_launch_count(void) { return owl::g_launches.load(); }
+
+int owl_set_coresident_reserve(int bytes) {
+  if (bytes < 0 || bytes > 65536) return OWL_ERR_BAD_ARG;
+  owl::g_smem_reserve.store(bytes);
+  return OWL_OK;
+}
 
 int owl_set_reserved_sms(int n) {
   if (n < 0 || n > 64) return OWL_ERR_BAD_ARG;

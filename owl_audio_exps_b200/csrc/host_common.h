@@ -32,6 +32,7 @@ int make_tmap_4d_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_
                       uint64_t row_stride, uint64_t sh_elems, uint64_t sb_elems, uint32_t box_cols, uint32_t box_rows);
 
 int sm_count();
+int coresident_smem_reserve();  // bytes of shared memory the persistent GEMM leaves free per SM (owl_set_coresident_reserve)
 int gemm_sm_count();  // sm_count() minus the SMs reserved for concurrent communication kernels (even for CTA pairs)
 
 extern std::atomic<uint64_t> g_launches;

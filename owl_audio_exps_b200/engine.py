@@ -84,6 +84,87 @@ def _align(n: int, a: int = 64) -> int:
     return (n + a - 1) // a * a
 
 
+import os
+
+
+class PeerExchange:
+    """Gradient all-reduce whose data movement runs on the COPY ENGINES, not on SMs.
+
+    `ncclAllReduce` next to the backward GEMMs costs twice: its CTAs take SMs (the persistent GEMM grid has to leave
+    16 of 148 free, or a GEMM CTA queues behind a communication CTA) and measured at N=2 (profiles/r02_symm_probe_n2.txt)
+    four 75 MB all-reduces on a side stream stretch six 8192^3 GEMMs from 4.02 to 4.97 ms, while four 75 MB peer copies
+    leave them at 4.02 ms.  So the buckets live in ONE symmetric-memory allocation (torch symmetric memory: every rank can
+    address every peer's buckets over NVLink), and an all-reduce of a bucket slice is
+        barrier                                   every rank's slice is complete
+        pull   my shard of the slice from each peer into local staging      (N-1 copy-engine peer copies)
+        reduce my shard = (mine + staged) / N                               (the only kernel: `owl_shard_reduce`, <= 32 CTAs)
+        barrier                                   every rank's shard is reduced
+        pull   every peer's reduced shard into my slice                     (N-1 copy-engine peer copies)
+    i.e. reduce-scatter + all-gather with NVSwitch carrying each byte once per direction, fp32 end to end (bitwise the
+    same on every rank).  Barriers are torch symmetric memory's device-side signal barriers; everything is enqueued on the
+    communication stream and is captured into the step's CUDA graph like the NCCL calls it replaces."""
+
+    def __init__(self, total_elems: int, device, group, average: bool):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.average = average
+        self.sym = symm_mem.empty(total_elems, dtype=f32, device=device)
+        self.hdl = symm_mem.rendezvous(self.sym, self.group)
+        self.sym.zero_()
+        self.peers = [self.sym if p == self.rank else self.hdl.get_buffer(p, (total_elems,), f32)
+                      for p in range(self.world)]
+        self._staging = {}          # lane -> [world - 1, shard] fp32
+        self.max_ctas = 32
+        # measurement aid: OWL_CE_SKIP=reduce|copy|all leaves out the reduction kernel / the peer copies / both (results are
+        # then wrong; tools/n2_sweep.sh uses it to attribute the exchange's cost)
+        self._skip = os.environ.get("OWL_CE_SKIP", "")
+
+    def _shard(self, n: int) -> int:
+        s = (n + self.world - 1) // self.world
+        return (s + 3) // 4 * 4          # 16-byte shards
+
+    def _stage(self, shard: int, lane: int):
+        st = self._staging.get(lane)
+        if st is None or st.shape[1] < shard:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("PeerExchange staging must exist before graph capture (run one eager step first)")
+            st = self._staging[lane] = torch.empty(self.world - 1, shard, device=self.sym.device, dtype=f32)
+        return st
+
+    def barrier(self, lane: int = 0):
+        self.hdl.barrier(channel=lane)
+
+    def all_reduce(self, flat: torch.Tensor, lane: int = 0):
+        """In place on `flat` (a contiguous fp32 slice of the symmetric allocation), on the CURRENT stream.  `lane`: exchanges
+        in flight at the same time (on different streams) use different lanes = their own staging buffer and barrier channel;
+        every rank must give the same exchange the same lane."""
+        from . import ops
+        n = flat.numel()
+        off = (flat.data_ptr() - self.sym.data_ptr()) // 4
+        if off < 0 or off + n > self.sym.numel():
+            raise RuntimeError("PeerExchange.all_reduce: the tensor is not a slice of the symmetric bucket memory")
+        S = self._shard(n)
+        lo, hi = min(self.rank * S, n), min((self.rank + 1) * S, n)
+        stage = self._stage(S, lane)
+        # pull order rotated by rank: at any moment the ranks read from different peers
+        others = [(self.rank + k) % self.world for k in range(1, self.world)]
+        skip_copy, skip_red = self._skip in ("copy", "all"), self._skip in ("reduce", "all")
+        self.barrier(lane)
+        if hi > lo:
+            if not skip_copy:
+                for j, p in enumerate(others):
+                    stage[j, :hi - lo].copy_(self.peers[p][off + lo:off + hi], non_blocking=True)
+            if not skip_red:
+                ops.shard_reduce(flat[lo:hi], stage, len(others), 1.0 / self.world if self.average else 1.0, self.max_ctas)
+        self.barrier(lane)
+        if not skip_copy:
+            for p in others:
+                plo, phi = min(p * S, n), min((p + 1) * S, n)
+                if phi > plo:
+                    flat[plo:phi].copy_(self.peers[p][off + plo:off + phi], non_blocking=True)
+
+
 class GradBuckets:
     def __init__(self, model: torch.nn.Module, process_group=None, comm_stream: Optional[torch.cuda.Stream] = None,
                  average: bool = True, wgrad_side_stream: bool = True, backwards_per_step: int = 1,
@@ -140,9 +221,25 @@ class GradBuckets:
         self._views: List = []       # (param, its bucket view): what begin_step re-attaches as p.grad
         self._bias_views: List[torch.Tensor] = []
         dev = next(model.parameters()).device
+        sizes = [max(sum(_align(p.numel()) for p in ps), 64) for ps in groups]
+        # all buckets in ONE allocation: symmetric memory (peer-addressable, PeerExchange) when several GPUs take part
+        self.exchange: Optional[PeerExchange] = None
+        base = None
+        if dev.type == "cuda" and self.world > 1 and os.environ.get("OWL_EXCHANGE", "ce").lower() != "nccl":
+            try:
+                self.exchange = PeerExchange(sum(sizes), dev, process_group, average)
+                base = self.exchange.sym
+            except Exception as e:  # noqa: BLE001  (no symmetric memory on this system: NCCL carries the exchange)
+                if dist.get_rank(process_group) == 0:
+                    print(f"owl engine: symmetric-memory exchange unavailable ({type(e).__name__}: {str(e)[:120]}); "
+                          "using ncclAllReduce", flush=True)
+                self.exchange = None
+        if base is None:
+            base = torch.zeros(sum(sizes), device=dev, dtype=f32)
+        goff = 0
         for gi, ps in enumerate(groups):
-            n = sum(_align(p.numel()) for p in ps)
-            flat = torch.zeros(max(n, 1), device=dev, dtype=f32)
+            flat = base[goff:goff + sizes[gi]]
+            goff += sizes[gi]
             off = 0
             for p in ps:
                 if p.dtype != f32:
@@ -158,6 +255,13 @@ class GradBuckets:
             self.flats.append(flat)
         self.is_cuda = dev.type == "cuda"
         self.comm_stream = comm_stream if comm_stream is not None else (torch.cuda.Stream(dev) if self.is_cuda else None)
+        # copy-engine exchange: one exchange is a dependent chain (barrier, pulls, reduce, barrier, pulls: ~0.3 ms for a 75 MB
+        # bucket); several chains in flight on their own streams keep the copy engines and the reduction busy
+        # measured (audio.yml): N=2 10.16 / 10.09 / 10.00 ms with 3 / 2 / 4 lanes; N=8 11.12 / 10.95 ms with 4 / 8 lanes
+        default_lanes = 4 if self.world <= 4 else 8
+        n_lanes = max(1, int(os.environ.get("OWL_CE_LANES", str(default_lanes)))) if self.exchange is not None else 1
+        self.comm_streams = [self.comm_stream] + [torch.cuda.Stream(dev) for _ in range(n_lanes - 1)]
+        self._lane = 0
         for i, blk in enumerate(self.blocks):
             blk._stage.after_backward = (lambda i=i: self._block_done(i))
         self._cond_low: List[int] = []   # per cond bucket: weight rows [low, n_rows) already handed to NCCL this step
@@ -177,6 +281,12 @@ class GradBuckets:
             import os
             from . import _lib
             self.comm_ctas = min(int(os.environ.get("OWL_COMM_CTAS", "16")), 64)  # measured at N=2: 0 -> 11.90, 16 -> 11.54, 24 -> 11.91 ms
+            if self.exchange is not None:
+                self.comm_ctas = 0   # copy engines move the data: backward keeps every SM
+                # ... and the shard reduction (128 threads x 32 registers per CTA) rides next to the GEMM CTAs: they leave
+                # 4 KB of shared memory per SM for it (every resident CTA costs 1 KB of reserved shared memory)
+                _lib.check(_lib.load().owl_set_coresident_reserve(4096), "owl_set_coresident_reserve")
+                self.exchange.max_ctas = 0      # one reduction CTA per SM
         self._reserved = 0
 
     # ---- step protocol -------------------------------------------------------------------------
@@ -184,6 +294,7 @@ class GradBuckets:
         """Call before the first micro-batch's forward."""
         self.accumulate = False
         self.step_id += 1
+        self._lane = 0                        # the same exchange takes the same lane on every rank, every step
         self._seen.clear()
         self._reattach()
         self._reserve_sms(0)                  # no exchange in flight during forward: GEMMs use every SM
@@ -233,12 +344,17 @@ class GradBuckets:
             return
         self._reserve_sms(self.comm_ctas)
         if self.is_cuda:
-            self.comm_stream.wait_stream(torch.cuda.current_stream())
+            lane = self._lane % len(self.comm_streams)
+            self._lane += 1
+            stream = self.comm_streams[lane]
+            stream.wait_stream(torch.cuda.current_stream())
             if self.side_stream is not None:
-                self.comm_stream.wait_stream(self.side_stream)
+                stream.wait_stream(self.side_stream)
             op = dist.ReduceOp.AVG if self.average else dist.ReduceOp.SUM
-            with torch.cuda.stream(self.comm_stream):
-                if self.comm_dtype == torch.bfloat16 and flat.numel() >= 4096 and flat.numel() % 8 == 0:
+            with torch.cuda.stream(stream):
+                if self.exchange is not None:
+                    self.exchange.all_reduce(flat, lane)
+                elif self.comm_dtype == torch.bfloat16 and flat.numel() >= 4096 and flat.numel() % 8 == 0:
                     from . import ops
                     key = (flat.data_ptr(), flat.numel())
                     wire = self._wire.get(key)
@@ -281,6 +397,11 @@ class GradBuckets:
                 self._cond_low[ci] = 0
             self._reduce(self.flats[self.rest_index])
         if self.is_cuda and self.world > 1:
+            for st in self.comm_streams[1:]:
+                self.comm_stream.wait_stream(st)
+            if self.exchange is not None and self.sync_grads:
+                with torch.cuda.stream(self.comm_stream):
+                    self.exchange.barrier()   # no peer still pulls from these buckets when the next step writes them
             torch.cuda.current_stream().wait_stream(self.comm_stream)
             self._reserve_sms(0)
 

@@ -13,9 +13,10 @@ integers (rows cached, ring start, RoPE position).  New rows are always written 
 graph bakes in (pointers, launch dimensions, scalar arguments) depends on the frame index, so ONE graph of the model call
 serves every denoise step and every cache commit of a rollout.
 
-`dit_decode_forward` is the schedule: per layer adaLN -> qkv GEMM -> QK-norm+RoPE into the ring -> split-KV attention ->
-out GEMM with gate+residual epilogue -> adaLN -> fc1 GEMM with bias+SiLU epilogue -> fc2 GEMM with gate+residual
-epilogue; the GEMMs are the weight-streaming split-K kernel (`owl_gemm_smallm`), 8 launches per layer."""
+`dit_decode_forward` is the schedule: per layer qkv GEMM with the adaLN PROLOGUE (rms_norm * (1 + a) + b is the A-operand
+transform) -> split-KV attention with QK-norm + RoPE + ring append in its load path -> out GEMM with gate+residual epilogue
+-> fc1 GEMM with adaLN prologue and bias+SiLU epilogue -> fc2 GEMM with gate+residual epilogue; the GEMMs are the
+weight-streaming split-K kernel (`owl_gemm_smallm`), 5 launches per layer."""
 from __future__ import annotations
 
 import torch
@@ -26,6 +27,14 @@ from .._lib import OWL_EPI_BIAS_SILU, OWL_EPI_GATE_RESIDUAL, OWL_EPI_STORE
 
 bf16 = torch.bfloat16
 MAX_NEW_ROWS = 128
+import os as _os
+
+# Both fusions of the north_star contract exist on this path and are switchable; the defaults are what measured fastest
+# (tools/decode_eval.py, DESIGN.md "Decode schedule"):
+#   FUSED_ATTENTION  QK-norm + RoPE + ring append inside the attention kernel's load path (one launch instead of two)
+#   ADALN_PROLOGUE   adaLN as the A-operand transform of the qkv / fc1 GEMMs (no separate adaLN launch)
+FUSED_ATTENTION = _os.environ.get("OWL_DECODE_FUSE_ATTN", "1") != "0"
+ADALN_PROLOGUE = _os.environ.get("OWL_DECODE_ADALN_PROLOGUE", "0") != "0"
 
 
 class RingKVCache:
@@ -162,17 +171,29 @@ def dit_decode_forward(dit, x, cond, ring: RingKVCache):
         a1, b1, c1 = mod[:, 0:d], mod[:, d:2 * d], mod[:, 2 * d:3 * d]
         a2, b2, c2 = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d], mod[:, 5 * d:6 * d]
         attn = blk.attn
-        h1, _ = ops.adaln_modulate_fwd(x2, a1, b1, T, OF.RMS_EPS, want_rstd=False)
         nxt = per_layer[i + 1]["wqkv"] if i + 1 < n_layers else None
-        ops.gemm_smallm(h1, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d), next_w=W["wout"])
-        ops.qk_norm_rope_decode(qkv, attn.rope.cos, attn.rope.sin, ring.state, q, ring.k[i], ring.v[i], H, OF.RMS_EPS)
+        if ADALN_PROLOGUE:   # adaLN-1 as the A-operand transform of the qkv GEMM (no separate pass over the residual stream)
+            ops.gemm_smallm(x2, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d), next_w=W["wout"],
+                            adaln=(a1, b1, T, OF.RMS_EPS))
+        else:
+            h1, _ = ops.adaln_modulate_fwd(x2, a1, b1, T, OF.RMS_EPS, want_rstd=False)
+            ops.gemm_smallm(h1, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d), next_w=W["wout"])
         vis = attn.local_offset if attn.local else 0
-        ops.attn_decode(q, ring.k[i], ring.v[i], ring.state, vis, out=o)
+        if FUSED_ATTENTION:
+            # QK-norm + RoPE + ring append applied in the attention kernel's own load path (one launch)
+            ops.attn_decode_fused(qkv, attn.rope.cos, attn.rope.sin, ring.k[i], ring.v[i], ring.state, H, OF.RMS_EPS, vis, out=o)
+        else:
+            ops.qk_norm_rope_decode(qkv, attn.rope.cos, attn.rope.sin, ring.state, q, ring.k[i], ring.v[i], H, OF.RMS_EPS)
+            ops.attn_decode(q, ring.k[i], ring.v[i], ring.state, vis, out=o)
         x1 = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm_smallm(o.view(M, d), W["wout"], M, d, d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["bout"], out0=x1, aux0=x2,
                         aux1=c1, rows_per_frame=T, next_w=W["w1"])
-        h2, _ = ops.adaln_modulate_fwd(x1, a2, b2, T, OF.RMS_EPS, want_rstd=False)
-        ops.gemm_smallm(h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"])
+        if ADALN_PROLOGUE:
+            ops.gemm_smallm(x1, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"],
+                            adaln=(a2, b2, T, OF.RMS_EPS))
+        else:
+            h2, _ = ops.adaln_modulate_fwd(x1, a2, b2, T, OF.RMS_EPS, want_rstd=False)
+            ops.gemm_smallm(h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"])
         x2n = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm_smallm(s, W["w2"], M, d, 4 * d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["b2"], out0=x2n, aux0=x1, aux1=c2,
                         rows_per_frame=T, next_w=nxt)

@@ -191,9 +191,10 @@ def _smallm_workspace(dev: torch.device, N: int) -> torch.Tensor:
 def gemm_smallm(a: torch.Tensor, w: torch.Tensor, M: int, N: int, K: int, *, mode: int = OWL_EPI_STORE,
                 bias: Optional[torch.Tensor] = None, out0: Optional[torch.Tensor] = None,
                 aux0: Optional[torch.Tensor] = None, aux1: Optional[torch.Tensor] = None, rows_per_frame: int = 1,
-                next_w: Optional[torch.Tensor] = None) -> None:
+                next_w: Optional[torch.Tensor] = None, adaln=None) -> None:
     """out0[M <= 128, N] = epi(a[M, K] . w[N, K]^T + bias): the decode regime's weight-streaming GEMM (owl_gemm_smallm).
-    `next_w`: the (contiguous) weight matrix the next Linear of the schedule reads, prefetched into L2 meanwhile."""
+    `next_w`: the (contiguous) weight matrix the next Linear of the schedule reads, prefetched into L2 meanwhile.
+    `adaln` = (a, b, T, eps): `a` is the raw residual stream and the GEMM multiplies rms_norm(a)*(1+a_mod[frame])+b_mod[frame]."""
     _req(a), _req(w), _req(out0)
     e = GemmEpilogue()
     e.mode, e.rows_per_frame = mode, rows_per_frame
@@ -207,7 +208,14 @@ def gemm_smallm(a: torch.Tensor, w: torch.Tensor, M: int, N: int, K: int, *, mod
         e.aux1, e.lda1 = aux1.data_ptr(), _ld(aux1)
     ws = _smallm_workspace(a.device, N)
     nw, nb = (next_w.data_ptr(), next_w.numel() * next_w.element_size()) if next_w is not None else (None, 0)
-    rc = _lib.load().owl_gemm_smallm(M, N, K, a.data_ptr(), _ld(a), w.data_ptr(), _ld(w), C.byref(e), ws.data_ptr(),
+    ln = None
+    if adaln is not None:
+        am, bm, T, eps = adaln
+        _req(am), _req(bm)
+        ln = _lib.AdaLNPrologue()
+        ln.a, ln.b, ln.ld_ab, ln.rows_per_frame, ln.eps = am.data_ptr(), bm.data_ptr(), _ld(am), T, eps
+        ln = C.byref(ln)
+    rc = _lib.load().owl_gemm_smallm(M, N, K, a.data_ptr(), _ld(a), w.data_ptr(), _ld(w), C.byref(e), ln, ws.data_ptr(),
                                      ws.numel(), nw, nb, _stream())
     if rc != 0:
         _lib.check(rc, "owl_gemm_smallm")
@@ -591,6 +599,27 @@ def attn_decode(q, k_cache, v_cache, state, vis_rows: int = 0, out=None):
     return o
 
 
+@_prof("attn_decode_fused")
+def attn_decode_fused(qkv, cos, sin, k_cache, v_cache, state, H: int, eps: float, vis_rows: int = 0, out=None):
+    """qkv [B, Lq <= 128, 3*H*dh] straight from the qkv GEMM: QK-norm + RoPE + ring append + split-KV attention in one
+    launch -> o [B, Lq, H*dh] (owl_attn_decode_fused)."""
+    B, Lq, three_d = qkv.shape
+    dh = three_d // (3 * H)
+    _req(qkv), _req(k_cache), _req(v_cache), _req(state, torch.int32)
+    _req(cos, torch.float32), _req(sin, torch.float32)
+    if k_cache.stride() != v_cache.stride() or k_cache.stride(3) != 1 or k_cache.stride(2) != dh or not qkv.is_contiguous():
+        raise RuntimeError("ring cache buffers must be [B, H, cap, dh] with contiguous rows and equal strides; qkv contiguous")
+    o = torch.empty(B, Lq, H * dh, device=qkv.device, dtype=bf16) if out is None else out
+    cap = k_cache.shape[2]
+    ws = _decode_workspace(qkv.device, B, H, cap, dh)
+    rc = _lib.load().owl_attn_decode_fused(qkv.data_ptr(), cos.data_ptr(), sin.data_ptr(), cos.shape[0], k_cache.data_ptr(),
+                                           v_cache.data_ptr(), k_cache.stride(0), k_cache.stride(1), cap, state.data_ptr(),
+                                           vis_rows, o.data_ptr(), o.stride(0), o.stride(1), B, H, Lq, dh, eps, ws.data_ptr(),
+                                           ws.numel(), _stream())
+    _lib.check(rc, "owl_attn_decode_fused")
+    return o
+
+
 def decode_state_advance(state, commit_rows: int, drop_rows: int, cap: int) -> None:
     _lib.check(_lib.load().owl_decode_state_advance(state.data_ptr(), commit_rows, drop_rows, cap, _stream()),
                "owl_decode_state_advance")
@@ -627,3 +656,12 @@ def mse_bwd(pred, target, dloss):
     _lib.check(_lib.load().owl_mse_bwd(pred.data_ptr(), target.data_ptr(), dloss.data_ptr(), dpred.data_ptr(), pred.numel(),
                                        _stream()), "owl_mse_bwd")
     return dpred
+
+
+def shard_reduce(dst, srcs, n_src: int, scale: float, max_ctas: int = 32) -> None:
+    """dst (fp32 [n]) <- (dst + sum of the first n_src rows of srcs (fp32 [>= n_src, stride])) * scale."""
+    _req(dst, torch.float32)
+    stride = srcs.stride(0) if n_src > 0 else 0
+    rc = _lib.load().owl_shard_reduce(dst.data_ptr(), _p(srcs) if n_src > 0 else None, stride, n_src, dst.numel(), float(scale),
+                                      max_ctas, _stream())
+    _lib.check(rc, "owl_shard_reduce")

@@ -91,6 +91,34 @@ def test_qk_norm_rope_decode_vs_training_kernel(dh, H, L, cap, n_valid, start):
     assert bool((kc[:, :, other] == 7.0).all()) and bool((vc[:, :, other] == 7.0).all())
 
 
+@pytest.mark.parametrize("case", [(1, 24, 65, 64, 1105, 975, 0, 0), (1, 24, 65, 64, 1105, 1040, 1100, 260),
+                                  (2, 3, 1, 64, 300, 120, 250, 16), (1, 2, 65, 128, 700, 130, 0, 0),
+                                  (1, 2, 128, 64, 256, 0, 0, 0), (3, 20, 7, 64, 100, 93, 50, 0)],
+                         ids=lambda c: "-".join(map(str, c)))
+def test_attn_decode_fused_equals_two_kernel_path(case):
+    """owl_attn_decode_fused (QK-norm + RoPE + ring append in the attention's load path) against owl_qk_norm_rope_decode
+    followed by owl_attn_decode: the ring contents must be bit for bit the same, the outputs equal to summation order."""
+    ops = _ops()
+    B, H, Lq, dh, cap, n_valid, start, vis = case
+    g = torch.Generator().manual_seed(sum(case) + 1)
+    qkv = torch.randn(B, Lq, 3 * H * dh, generator=g).to(bf16).to(DEV)
+    pos = 11
+    cos = torch.rand(pos + Lq + 3, dh // 2, generator=g).to(DEV)
+    sin = torch.rand(pos + Lq + 3, dh // 2, generator=g).to(DEV)
+    k0 = torch.randn(B, H, cap, dh, generator=g).to(bf16).to(DEV)
+    v0 = torch.randn(B, H, cap, dh, generator=g).to(bf16).to(DEV)
+    state = torch.tensor([n_valid, start, pos, 0], dtype=torch.int32, device=DEV)
+    k1, v1 = k0.clone(), v0.clone()
+    q = torch.empty(B, H, Lq, dh, device=DEV, dtype=bf16)
+    ops.qk_norm_rope_decode(qkv, cos, sin, state, q, k1, v1, H, 1e-6)
+    o_two = ops.attn_decode(q, k1, v1, state, vis)
+    k2, v2 = k0.clone(), v0.clone()
+    o_one = ops.attn_decode_fused(qkv, cos, sin, k2, v2, state, H, 1e-6, vis)
+    torch.cuda.synchronize()
+    assert torch.equal(k2, k1) and torch.equal(v2, v1)
+    assert relerr(o_one, o_two) <= 1e-2
+
+
 def _build(cfg, state, rope, dtype=torch.bfloat16):
     N = _nn()
     model = N.DiT(cfg)

@@ -216,3 +216,23 @@ def test_weight_stage_sees_data_mutations():
         with OF.frozen_weights():
             yd = model(x, cond).clone()
         assert not torch.equal(yd, yc)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on the box")
+def test_copy_engine_exchange_matches_nccl_two_ranks():
+    """engine.PeerExchange (copy-engine peer copies over symmetric memory + owl_shard_reduce) == ncclAllReduce on the same
+    model and per-rank batches, eager and captured in the step's graph, bitwise identical on every rank
+    (tools/exchange_check.py under torchrun, 2 ranks)."""
+    import os
+    import socket
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", str(port),
+                          os.path.join(root, "tools", "exchange_check.py")], capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0 and "OK" in out.stdout, (out.stdout[-1500:], out.stderr[-1500:])

@@ -188,7 +188,9 @@ def test_gemm_smallm(mode, M, N, K):
     if mode == 2:
         kw.update(aux0=res, aux1=gate, rows_per_frame=T)
     outs = []
-    for forced in (None, "1", "3"):            # the planner's choice, no split, an odd split count
+    # the planner's choice, no split, an odd split count (cluster of 3), 8 splits (largest cluster), 12 splits (more than a
+    # cluster holds: fp32 workspace + L2 atomics)
+    for forced in (None, "1", "3", "8", "12"):
         if forced is None:
             os.environ.pop("OWL_SMALLM_SPLITS", None)
         else:
@@ -219,3 +221,41 @@ def test_gemm_smallm_rejects_large_m():
     W = torch.zeros(64, 64, device=dev, dtype=bf16)
     with pytest.raises(RuntimeError):
         ops.gemm_smallm(A, W, 129, 64, 64, out0=torch.empty(129, 64, device=dev, dtype=bf16))
+
+
+@pytest.mark.parametrize("M,N,K,T", [(65, 4608, 1536, 65), (65, 6144, 1536, 65), (1, 3072, 1024, 1), (128, 192, 320, 1),
+                                     (130 // 2, 72, 136, 5), (2, 64, 64, 1)])
+def test_gemm_smallm_adaln_prologue_matches_the_separate_pass(M, N, K, T):
+    """adaLN as the A-operand transform of the decode GEMM (north_star: adaLN scale/shift fused into the GEMM prologue):
+    same arithmetic as owl_adaln_modulate_fwd up to the summation order of the row statistic (per-thread here, warp
+    shuffles there: the normalised operand can differ by one bf16 ulp), so the product matches the two-kernel result to
+    bf16 rounding."""
+    import os
+    ops = _ops()
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device="cpu").manual_seed(M + N + K)
+    x = torch.randn(M, K, generator=g).to(bf16).to(dev)
+    mod = torch.randn(M // T, 3 * K, generator=g).to(bf16).to(dev)      # a, b are column slices with a row stride
+    a, b = mod[:, :K], mod[:, K:2 * K]
+    W = (torch.randn(N, K, generator=g) * K ** -0.5).to(bf16).to(dev)
+    bias = torch.randn(N, generator=g).to(dev)
+    eps = 1.1920928955078125e-07
+    h, _ = ops.adaln_modulate_fwd(x, a, b, T, eps, want_rstd=False)
+    ref_math = torch.nn.functional.rms_norm(x.float(), (K,), eps=eps) * (1 + a.float().repeat_interleave(T, 0)) \
+        + b.float().repeat_interleave(T, 0)
+    assert relerr(h, ref_math) <= 1e-2
+    for forced in (None, "1", "2"):
+        if forced is None:
+            os.environ.pop("OWL_SMALLM_SPLITS", None)
+        else:
+            os.environ["OWL_SMALLM_SPLITS"] = forced
+        try:
+            two = torch.empty(M, N, device=dev, dtype=bf16)
+            ops.gemm_smallm(h, W, M, N, K, mode=1, bias=bias, out0=two)
+            one = torch.full((M, N), float("nan"), device=dev, dtype=bf16)
+            ops.gemm_smallm(x, W, M, N, K, mode=1, bias=bias, out0=one, adaln=(a, b, T, eps))
+            torch.cuda.synchronize()
+            assert relerr(one, two) <= 1e-2, forced
+            assert relerr(one, torch.nn.functional.silu((ref_math.to(bf16).float() @ W.float().t() + bias).to(bf16).float())) <= 2e-2
+        finally:
+            os.environ.pop("OWL_SMALLM_SPLITS", None)
