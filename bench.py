@@ -237,7 +237,8 @@ def loss_fn(model, x, cond, target):
     x = x.detach().requires_grad_(True)
     cond = cond.detach().requires_grad_(True)
     y = model(x, cond)
-    return torch.nn.functional.mse_loss(y.float(), target.float())
+    from owl_audio_exps_b200 import functional as OF
+    return OF.mse_loss(y, target)      # mean((y - target)^2) in fp32 from the bf16 tensors, as models/*.py compute it
 
 
 def run_owl(args):

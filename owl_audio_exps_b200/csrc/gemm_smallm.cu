@@ -11,12 +11,12 @@
 //     ~1/148th of the weight matrix through a deep TMA ring (up to 8 x 24 KB in flight per SM);
 //   * each chunk is a 128 x BN x (64 * kb) tcgen05 MMA with the fp32 accumulator in TMEM (the token rows are padded
 //     to 128 by TMA zero fill: no traffic for them, and the tensor pipe is idle anyway);
-//   * split-K partials of a tile meet on chip: the <= 8 CTAs that share an n-tile are ONE thread-block cluster, each parks
-//     its fp32 partial in its own shared memory and, after a cluster barrier, sums a slice of the rows over all partials
-//     through distributed shared memory (ld.shared::cluster), applies the epilogue (bias, bias+SiLU, bias+gate*y+residual)
-//     and writes bf16.  More than 8 splits (or OWL_SMALLM_CLUSTER=0) fall back to an fp32 workspace tile with
-//     red.global.add.v4.f32 (L2 atomics) and a per-tile arrival counter that elects the LAST chunk's CTA; that CTA
-//     re-zeroes tile and counter, so no memset node precedes the kernel (one launch per Linear, graph-friendly);
+//   * split-K partials meet in an fp32 workspace tile with red.global.add.v4.f32 (L2 atomics); a per-tile arrival
+//     counter elects the LAST chunk's CTA, which reads the sum back, applies the epilogue (bias, bias+SiLU,
+//     bias+gate*y+residual) and writes bf16.  That CTA also zeroes the tile and the counter again, so the workspace
+//     is zero between launches and no memset node precedes the kernel (one launch per Linear, graph-friendly).
+//     OWL_SMALLM_CLUSTER=1 instead makes the <= 8 CTAs of a tile ONE thread-block cluster that reduces through
+//     distributed shared memory (no atomics, no workspace): correct (tests) but measured slower, see owl_gemm_smallm;
 //   * persistent over chunks (conditioning bank at decode: M = 1 row, N = 6d * n_layers -> 1728 tiles).
 #include <cuda_bf16.h>
 #include <stdlib.h>
@@ -540,8 +540,7 @@ static SmallMPlan plan_smallm(long long M, long long N, int kb_total, int sms) {
       const long long ctas = tiles * sp;
       const long long waves = (ctas + sms - 1) / sms;
       const double bytes = static_cast<double>(kbps) * (bn * 128.0 + static_cast<double>(M) * 128.0);
-      // reduction: ~0.4 us through distributed shared memory (<= 8 splits = one cluster), ~3 us through L2 atomics
-      const double cost = static_cast<double>(waves) * (1500.0 + bytes / 45.0) + (sp > 8 ? 3000.0 : (sp > 1 ? 400.0 : 0.0));
+      const double cost = static_cast<double>(waves) * (1500.0 + bytes / 45.0) + (sp > 1 ? 700.0 : 0.0);  // ns
       if (cost < best_cost) { best_cost = cost; best = SmallMPlan{bn, sp}; }
       if (ctas >= 2LL * sms) break;
     }
@@ -622,7 +621,10 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
   p.kb_per_split = (kb_total + plan.splits - 1) / plan.splits;
   p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;
   // the splits of a tile as one thread-block cluster (<= 8 CTAs, one tile per CTA): reduction through distributed shared memory
-  static const int no_cluster = [] { const char* e = getenv("OWL_SMALLM_CLUSTER"); return e && e[0] == '0' ? 1 : 0; }();
+  // (opt-in: OWL_SMALLM_CLUSTER=1.  Measured on B200, tools/smallm_bench.py: qkv 16.3 vs 12.0 us, out 13.4 vs 10.8, fc1 18.3 vs
+  // 13.8, fc2 21.6 vs 14.8 against the L2-atomic path -- a cluster is only scheduled once 2..8 SMs of ONE GPC are free at
+  // the same time, which gives back the overlap with the previous kernel's tail that programmatic dependent launch buys.)
+  static const int no_cluster = [] { const char* e = getenv("OWL_SMALLM_CLUSTER"); return e && e[0] == '1' ? 0 : 1; }();
   p.cluster = (!no_cluster && p.splits > 1 && p.splits <= 8 && static_cast<long long>(p.tiles_n) * p.splits <= 2LL * sms) ? 1 : 0;
   if (p.splits > 1 && !p.cluster) {
     if (!workspace || !aligned16(workspace)) return OWL_ERR_BAD_ARG;

@@ -852,7 +852,11 @@ class DiTBlockFn(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, cond, scond, token, plan: AttnPlan, stage: WeightStage, bank, *P):
+    def forward(ctx, x, cond, scond, token, plan: AttnPlan, stage: WeightStage, bank, light, *P):
+        """`light`: activation checkpointing sized for 180 GB (attn.py:187-188, dit_v4_5B.yml `gradient_checkpointing`): keep
+        only the block input, the modulation vectors, the attention output and its log-sum-exp; the backward re-runs the
+        cheap part of the forward (adaLN, the four GEMMs, QK-norm/RoPE) and NOT the attention kernel, which torch's
+        per-block checkpoint would run a second time."""
         B, L, d = x.shape
         R = cond.shape[0] * cond.shape[1]
         M = B * L
@@ -913,17 +917,26 @@ class DiTBlockFn(torch.autograd.Function):
             x2 = ops.gate_fwd(y2, c2, x1, T)
         ops.stamp("f8 gate2")
 
+        light = bool(light) and plan.kv_cache is None
+        ctx.light = light
         if need_grad:
             q, k_all, v_all, lse, rq, rk, offset, mask = asaved
-            ctx.save_for_backward(x16, cond16, scond16, mod, rstd1, h1, q, k_all, v_all, lse, rq, rk, o2, y1, x1, rstd2,
-                                  h2, z, s, y2, W["wqkv"], W["wout"], W["w1"], W["w2"],
-                                  W["wc"] if bank is None else None, plan.cos, plan.sin, *P)
+            if light:
+                ctx.save_for_backward(x16, cond16, scond16, mod, None, None, None, None, None, lse, None, None, o2, None, None,
+                                      None, None, None, None, None, W["wqkv"], W["wout"], W["w1"], W["w2"],
+                                      W["wc"] if bank is None else None, plan.cos, plan.sin, *P)
+                ctx.n_heads = plan.n_heads
+                ctx.biases = (W["bqkv"], W["bout"], W["b1"], W["b2"])
+            else:
+                ctx.save_for_backward(x16, cond16, scond16, mod, rstd1, h1, q, k_all, v_all, lse, rq, rk, o2, y1, x1, rstd2,
+                                      h2, z, s, y2, W["wqkv"], W["wout"], W["w1"], W["w2"],
+                                      W["wc"] if bank is None else None, plan.cos, plan.sin, *P)
             ctx.meta = (B, L, d, R, T, offset, mask, x.dtype, cond.dtype, cond.shape,
                         None if scond is None else scond.shape)
             ctx.stage = stage
             ctx.bank = bank
             ctx.layer = plan.layer_idx
-            if bank is not None and bank.chain:
+            if bank is not None and bank.chain and not light:
                 bank.tail[plan.layer_idx] = (y2, c2)
         return x2.view(B, L, d) if x.dtype == bf16 else x2.view(B, L, d).to(x.dtype)
 
@@ -938,7 +951,29 @@ class DiTBlockFn(torch.autograd.Function):
         M = B * L
         dev = x16.device
         need = ctx.needs_input_grad
-        np0 = 7  # index of the first parameter among forward's inputs
+        np0 = 8  # index of the first parameter among forward's inputs
+        if ctx.light:
+            # re-run the forward up to what the backward reads, except the attention (its output and lse were kept)
+            bq, bo_, b1_, b2_ = ctx.biases
+            H = ctx.n_heads
+            dh = d // H
+            a1_, b1m, c1_ = mod[:, 0:d], mod[:, d:2 * d], mod[:, 2 * d:3 * d]
+            a2_, b2m = mod[:, 3 * d:4 * d], mod[:, 4 * d:5 * d]
+            h1, rstd1 = ops.adaln_modulate_fwd(x16, a1_, b1m, T, RMS_EPS, want_rstd=True)
+            qkv = torch.empty(B, L, 3 * d, device=dev, dtype=bf16)
+            ops.gemm(OWL_GEMM_NT, h1, wqkv16, M, 3 * d, d, mode=OWL_EPI_STORE, bias=bq, out0=qkv)
+            q = torch.empty(B, H, L, dh, device=dev, dtype=bf16)
+            k_all, v_all = torch.empty_like(q), torch.empty_like(q)
+            rq, rk = ops.qk_norm_rope_fwd(qkv, cos, sin, offset, H, RMS_EPS, q, k_all, v_all, want_rstd=True)
+            del qkv
+            y1 = torch.empty(M, d, device=dev, dtype=bf16)
+            ops.gemm(OWL_GEMM_NT, o2, wout16, M, d, d, mode=OWL_EPI_STORE, bias=bo_, out0=y1)
+            x1, h2, rstd2 = ops.residual_adaln_fwd(x16, y1, c1_, a2_, b2m, T, RMS_EPS, want_rstd=True)
+            z = torch.empty(M, 4 * d, device=dev, dtype=bf16)
+            s = torch.empty(M, 4 * d, device=dev, dtype=bf16)
+            ops.gemm(OWL_GEMM_NT, h2, w116, M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=b1_, out0=z, out1=s)
+            y2 = torch.empty(M, d, device=dev, dtype=bf16)
+            ops.gemm(OWL_GEMM_NT, s, w216, M, d, 4 * d, mode=OWL_EPI_STORE, bias=b2_, out0=y2)
         bank = ctx.bank
         dx2 = _as_bf16(dx2).view(M, d)
         c1, a2, c2, a1 = mod[:, 2 * d:3 * d], mod[:, 3 * d:4 * d], mod[:, 5 * d:6 * d], mod[:, 0:d]
@@ -1041,7 +1076,7 @@ class DiTBlockFn(torch.autograd.Function):
         side_mark()
         if ctx.stage.after_backward is not None:
             ctx.stage.after_backward()
-        return (dx if need[0] else None, dcond, dscond, dtoken, None, None, None,
+        return (dx if need[0] else None, dcond, dscond, dtoken, None, None, None, None,
                 g_wqkv, g_bqkv, g_wout, g_bout, g_w1, g_b1, g_w2, g_b2,
                 g_wa1, g_ba1, g_wg1, g_bg1, g_wa2, g_ba2, g_wg2, g_bg2)
 

@@ -114,12 +114,12 @@ class DiTBlock(nn.Module):
     def cond_params(self):
         return self.block_params()[8:]
 
-    def forward(self, x, cond, block_mask, kv_cache=None, scond=None, bank=None, token=None):
+    def forward(self, x, cond, block_mask, kv_cache=None, scond=None, bank=None, token=None, light=False):
         """attn.py:130-143.  Extensions used by DiT.forward: `scond` = silu(cond) precomputed once per
         stack forward (the reference recomputes it in each of the block's four modulation layers,
         modulation.py:17,38); `bank`/`token` = the stack's batched conditioning projections
         (functional.CondBank) -- the block then reads its modulation vectors instead of projecting them."""
-        return OF.DiTBlockFn.apply(x, cond, scond, token, self.attn.plan(block_mask, kv_cache), self._stage, bank,
+        return OF.DiTBlockFn.apply(x, cond, scond, token, self.attn.plan(block_mask, kv_cache), self._stage, bank, light,
                                    *self.block_params())
 
 
@@ -165,6 +165,11 @@ class DiT(nn.Module):
 
         scond = OF.silu(cond)  # layer-invariant: once per forward instead of 4x per block
         ckpt = self.training and getattr(self.config, "gradient_checkpointing", False)
+        # gradient checkpointing (attn.py:187-188): `light` keeps block input + attention output + lse and re-runs the rest
+        # of the block in backward WITHOUT the attention kernel (functional.DiTBlockFn); `torch` = torch.utils.checkpoint per
+        # block as the reference does (recomputes the attention too)
+        light = ckpt and getattr(self, "checkpoint_impl", "light") == "light" and kv_cache is None
+        ckpt = ckpt and not light
         bank = token = None
         if not ckpt and self.cond_group > 0:
             # all 4 x n_layers conditioning projections as one GEMM (cond is the same for every block)
@@ -172,13 +177,13 @@ class DiT(nn.Module):
                                        self._stage, self.cond_group)
             # the blocks below form a linear chain on a bf16 residual stream: the passes either side of every layer
             # boundary fuse (functional.CondBank.pre / tail / pre_bwd)
-            bank.chain = x.dtype == torch.bfloat16 and getattr(self, "chain_fusion", True)
+            bank.chain = x.dtype == torch.bfloat16 and getattr(self, "chain_fusion", True) and not light
         for layer_idx, block in enumerate(self.blocks):
             block_mask = local_block_mask if self.local_layers[layer_idx] else global_block_mask
             if ckpt:
                 x = checkpoint(block, x, cond, block_mask, kv_cache, scond)
             else:
-                x = block(x, cond, block_mask, kv_cache, scond, bank, token)
+                x = block(x, cond, block_mask, kv_cache, scond, bank, token, light)
         return x
 
 

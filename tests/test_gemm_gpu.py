@@ -188,8 +188,7 @@ def test_gemm_smallm(mode, M, N, K):
     if mode == 2:
         kw.update(aux0=res, aux1=gate, rows_per_frame=T)
     outs = []
-    # the planner's choice, no split, an odd split count (cluster of 3), 8 splits (largest cluster), 12 splits (more than a
-    # cluster holds: fp32 workspace + L2 atomics)
+    # the planner's choice, no split, an odd split count, 8 splits (largest cluster when OWL_SMALLM_CLUSTER=1), 12 splits
     for forced in (None, "1", "3", "8", "12"):
         if forced is None:
             os.environ.pop("OWL_SMALLM_SPLITS", None)
@@ -259,3 +258,41 @@ def test_gemm_smallm_adaln_prologue_matches_the_separate_pass(M, N, K, T):
             assert relerr(one, torch.nn.functional.silu((ref_math.to(bf16).float() @ W.float().t() + bias).to(bf16).float())) <= 2e-2
         finally:
             os.environ.pop("OWL_SMALLM_SPLITS", None)
+
+
+def test_gemm_smallm_cluster_reduction_subprocess():
+    """OWL_SMALLM_CLUSTER=1 (read once per process): the splits of a tile as one thread-block cluster reducing through
+    distributed shared memory, against fp32 math, for clusters of 2, 3 and 8 CTAs and all three epilogues."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r"""
+import os, sys, torch
+sys.path.insert(0, %r)
+from owl_audio_exps_b200 import ops
+bf16, dev = torch.bfloat16, "cuda:0"
+g = torch.Generator().manual_seed(0)
+for M, N, K, T in [(65, 1536, 1536, 65), (1, 3072, 1024, 1), (128, 192, 512, 1)]:
+    A = torch.randn(M, K, generator=g).to(bf16).to(dev)
+    W = (torch.randn(N, K, generator=g) * K ** -0.5).to(bf16).to(dev)
+    bias = torch.randn(N, generator=g).to(dev)
+    res = torch.randn(M, N, generator=g).to(bf16).to(dev)
+    gate = torch.randn(M // T, N, generator=g).to(bf16).to(dev)
+    y = A.float() @ W.float().t() + bias
+    yb = y.to(bf16).float()
+    refs = {0: y, 1: torch.nn.functional.silu(yb), 2: res.float() + gate.float().repeat_interleave(T, 0) * yb}
+    for sp in ("2", "3", "8"):
+        os.environ["OWL_SMALLM_SPLITS"] = sp
+        for mode in (0, 1, 2):
+            out = torch.full((M, N), float("nan"), device=dev, dtype=bf16)
+            kw = dict(aux0=res, aux1=gate, rows_per_frame=T) if mode == 2 else {}
+            ops.gemm_smallm(A, W, M, N, K, mode=mode, bias=bias, out0=out, **kw)
+            torch.cuda.synchronize()
+            err = ((out.float() - refs[mode]).abs().max() / refs[mode].abs().max()).item()
+            assert err <= 1e-2, (M, N, K, sp, mode, err)
+print("ok")
+""" % root
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300,
+                         env=dict(os.environ, OWL_SMALLM_CLUSTER="1"))
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), (out.stdout[-800:], out.stderr[-1500:])
