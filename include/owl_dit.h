@@ -374,6 +374,10 @@ int owl_mse_bwd(const void* pred, const void* target, const float* dloss, void* 
  * shards arrive by copy-engine peer copies; `max_ctas` bounds the grid (the kernel runs next to the backward GEMMs). */
 int owl_shard_reduce(float* dst, const float* srcs, int64_t src_stride, int n_src, int64_t n, float scale, int max_ctas,
                      owl_stream_t stream);
+/* The same with the n_src <= 15 sources given as (host array of) device pointers, e.g. peer-mapped pointers into the other
+ * ranks' buckets: the shard is then summed straight over NVLink, without a staging copy. */
+int owl_shard_reduce_peers(float* dst, const float* const* srcs, int n_src, int64_t n, float scale, int max_ctas,
+                           owl_stream_t stream);
 
 #ifdef __cplusplus
 }

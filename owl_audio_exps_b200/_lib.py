@@ -90,6 +90,7 @@ SIGNATURES = {
     "owl_qk_norm_rope_decode": ([vp, vp, vp, i64, vp, vp, i64, i64, vp, vp, i64, i64, i64, i64, i64, i64, i64, f32, vp],
                                 C.c_int),
     "owl_decode_state_advance": ([vp, i64, i64, i64, vp], C.c_int),
+    "owl_shard_reduce_peers": ([vp, vp, C.c_int, i64, f32, C.c_int, vp], C.c_int),
     "owl_shard_reduce": ([vp, vp, i64, C.c_int, i64, f32, C.c_int, vp], C.c_int),
     "owl_rf_noise": ([vp, vp, vp, vp, vp, i64, i64, vp], C.c_int),
     "owl_mse_fwd": ([vp, vp, vp, i64, vp], C.c_int),

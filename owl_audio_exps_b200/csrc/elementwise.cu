@@ -135,7 +135,9 @@ static inline int grid_for(int64_t work_items, int threads) {
 // ------------------------------------------------------------------------------------------------
 // adaLN modulate forward: h = rms_norm(x) * (1 + a[frame]) + b[frame]      (a, b may be NULL)
 // ------------------------------------------------------------------------------------------------
-template <int NV>
+// RES: the residual variant (x <- x + gate * y first).  A template parameter, not a null test: the plain variant must not
+// carry the y / gate register arrays (ncu r02: 12 % warps active with them, registers bound the occupancy).
+template <int NV, bool RES>
 __global__ void __launch_bounds__(kRowThreads)
 adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const bf16* __restrict__ b, int64_t ld_ab,
                  bf16* __restrict__ h, float* __restrict__ rstd_out, int64_t M, int d, int T, float eps,
@@ -148,15 +150,15 @@ adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const b
     const int64_t frow = row / T;
     // every load of the row is issued before the first use: NV (x) to 5 NV (x, y, gate, a, b) independent 16-byte
     // requests per lane in flight (one row per warp at a time otherwise leaves HBM idle: ncu r02, 34 % warps active)
-    uint4 xv[NV], yv[NV], gtv[NV], av[NV], bv[NV];
+    uint4 xv[NV], yv[RES ? NV : 1], gtv[RES ? NV : 1], av[NV], bv[NV];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * 8;
       if (c < d) {
         xv[i] = ldg16(xr + c);
-        if (y != nullptr) {
-          yv[i] = ldg16(y + row * d + c);
-          gtv[i] = ldg16(gate + frow * ld_g + c);
+        if (RES) {
+          yv[RES ? i : 0] = ldg16(y + row * d + c);
+          gtv[RES ? i : 0] = ldg16(gate + frow * ld_g + c);
         }
         if (a != nullptr) {
           av[i] = ldg16(a + frow * ld_ab + c);
@@ -171,10 +173,10 @@ adaln_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ a, const b
       if (c < d) {
         float f[8];
         unpack8(xv[i], f);
-        if (y != nullptr) {  // x <- x + gate[frame] * y, the residual of the previous branch (attn.py:135,141)
+        if (RES) {  // x <- x + gate[frame] * y, the residual of the previous branch (attn.py:135,141)
           float fy[8], fg[8];
-          unpack8(yv[i], fy);
-          unpack8(gtv[i], fg);
+          unpack8(yv[RES ? i : 0], fy);
+          unpack8(gtv[RES ? i : 0], fg);
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = fmaf(fg[j], fy[j], f[j]);
           xv[i] = pack8(f);  // the residual stream is bf16: normalise exactly what is stored
@@ -875,7 +877,7 @@ int owl_adaln_modulate_fwd(const void* x, const void* a, const void* b, int64_t 
   OWL_REQUIRE(aligned16(x) && aligned16(h) && aligned16(a) && aligned16(b) && (a == nullptr || ld_ab % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
+  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_fwd_kernel<NV, false>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
                          static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps, nullptr, nullptr,
                          0, nullptr)));
   return launch_status();
@@ -891,7 +893,7 @@ int owl_residual_adaln_fwd(const void* x, const void* y, const void* gate, int64
                   aligned16(b) && ld_g % 8 == 0 && (a == nullptr || ld_ab % 8 == 0),
               OWL_ERR_ALIGN);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_fwd_kernel<NV>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
+  OWL_DISPATCH_NV(d, ((void)launch_k(adaln_fwd_kernel<NV, true>, dim3(row_grid(M)), dim3(kRowThreads), 0, s, static_cast<const bf16*>(x), static_cast<const bf16*>(a), static_cast<const bf16*>(b), ld_ab,
                          static_cast<bf16*>(h), rstd, M, static_cast<int>(d), static_cast<int>(T), eps,
                          static_cast<const bf16*>(y), static_cast<const bf16*>(gate), ld_g, static_cast<bf16*>(xsum))));
   return launch_status();

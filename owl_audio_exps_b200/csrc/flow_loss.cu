@@ -206,3 +206,54 @@ extern "C" int owl_shard_reduce(float* dst, const float* srcs, int64_t src_strid
                       static_cast<long long>(n / 4), static_cast<long long>(n), scale);
   return owl::launch_status();
 }
+
+// Same reduction with the sources read IN PLACE from the peers' buckets over NVLink (peer-mapped pointers of the symmetric
+// allocation) instead of from a local staging copy: no copy-engine pulls and no staging traffic for the reduce-scatter half
+// of the exchange; 2 x 16 bytes x (n_src) loads in flight per thread cover the NVLink latency.
+namespace owl {
+
+struct ShardSrcs {
+  const float* p[15];
+};
+
+__global__ void __launch_bounds__(128, 16)
+shard_reduce_peers_kernel(float* __restrict__ dst, const ShardSrcs srcs, int n_src, long long n4, long long n, float scale) {
+  pdl_prologue();
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 a = reinterpret_cast<const float4*>(dst)[i];
+#pragma unroll 5
+    for (int j = 0; j < n_src; ++j) {
+      const float4 b = __ldcg(reinterpret_cast<const float4*>(srcs.p[j]) + i);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    a.x *= scale; a.y *= scale; a.z *= scale; a.w *= scale;
+    reinterpret_cast<float4*>(dst)[i] = a;
+  }
+  for (long long t = n4 * 4 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += stride) {
+    float a = dst[t];
+    for (int j = 0; j < n_src; ++j) a += __ldcg(srcs.p[j] + t);
+    dst[t] = a * scale;
+  }
+}
+
+}  // namespace owl
+
+extern "C" int owl_shard_reduce_peers(float* dst, const float* const* srcs, int n_src, int64_t n, float scale, int max_ctas,
+                                      owl_stream_t stream) {
+  if (!dst || n <= 0 || n_src < 0 || n_src > 15 || (n_src > 0 && !srcs)) return OWL_ERR_BAD_ARG;
+  if (!owl::aligned16(dst)) return OWL_ERR_ALIGN;
+  owl::ShardSrcs s{};
+  for (int j = 0; j < n_src; ++j) {
+    if (!srcs[j] || !owl::aligned16(srcs[j])) return OWL_ERR_ALIGN;
+    s.p[j] = srcs[j];
+  }
+  long long blocks = (n / 4 + 127) / 128;
+  const long long cap = max_ctas > 0 ? max_ctas : owl::sm_count();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  (void)owl::launch_k(owl::shard_reduce_peers_kernel, dim3(static_cast<unsigned>(blocks)), dim3(128), 0,
+                      static_cast<cudaStream_t>(stream), dst, s, n_src, static_cast<long long>(n / 4),
+                      static_cast<long long>(n), scale);
+  return owl::launch_status();
+}

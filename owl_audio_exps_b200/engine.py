@@ -119,6 +119,10 @@ class PeerExchange:
         # measurement aid: OWL_CE_SKIP=reduce|copy|all leaves out the reduction kernel / the peer copies / both (results are
         # then wrong; tools/n2_sweep.sh uses it to attribute the exchange's cost)
         self._skip = os.environ.get("OWL_CE_SKIP", "")
+        # OWL_CE_DIRECT=1: reduce-scatter half without staging copies - the reduction kernel sums the peers' shards in place
+        # over NVLink.  Correct (tools/exchange_check.py) but measured slower at N=2 (10.59 vs 10.13 ms/step): the 128-thread
+        # co-resident CTAs cannot keep enough remote loads in flight, and the longer kernel sits next to the GEMMs longer.
+        self.direct = os.environ.get("OWL_CE_DIRECT", "0") == "1" and self.world <= 16
 
     def _shard(self, n: int) -> int:
         s = (n + self.world - 1) // self.world
@@ -146,12 +150,16 @@ class PeerExchange:
             raise RuntimeError("PeerExchange.all_reduce: the tensor is not a slice of the symmetric bucket memory")
         S = self._shard(n)
         lo, hi = min(self.rank * S, n), min((self.rank + 1) * S, n)
-        stage = self._stage(S, lane)
+        stage = None if self.direct else self._stage(S, lane)
         # pull order rotated by rank: at any moment the ranks read from different peers
         others = [(self.rank + k) % self.world for k in range(1, self.world)]
         skip_copy, skip_red = self._skip in ("copy", "all"), self._skip in ("reduce", "all")
         self.barrier(lane)
-        if hi > lo:
+        if hi > lo and self.direct:
+            if not skip_red:
+                ops.shard_reduce_peers(flat[lo:hi], [self.peers[p][off + lo:off + hi] for p in others],
+                                       1.0 / self.world if self.average else 1.0, self.max_ctas)
+        elif hi > lo:
             if not skip_copy:
                 for j, p in enumerate(others):
                     stage[j, :hi - lo].copy_(self.peers[p][off + lo:off + hi], non_blocking=True)

@@ -665,3 +665,12 @@ def shard_reduce(dst, srcs, n_src: int, scale: float, max_ctas: int = 32) -> Non
     rc = _lib.load().owl_shard_reduce(dst.data_ptr(), _p(srcs) if n_src > 0 else None, stride, n_src, dst.numel(), float(scale),
                                       max_ctas, _stream())
     _lib.check(rc, "owl_shard_reduce")
+
+
+def shard_reduce_peers(dst, srcs, scale: float, max_ctas: int = 0) -> None:
+    """dst (fp32 [n]) <- (dst + sum of the tensors in `srcs` (fp32 [n] each, e.g. peer-mapped bucket slices)) * scale."""
+    _req(dst, torch.float32)
+    n = len(srcs)
+    arr = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in srcs])
+    rc = _lib.load().owl_shard_reduce_peers(dst.data_ptr(), arr, n, dst.numel(), float(scale), max_ctas, _stream())
+    _lib.check(rc, "owl_shard_reduce_peers")
