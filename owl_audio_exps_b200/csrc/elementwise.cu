@@ -10,7 +10,7 @@
 
 namespace owl {
 
-static constexpr int kRowThreads = 256;  // 8 warps = 8 rows per CTA pass
+static constexpr int kRowThreads = 128;  // 4 warps = 4 rows per CTA pass (register-heavy row kernels: more CTAs fit an SM)
 
 __device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ void stg16(void* p, const uint4& v) { *reinterpret_cast<uint4*>(p) = v; }
@@ -824,7 +824,7 @@ layer_norm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, b
 
 static inline int row_grid(int64_t M) {
   int64_t blocks = (M + (kRowThreads / 32) - 1) / (kRowThreads / 32);
-  const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+  const int64_t cap = static_cast<int64_t>(sm_count()) * 16;
   if (blocks > cap) blocks = cap;
   return static_cast<int>(blocks < 1 ? 1 : blocks);
 }

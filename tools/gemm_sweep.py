@@ -30,6 +30,12 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
 else:
     for env in [{}, {"OWL_GEMM_BN": "256"}, {"OWL_GEMM_BN": "128"}, {"OWL_GEMM_BN": "64"}, {"OWL_GEMM_BN": "256", "OWL_GEMM_STAGES": "3"},
                 {"OWL_GEMM_BN": "128", "OWL_GEMM_STAGES": "3"}, {"OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "4"},
-                {"OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "2"}, {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "2"}]:
+                {"OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "2"}, {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "2"},
+                {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "1"},
+                {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "2"},
+                {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "3"},
+                {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "4"},
+                {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "6"},
+                {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "3"}, {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "4"}]:
         r = subprocess.run([sys.executable, __file__, "child"], env={**os.environ, **env}, capture_output=True, text=True)
         print(env, "\n   ", r.stdout.strip() or r.stderr[-300:])
