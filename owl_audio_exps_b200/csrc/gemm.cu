@@ -500,6 +500,11 @@ static int stages_for(int bn, int n_slots, int ctas = 1) {
 static GemmPlan plan_gemm(long long M, long long N, int kb_total, bool can_split, int n_slots, int sms, int force_ctas) {
   GemmPlan best{64, 1, 2, n_slots, 1};
   double best_cost = 1e300;
+  // OWL_GEMM_MODEL (A/B aid): bit 1 = charge the split-K reduce-add traffic (default), bit 0 = prefer single CTAs for
+  // one-wave problems. Bit 0 wins every isolated timing (tools/gemm_sweep.py: 0.5-1.2 us per GEMM) and LOSES 0.3 ms on
+  // the audio step (9.36 -> 9.68 ms, same box): back-to-back launches of an under-filled grid overlap through PDL in
+  // the microbenchmark, dependent kernels of the real step do not. Off.
+  static const int model = getenv("OWL_GEMM_MODEL") ? atoi(getenv("OWL_GEMM_MODEL")) : 2;
   // {tile width, CTAs per tile, relative time per k-block of one tile (measured on B200, tools/gemm_one.py and
   // tools/gemm_sweep.py)}: a CTA pair finishes its 256x256 tile in ~0.95x the time one CTA needs for 128x256 (each SM
   // pulls only half of B through L2 and shared memory: -5..9 % on the conditioning-bank GEMMs, equal on the K = 1024
@@ -521,8 +526,18 @@ static GemmPlan plan_gemm(long long M, long long N, int kb_total, bool can_split
       const int kbps = (kb_total + sp - 1) / sp;
       const int real_sp = (kb_total + kbps - 1) / kbps;
       const long long waves = (tiles * real_sp + workers - 1) / workers;
-      const double fixed = 400.0 + (real_sp > 1 ? 150.0 : 0.0);  // reduce-add traffic of a split tile
-      const double cost = static_cast<double>(waves) * (kbps * bn * eff[i] + fixed);
+      const bool lone = (model & 1) && ctas == 2 && waves == 1;
+      const double e = lone ? 1.0 : eff[i];
+      const double fixed = 400.0 + (lone ? 200.0 : 0.0) + (!(model & 2) && real_sp > 1 ? 150.0 : 0.0);
+      // Split-K reduce-add: every split pushes its fp32 tile through the L2 atomics (~2.5 TB/s measured; one cost unit
+      // is ~1.64 ns, so 4100 bytes per unit); the last wave's share is exposed, earlier waves hide theirs under the
+      // next tile's main loop.
+      double red = 0.0;
+      if ((model & 2) && real_sp > 1) {
+        const double bytes = static_cast<double>(tiles) * real_sp * (BM * ctas) * bn * 4.0;
+        red = bytes / 4100.0 * (waves > 2 ? 2.0 / static_cast<double>(waves) : 1.0);
+      }
+      const double cost = static_cast<double>(waves) * (kbps * bn * e + fixed) + red;
       if (cost < best_cost) { best_cost = cost; best = GemmPlan{bn, real_sp, stages, n_slots, ctas}; }
       if (tiles * sp >= 2LL * workers) break;
     }

@@ -10,7 +10,8 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
     out = []
     for tag, layout, M, N, K in [("qkvNT", 0, 3840, 3072, 1024), ("fc1NT", 0, 3840, 4096, 1024), ("outNT", 0, 3840, 1024, 1024),
                                  ("fc2NT", 0, 3840, 1024, 4096), ("qkvNN", 1, 3840, 1024, 3072), ("outNN", 1, 3840, 1024, 1024),
-                                 ("woutTN", 2, 1024, 1024, 3840), ("wqkvTN", 2, 3072, 1024, 3840), ("wcTN", 2, 6144, 1024, 3840)]:
+                                 ("woutTN", 2, 1024, 1024, 3840), ("wqkvTN", 2, 3072, 1024, 3840), ("wcTN", 2, 6144, 1024, 3840),
+                                 ("wfc1TN", 2, 4096, 1024, 3840), ("wfc2TN", 2, 1024, 4096, 3840), ("dfc2NN", 1, 3840, 4096, 1024)]:
         if layout == 0:
             a, b = g(M, K), g(N, K)
         elif layout == 1:
@@ -28,7 +29,8 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
         out.append(f"{tag}:{us:.1f}us/{2.0*M*N*K/us/1e6:.0f}TF")
     print(" ".join(out))
 else:
-    for env in [{}, {"OWL_GEMM_BN": "256"}, {"OWL_GEMM_BN": "128"}, {"OWL_GEMM_BN": "64"}, {"OWL_GEMM_BN": "256", "OWL_GEMM_STAGES": "3"},
+    quick = [{}, {"OWL_GEMM_CTAS": "1"}, {"OWL_GEMM_CTAS": "2"}, {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "1"}]
+    full = [{}, {"OWL_GEMM_BN": "256"}, {"OWL_GEMM_BN": "128"}, {"OWL_GEMM_BN": "64"}, {"OWL_GEMM_BN": "256", "OWL_GEMM_STAGES": "3"},
                 {"OWL_GEMM_BN": "128", "OWL_GEMM_STAGES": "3"}, {"OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "4"},
                 {"OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "2"}, {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "2"},
                 {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "1"},
@@ -36,6 +38,7 @@ else:
                 {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "3"},
                 {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "4"},
                 {"OWL_GEMM_CTAS": "2", "OWL_GEMM_BN": "256", "OWL_GEMM_SPLITS": "6"},
-                {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "3"}, {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "4"}]:
+                {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "3"}, {"OWL_GEMM_BN": "128", "OWL_GEMM_SPLITS": "4"}]
+    for env in (quick if "--quick" in sys.argv else full):
         r = subprocess.run([sys.executable, __file__, "child"], env={**os.environ, **env}, capture_output=True, text=True)
         print(env, "\n   ", r.stdout.strip() or r.stderr[-300:])
