@@ -362,7 +362,9 @@ def run_owl(args):
             "config": {"workload": w["name"], "per_gpu_batch": B, "tokens_per_sample": L, "d_model": d,
                        "n_layers": cfg.n_layers, "n_heads": cfg.n_heads, "params": n_params, "parallelism": f"dp{world}",
                        "step": "DiT stack fwd + bwd + grad all-reduce (bucket per block, overlapped; "
-                               + ("copy-engine peer copies over symmetric memory + shard-reduce kernel, fp32"
+                               + (("in-switch reduction over the symmetric buckets (multimem.ld_reduce / multimem.st kernel), fp32"
+                                   if getattr(buckets.exchange, "mode", "ce") == "mc" else
+                                   "copy-engine peer copies over symmetric memory + shard-reduce kernel, fp32")
                                   if getattr(buckets, "exchange", None) is not None else
                                   "ncclAllReduce, wire dtype " + ("bf16" if buckets.comm_dtype == torch.bfloat16 else "fp32"))
                                + "); optimizer excluded",

@@ -379,6 +379,12 @@ int owl_shard_reduce(float* dst, const float* srcs, int64_t src_stride, int n_sr
 int owl_shard_reduce_peers(float* dst, const float* const* srcs, int n_src, int64_t n, float scale, int max_ctas,
                            owl_stream_t stream);
 
+/* In-switch variant (NVLink SHARP): `mc_shard` is the MULTICAST address of this rank's shard of a bucket that every rank
+ * allocated symmetrically (torch symmetric memory's multicast_ptr + offset).  Every 16 bytes are fetched from all ranks and
+ * summed inside NVSwitch (multimem.ld_reduce), scaled, and written back to all ranks (multimem.st): all-reduce of the shard
+ * with no staging and no copies.  The caller brackets the call with device-side barriers across the ranks. */
+int owl_mc_allreduce(float* mc_shard, int64_t n, float scale, int max_ctas, owl_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

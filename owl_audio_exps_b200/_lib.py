@@ -91,6 +91,7 @@ SIGNATURES = {
                                 C.c_int),
     "owl_decode_state_advance": ([vp, i64, i64, i64, vp], C.c_int),
     "owl_shard_reduce_peers": ([vp, vp, C.c_int, i64, f32, C.c_int, vp], C.c_int),
+    "owl_mc_allreduce": ([vp, i64, f32, C.c_int, vp], C.c_int),
     "owl_shard_reduce": ([vp, vp, i64, C.c_int, i64, f32, C.c_int, vp], C.c_int),
     "owl_rf_noise": ([vp, vp, vp, vp, vp, i64, i64, vp], C.c_int),
     "owl_mse_fwd": ([vp, vp, vp, i64, vp], C.c_int),

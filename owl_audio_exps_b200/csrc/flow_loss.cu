@@ -257,3 +257,61 @@ extern "C" int owl_shard_reduce_peers(float* dst, const float* const* srcs, int 
                       static_cast<long long>(n), scale);
   return owl::launch_status();
 }
+
+// ------------------------------------------------------------------------------------------------
+// In-switch all-reduce of a bucket shard (NVLink SHARP / multimem): `mc` is the MULTICAST address of this rank's shard inside
+// the symmetric bucket allocation.  multimem.ld_reduce makes NVSwitch fetch the 16 bytes from every rank and add them on
+// the way (one fp32 sum arrives), multimem.st writes the scaled sum back to every rank's copy.  Per rank and exchange the
+// links carry the bucket once per direction (reduce-scatter + all-gather by copies: 2 (N-1)/N times), nothing is staged
+// in HBM and no copy is enqueued.  Same co-residency recipe as shard_reduce_kernel (128 threads, <= 32 registers); four
+// independent 16-byte requests per thread cover the ~3.5 us round trip through the switch.
+// ------------------------------------------------------------------------------------------------
+namespace owl {
+
+__device__ __forceinline__ float4 mc_ld_reduce(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st(float* p, float4 v, float s) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               :: "l"(p), "f"(v.x * s), "f"(v.y * s), "f"(v.z * s), "f"(v.w * s) : "memory");
+}
+
+__global__ void __launch_bounds__(128, 16) mc_allreduce_kernel(float* __restrict__ mc, long long n4, long long n, float scale) {
+  pdl_prologue();
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n4; i += 4 * stride) {
+    const float4 a = mc_ld_reduce(mc + 4 * i);
+    const float4 b = mc_ld_reduce(mc + 4 * (i + stride));
+    const float4 c = mc_ld_reduce(mc + 4 * (i + 2 * stride));
+    const float4 d = mc_ld_reduce(mc + 4 * (i + 3 * stride));
+    mc_st(mc + 4 * i, a, scale);
+    mc_st(mc + 4 * (i + stride), b, scale);
+    mc_st(mc + 4 * (i + 2 * stride), c, scale);
+    mc_st(mc + 4 * (i + 3 * stride), d, scale);
+  }
+  for (; i < n4; i += stride) mc_st(mc + 4 * i, mc_ld_reduce(mc + 4 * i), scale);
+  for (long long t = n4 * 4 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; t < n; t += stride) {
+    float v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc + t) : "memory");
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" :: "l"(mc + t), "f"(v * scale) : "memory");
+  }
+}
+
+}  // namespace owl
+
+extern "C" int owl_mc_allreduce(float* mc_shard, int64_t n, float scale, int max_ctas, owl_stream_t stream) {
+  if (!mc_shard || n <= 0) return OWL_ERR_BAD_ARG;
+  if (!owl::aligned16(mc_shard)) return OWL_ERR_ALIGN;
+  long long blocks = (n / 4 + 511) / 512;     // four 16-byte requests per thread
+  const long long cap = max_ctas > 0 ? max_ctas : owl::sm_count();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  (void)owl::launch_k(owl::mc_allreduce_kernel, dim3(static_cast<unsigned>(blocks)), dim3(128), 0,
+                      static_cast<cudaStream_t>(stream), mc_shard, static_cast<long long>(n / 4), static_cast<long long>(n),
+                      scale);
+  return owl::launch_status();
+}

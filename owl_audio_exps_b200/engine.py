@@ -123,6 +123,24 @@ class PeerExchange:
         # over NVLink.  Correct (tools/exchange_check.py) but measured slower at N=2 (10.59 vs 10.13 ms/step): the 128-thread
         # co-resident CTAs cannot keep enough remote loads in flight, and the longer kernel sits next to the GEMMs longer.
         self.direct = os.environ.get("OWL_CE_DIRECT", "0") == "1" and self.world <= 16
+        # In-switch reduction (NVLink SHARP), OWL_EXCHANGE=mc: when the symmetric allocation has a multicast mapping, a
+        # bucket's all-reduce is
+        #   barrier -> owl_mc_allreduce on my shard (multimem.ld_reduce: NVSwitch sums the ranks' copies; multimem.st: the
+        #   result lands in every rank's copy) -> barrier
+        # with no staging traffic and no copies.  Correct (tools/exchange_check.py: 4.9e-8 of ncclAllReduce, bitwise the same
+        # on every rank, eager and in the graph) but NOT the default: measured at N=2 on audio.yml 10.45 ms (2 lanes, 64 CTAs)
+        # and 10.88 ms (4 lanes, 148 CTAs) against 9.90 ms for the copy-engine exchange, and the 4-lane runs with 32 / 64
+        # CTAs did not finish inside 300 s (profiles/r02_mc_sweep_n2.txt) - the multimem CTAs sit next to the GEMM CTAs for
+        # the whole ~3.5 us switch round trip of every request, where a copy engine costs the SMs nothing.
+        mode = os.environ.get("OWL_EXCHANGE", "ce").lower()
+        try:
+            self.mc_ptr = int(self.hdl.multicast_ptr) if mode == "mc" else 0
+        except Exception:  # noqa: BLE001
+            self.mc_ptr = 0
+        if mode == "mc" and not self.mc_ptr:
+            raise RuntimeError("OWL_EXCHANGE=mc: the symmetric allocation has no multicast mapping on this system")
+        self.mode = "mc" if self.mc_ptr else "ce"
+        self.mc_ctas = int(os.environ.get("OWL_MC_CTAS", "64"))
 
     def _shard(self, n: int) -> int:
         s = (n + self.world - 1) // self.world
@@ -150,11 +168,17 @@ class PeerExchange:
             raise RuntimeError("PeerExchange.all_reduce: the tensor is not a slice of the symmetric bucket memory")
         S = self._shard(n)
         lo, hi = min(self.rank * S, n), min((self.rank + 1) * S, n)
-        stage = None if self.direct else self._stage(S, lane)
+        stage = None if (self.direct or self.mc_ptr) else self._stage(S, lane)
         # pull order rotated by rank: at any moment the ranks read from different peers
         others = [(self.rank + k) % self.world for k in range(1, self.world)]
         skip_copy, skip_red = self._skip in ("copy", "all"), self._skip in ("reduce", "all")
         self.barrier(lane)
+        if self.mc_ptr:
+            if hi > lo and not skip_red:
+                ops.mc_allreduce(self.mc_ptr + 4 * (off + lo), hi - lo, 1.0 / self.world if self.average else 1.0,
+                                 self.mc_ctas)
+            self.barrier(lane)
+            return
         if hi > lo and self.direct:
             if not skip_red:
                 ops.shard_reduce_peers(flat[lo:hi], [self.peers[p][off + lo:off + hi] for p in others],

@@ -674,3 +674,10 @@ def shard_reduce_peers(dst, srcs, scale: float, max_ctas: int = 0) -> None:
     arr = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in srcs])
     rc = _lib.load().owl_shard_reduce_peers(dst.data_ptr(), arr, n, dst.numel(), float(scale), max_ctas, _stream())
     _lib.check(rc, "owl_shard_reduce_peers")
+
+
+def mc_allreduce(mc_ptr: int, n: int, scale: float, max_ctas: int = 0) -> None:
+    """All-reduce (sum * scale) of n fp32 at the MULTICAST address `mc_ptr` (this rank's shard of a symmetric bucket),
+    reduced inside NVSwitch.  The caller orders it between two cross-rank barriers."""
+    rc = _lib.load().owl_mc_allreduce(C.c_void_p(int(mc_ptr)), int(n), float(scale), max_ctas, _stream())
+    _lib.check(rc, "owl_mc_allreduce")

@@ -32,7 +32,9 @@ def loss_fn(m, x, c, t):
 def grads(mode, graph):
     os.environ["OWL_EXCHANGE"] = mode
     b = engine.GradBuckets(model)
-    assert (b.exchange is not None) == (mode == "ce"), mode
+    assert (b.exchange is not None) == (mode != "nccl"), mode
+    if b.exchange is not None:
+        assert b.exchange.mode == mode, (b.exchange.mode, mode)
     step = engine.TrainStep(model, loss_fn, [x, cond, tgt], buckets=b, use_graph=graph, warmup=2)
     for _ in range(2):
         step(x, cond, tgt)
@@ -44,14 +46,19 @@ def grads(mode, graph):
 
 ref = grads("nccl", False)
 ok = True
-for graph in (False, True):
-    got = grads("ce", graph)
+import torch.distributed._symmetric_memory as _sm
+_probe = _sm.empty(1024, dtype=torch.float32, device=dev)
+has_mc = bool(int(_sm.rendezvous(_probe, dist.group.WORLD).multicast_ptr))
+if rank == 0:
+    print("multicast mapping:", has_mc, flush=True)
+for mode, graph in [(m, g_) for m in (["ce", "mc"] if has_mc else ["ce"]) for g_ in (False, True)]:
+    got = grads(mode, graph)
     err = ((got - ref).abs().max() / ref.abs().max()).item()
     same_across = got.clone()
     dist.broadcast(same_across, 0)
     bit_equal = bool(torch.equal(same_across, got))
     if rank == 0:
-        print(f"copy-engine exchange ({'graph' if graph else 'eager'}) vs nccl: max rel err {err:.2e}; identical on every rank: {bit_equal}",
+        print(f"{mode} exchange ({'graph' if graph else 'eager'}) vs nccl: max rel err {err:.2e}; identical on every rank: {bit_equal}",
               flush=True)
     ok = ok and err <= 1e-5 and bit_equal
 dist.barrier()
