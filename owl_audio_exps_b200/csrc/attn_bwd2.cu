@@ -83,6 +83,33 @@ __device__ __forceinline__ Bwd2Item bwd2_item(const AttnBwd2Params& p, int w) {
   return it;
 }
 
+// 32 query columns of one key row: P^T = exp2(S^T c - lse), dS^T = P^T (dP^T / sqrt(dh) - delta / sqrt(dh)), both packed to bf16.
+// FULL = every (key, query) of the chunk is visible: no per-element mask test (the common case away from the band edges:
+// 5 instructions per element instead of 8).
+template <bool FULL>
+__device__ __forceinline__ void bwd2_softmax_chunk(const uint32_t (&rs)[32], const uint32_t (&rp)[32], uint32_t (&pk)[16],
+                                                   uint32_t (&dk)[16], const float4* st_lse, const float4* st_del,
+                                                   float scale_log2, float scale, uint32_t valid) {
+#pragma unroll
+  for (int e4 = 0; e4 < 8; ++e4) {
+    const float4 l4 = st_lse[e4], d4 = st_del[e4];
+    const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, dl[4] = {d4.x, d4.y, d4.z, d4.w};
+    float pv[4], dv[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int idx = e4 * 4 + e;
+      float pe = exp2f(fmaf(__uint_as_float(rs[idx]), scale_log2, -ls[e]));
+      if (!FULL && !((valid >> idx) & 1u)) pe = 0.f;
+      pv[e] = pe;
+      dv[e] = pe * fmaf(__uint_as_float(rp[idx]), scale, -dl[e]);
+    }
+    pk[e4 * 2] = pack_bf16(pv[0], pv[1]);
+    pk[e4 * 2 + 1] = pack_bf16(pv[2], pv[3]);
+    dk[e4 * 2] = pack_bf16(dv[0], dv[1]);
+    dk[e4 * 2 + 1] = pack_bf16(dv[2], dv[3]);
+  }
+}
+
 template <int DH>
 __global__ void __launch_bounds__(512, 1)
 attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmDO,
@@ -196,6 +223,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           float x = i < p.Lq ? __ldg(row + i) : (is_lse ? -INFINITY : 0.f);
           // rows with nothing visible (lse = -inf) and padding rows: exponent offset +inf -> P = 0
           if (is_lse) x = x == -INFINITY ? INFINITY : x * 1.4426950408889634f;
+          else x *= p.scale;               // delta / sqrt(dh): dS = P (dP / sqrt(dh) - delta / sqrt(dh)) is one FFMA + one FMUL
           v[e] = x;
         }
         *reinterpret_cast<float4*>(dst + lane * 4) = make_float4(v[0], v[1], v[2], v[3]);
@@ -416,24 +444,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             }
           }
           tmem_ld_wait();
-#pragma unroll
-          for (int e4 = 0; e4 < 8; ++e4) {
-            const float4 l4 = st_lse[c * 8 + e4], d4 = st_del[c * 8 + e4];
-            const float ls[4] = {l4.x, l4.y, l4.z, l4.w}, dl[4] = {d4.x, d4.y, d4.z, d4.w};
-            float pv[4], dv[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int idx = e4 * 4 + e;
-              float pe = exp2f(fmaf(__uint_as_float(rs[idx]), p.scale_log2, -ls[e]));
-              if (!full && !((valid >> idx) & 1u)) pe = 0.f;
-              pv[e] = pe;
-              dv[e] = pe * (__uint_as_float(rp[idx]) - dl[e]) * p.scale;
-            }
-            pk[e4 * 2] = pack_bf16(pv[0], pv[1]);
-            pk[e4 * 2 + 1] = pack_bf16(pv[2], pv[3]);
-            dk[e4 * 2] = pack_bf16(dv[0], dv[1]);
-            dk[e4 * 2 + 1] = pack_bf16(dv[2], dv[3]);
-          }
+          if (full) bwd2_softmax_chunk<true>(rs, rp, pk, dk, st_lse + c * 8, st_del + c * 8, p.scale_log2, p.scale, valid);
+          else bwd2_softmax_chunk<false>(rs, rp, pk, dk, st_lse + c * 8, st_del + c * 8, p.scale_log2, p.scale, valid);
           // P^T / dS^T over the columns this thread has already read (first half of its own 64-column region)
           tmem_st_x16(tST + c * 16, pk);
           tmem_st_x16(tDPT + c * 16, dk);
