@@ -135,7 +135,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* dq_free = sdp_full + 4;         // [2] drain -> MMA (128 arrivals)
   uint64_t* acc_done = sdp_full + 6;        // MMA -> softmax epilogue (dV / dK complete)
   uint64_t* acc_free = sdp_full + 7;        // softmax epilogue -> MMA (256 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 8);
+  uint64_t* pds_half = sdp_full + 8;        // softmax -> MMA: first 32 query columns of both halves are in TMEM (256 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -152,6 +153,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
     mbar_init(sdp_full, 1);
     mbar_init(pds_full, 256);
+    mbar_init(pds_half, 256);
     for (int s = 0; s < 2; ++s) {
       mbar_init(&dq_full[s], 1);
       mbar_init(&dq_free[s], 128);
@@ -263,29 +265,34 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
           for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDPT, desc_kmajor(sV, k), desc_kmajor(sDO, k), idesc_s, k > 0);
           umma_commit(sdp_full);
-          // MMA 2
-          mbar_wait(pds_full, pair_n & 1);
+          // MMA 2, first part: the k-steps of dV / dK over the query columns the softmax finishes first (chunk 0 of both
+          // warpgroups = columns [0,32) and [64,96) = k 0,1,4,5) run while the softmax is still on the other 64 columns
+          mbar_wait(pds_half, pair_n & 1);
           if (q == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);       // the previous item's epilogue has read dV / dK
           const uint32_t acc = q > 0 ? 1u : 0u;
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
+            const int k = (kk >> 1) * 4 + (kk & 1);
+            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+            umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+          }
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const int k = (kk >> 1) * 4 + (kk & 1);
+            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+            umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+          }
+          // second part: everything is in TMEM / shared memory
+          mbar_wait(pds_full, pair_n & 1);
           if (DH == 64) {
             const uint32_t buf = pair_n & 1;
             mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);     // the drain has read this dQ buffer's previous content
             tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < kTile / 16; ++k) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
-              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-              umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
-            }
-#pragma unroll
-            for (int k = 0; k < kTile / 16; ++k) {
-              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-              umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
-            }
             const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
 #pragma unroll
             for (int k = 0; k < kTile / 16; ++k)
               umma_bf16_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
-            umma_commit(&qdo_empty[s]);
             umma_commit(&dq_full[buf]);
           } else {
             tc_fence_after();
@@ -301,18 +308,20 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                              k > 0 ? 1u : 0u);
             }
             umma_commit(&dq_full[0]);
-#pragma unroll
-            for (int k = 0; k < kTile / 16; ++k) {
-              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-              umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
-            }
-#pragma unroll
-            for (int k = 0; k < kTile / 16; ++k) {
-              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-              umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (k > 0)) ? 1u : 0u);
-            }
-            umma_commit(&qdo_empty[s]);
           }
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const int k = (kk >> 1) * 4 + (kk & 1) + 2;
+            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+            umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, 1u);
+          }
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const int k = (kk >> 1) * 4 + (kk & 1) + 2;
+            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+            umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, 1u);
+          }
+          umma_commit(&qdo_empty[s]);
           ++pair_n;
         }
         umma_commit(acc_done);
@@ -453,6 +462,11 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           for (int g = 0; g < 4; ++g)
             *reinterpret_cast<uint4*>(sDS + tile_chunk_offset(r, hf * 8 + c * 4 + g)) =
                 make_uint4(dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
+          if (c == 0) {    // dV / dK over these 32 query columns may start (they read P^T / dS^T from TMEM only)
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(pds_half);
+          }
         }
         tmem_st_wait();
         tc_fence_before();
