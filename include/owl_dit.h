@@ -32,6 +32,7 @@ extern "C" {
 #define OWL_ERR_ALIGN (-2)       /* pointer or leading dimension violates 16-byte alignment    */
 #define OWL_ERR_UNSUPPORTED (-3) /* shape outside what the kernels implement (e.g. head dim)   */
 #define OWL_ERR_DRIVER (-4)      /* CUDA driver entry point / tensor-map encoding failed       */
+#define OWL_ERR_TOO_LARGE (-5)   /* size beyond the fixed capacity of a no-allocation entry point */
 
 typedef void* owl_stream_t; /* cudaStream_t */
 
@@ -384,6 +385,18 @@ int owl_shard_reduce_peers(float* dst, const float* const* srcs, int n_src, int6
  * summed inside NVSwitch (multimem.ld_reduce), scaled, and written back to all ranks (multimem.st): all-reduce of the shard
  * with no staging and no copies.  The caller brackets the call with device-side barriers across the ranks. */
 int owl_mc_allreduce(float* mc_shard, int64_t n, float scale, int max_ctas, owl_stream_t stream);
+
+/* owl_gemm_smallm for callers that cannot allocate (no cudaMalloc under CUDA graph capture, in a tight serving loop, in a
+ * harness that forbids it).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arithmetic and epilogues as owl_gemm_smallm (no adaLN prologue, no next-weight prefetch); the split-K scratch is a
+ * file-scope __device__ array of the library (4 194 816 bytes, resident on every GPU that loads the library until the
+ * process exits) instead of a caller workspace, so the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine).  Limit: N <= owl_gemm_smallm_static_max_n() = 8192; a larger N returns OWL_ERR_TOO_LARGE.  All calls on
+ * a device share the array and it keeps the previous call's contents: the part a call uses is cleared on `stream` first;
+ * calls that overlap on the GPU (other streams, parallel graph branches) race on it and must be serialised by the caller. */
+int64_t owl_gemm_smallm_static_max_n(void);
+int owl_gemm_smallm_static(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
+                           const owl_gemm_epilogue* epi, owl_stream_t stream);
 
 #ifdef __cplusplus
 }

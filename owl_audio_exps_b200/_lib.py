@@ -59,6 +59,8 @@ SIGNATURES = {
     "owl_gemm_smallm_workspace_bytes": ([i64], i64),
     "owl_gemm_smallm": ([i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), C.POINTER(AdaLNPrologue), vp, i64, vp,
                          i64, vp], C.c_int),
+    "owl_gemm_smallm_static_max_n": ([], i64),
+    "owl_gemm_smallm_static": ([i64, i64, i64, vp, i64, vp, i64, C.POINTER(GemmEpilogue), vp], C.c_int),
     "owl_gemm_bf16_check": ([C.c_int, i64, i64, i64, vp, i64, vp, i64, vp, i64, vp], C.c_int),
     "owl_cast_f32_bf16": ([vp, vp, i64, vp], C.c_int),
     "owl_silu_bf16": ([vp, vp, i64, vp], C.c_int),

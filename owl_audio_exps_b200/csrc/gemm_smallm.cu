@@ -651,4 +651,86 @@ int owl_gemm_smallm(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda,
   return bn == 128 ? launch_smallm<128>(tmA, tmB, p, grid, smem_bytes, s) : launch_smallm<64>(tmA, tmB, p, grid, smem_bytes, s);
 }
 
+// ------------------------------------------------------------------------------------------------
+// owl_gemm_smallm_static: the same GEMM for callers that cannot allocate (no cudaMalloc under graph capture, in a tight
+// serving loop, in a harness that forbids it).  The split-K scratch (fp32 partial tiles + arrival counters) is a file-scope
+// __device__ array instead of a caller-provided workspace.  No counterpart in the
+// reference.
+//   * limit: N <= OWL_SMALLM_STATIC_MAX_N (8192): (8192 / 64) x (128 x 64 x 4 + 4) = 4 194 816 bytes, held by every GPU that
+//     loads the library until the process exits;
+//   * in host code `g_smallm_scratch` is only a stand-in for the symbol: its device address comes from
+//     cudaGetSymbolAddress, once per device, with that device current;
+//   * every call shares the array and it keeps the previous call's contents: the part this call uses is cleared on `stream`
+//     first (the partial tiles are accumulated with red.add and the counters count arrivals: both must start at zero);
+//   * two calls that overlap on the GPU (different streams, or graph branches) race on the array: serialise them.
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace owl {
+
+constexpr int64_t kStaticMaxN = 8192;
+constexpr int64_t kStaticTiles = kStaticMaxN / 64;
+constexpr int64_t kStaticScratchBytes = kStaticTiles * 128 * 64 * 4 + kStaticTiles * 4;
+
+static __device__ __align__(256) unsigned char g_smallm_scratch[kStaticScratchBytes];
+
+// clears the part of the scratch a call uses (a kernel, not a memset node: the GEMM behind it is launched with programmatic
+// stream serialisation, which wants a kernel in front of it)
+__global__ void __launch_bounds__(256) smallm_scratch_clear_kernel(uint4* __restrict__ dst, long long n16) {
+  pdl_prologue();   // the previous user of the array (an earlier call on this stream) has finished
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16; i += stride)
+    dst[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+static void* g_smallm_scratch_ptr[64];          // per device: the array's DEVICE address
+static std::atomic<uint64_t> g_smallm_scratch_have{0};
+
+static int smallm_scratch_address(void** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= 64) return OWL_ERR_UNSUPPORTED;
+  const uint64_t bit = 1ull << dev;
+  if (!(g_smallm_scratch_have.load(std::memory_order_acquire) & bit)) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_smallm_scratch);   // the current device's copy of the array
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return static_cast<int>(e);
+    }
+    if (ptr == nullptr) return OWL_ERR_DRIVER;
+    g_smallm_scratch_ptr[dev] = ptr;                    // two threads racing here store the same value
+    g_smallm_scratch_have.fetch_or(bit, std::memory_order_release);
+  }
+  *out = g_smallm_scratch_ptr[dev];
+  return OWL_OK;
+}
+
+}  // namespace owl
+
+extern "C" {
+
+int64_t owl_gemm_smallm_static_max_n(void) { return owl::kStaticMaxN; }
+
+int owl_gemm_smallm_static(int64_t M, int64_t N, int64_t K, const void* A, int64_t lda, const void* W, int64_t ldw,
+                           const owl_gemm_epilogue* epi, owl_stream_t stream) {
+  if (N > owl::kStaticMaxN) return OWL_ERR_TOO_LARGE;
+  if (N <= 0) return OWL_ERR_BAD_ARG;
+  void* scratch = nullptr;
+  int rc = owl::smallm_scratch_address(&scratch);
+  if (rc != OWL_OK) return rc;
+  const int64_t need = owl_gemm_smallm_workspace_bytes(N);   // <= kStaticScratchBytes for N <= kStaticMaxN
+  if (need > owl::kStaticScratchBytes) return OWL_ERR_TOO_LARGE;
+  // the array keeps whatever the previous call (any shape, possibly an aborted one) left: start this call's part at zero
+  const long long n16 = (need + 15) / 16;                    // the array is 256-byte aligned and a multiple of 16 bytes long
+  long long blocks = (n16 + 255) / 256;
+  if (blocks > 4LL * owl::sm_count()) blocks = 4LL * owl::sm_count();
+  (void)owl::launch_k(owl::smallm_scratch_clear_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0,
+                      static_cast<cudaStream_t>(stream), static_cast<uint4*>(scratch), n16);
+  rc = owl::launch_status();
+  if (rc != OWL_OK) return rc;
+  return owl_gemm_smallm(M, N, K, A, lda, W, ldw, epi, nullptr, scratch, need, nullptr, 0, stream);
+}
+
 }  // extern "C"

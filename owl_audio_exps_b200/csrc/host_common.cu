@@ -157,6 +157,7 @@ const char* owl_error_string(int code) {
     case OWL_ERR_ALIGN: return "pointer or leading dimension not 16-byte aligned";
     case OWL_ERR_UNSUPPORTED: return "shape not supported by the sm_100a kernels";
     case OWL_ERR_DRIVER: return "CUDA driver entry point / tensor-map encoding failed";
+    case OWL_ERR_TOO_LARGE: return "size beyond the fixed capacity of a no-allocation entry point (static device scratch)";
     default: break;
   }
   if (code > 0) return cudaGetErrorString(static_cast<cudaError_t>(code));
