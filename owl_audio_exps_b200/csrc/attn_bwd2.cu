@@ -52,14 +52,15 @@ template <int DH_>
 struct Bwd2Cfg {
   static constexpr int DH = DH_;
   static constexpr int kThreads = 512;
-  static constexpr int kStages = DH == 64 ? 3 : 2;         // {Q_i, dO_i, lse_i, delta_i} in flight
+  static constexpr int kStages = 2;                        // {Q_i, dO_i, lse_i, delta_i} in flight
+  static constexpr int kDSBufs = DH == 64 ? 2 : 1;         // dh 64: dS^T of pair n + 1 is written while dQ of pair n reads its own
   static constexpr int kTileBytes = kTile * DH * 2;        // 16 / 32 KB
   static constexpr int kOffK = 0;
   static constexpr int kOffV = kTileBytes;
   static constexpr int kOffRing = 2 * kTileBytes;          // per stage: Q then dO
   static constexpr int kStageBytes = 2 * kTileBytes;
   static constexpr int kOffDS = kOffRing + kStages * kStageBytes;   // dS^T [128 keys][128 q] bf16, two swizzled panels
-  static constexpr int kOffDQ = kOffDS + kTile * kTile * 2;         // dh = 64: fp32 staging [128 q][64], two 128B-swizzled panels
+  static constexpr int kOffDQ = kOffDS + kDSBufs * kTile * kTile * 2;         // dh = 64: fp32 staging [128 q][64], two 128B-swizzled panels
   static constexpr int kOffStat = kOffDQ + (DH == 64 ? kTile * DH * 4 : 0);   // per stage: lse2[128], delta[128] fp32
   static constexpr int kOffBar = kOffStat + kStages * 1024;
   static constexpr int kSmemBytes = kOffBar + 512;
@@ -136,7 +137,9 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* acc_done = sdp_full + 6;        // MMA -> softmax epilogue (dV / dK complete)
   uint64_t* acc_free = sdp_full + 7;        // softmax epilogue -> MMA (256 arrivals)
   uint64_t* pds_half = sdp_full + 8;        // softmax -> MMA: first 32 query columns of both halves are in TMEM (256 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 9);
+  uint64_t* s_half = sdp_full + 9;          // [2] dh 64, MMA -> softmax warpgroup h: S^T / dP^T of ITS 64 query columns
+  uint64_t* p_half = sdp_full + 11;         // [2] dh 64, softmax warpgroup h -> MMA (128 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -154,6 +157,10 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     mbar_init(sdp_full, 1);
     mbar_init(pds_full, 256);
     mbar_init(pds_half, 256);
+    for (int h = 0; h < 2; ++h) {
+      mbar_init(&s_half[h], 1);
+      mbar_init(&p_half[h], 128);
+    }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&dq_full[s], 1);
       mbar_init(&dq_free[s], 128);
@@ -249,6 +256,73 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         const Bwd2Item it = bwd2_item(p, w);
         if (it.n_q <= 0) continue;
         mbar_wait(kv_full, item_n & 1);
+        if (DH == 64) {
+          // dh 64: the two softmax warpgroups run HALF A PERIOD APART.  Warpgroup h owns query columns [64h, 64h + 64) of every
+          // pair: its S^T / dP^T columns, its k-steps of dV / dK and its half of dS^T touch nothing of the other half, so
+          //   MMA 2 (half h, pair q) -> MMA 1 (half h, pair q + 1)
+          // is issued the moment warpgroup h hands over P^T / dS^T, while the other warpgroup is still in its softmax:
+          // each warpgroup waits for 2 x 256 clk of MMA per pair instead of the whole pair's 1280.  dQ (all 128 queries,
+          // M = 128) follows half B and reads the dS^T buffer of the pair's parity.
+          constexpr uint32_t idesc_h = make_idesc_bf16(kTile, 64, false, false);   // S^T / dP^T of one half: N = 64 queries
+          auto mma1_half = [&](uint32_t st, uint32_t h) {
+            const uint32_t sQh = smem_u32(smem + kOffRing + st * kStageBytes) + h * (64 * 128), sDOh = sQh + kTileBytes;
+#pragma unroll
+            for (int k = 0; k < DH / 16; ++k)
+              umma_bf16_ss(tST + h * 64, desc_kmajor(sK, k), desc_kmajor(sQh, k), idesc_h, k > 0);
+#pragma unroll
+            for (int k = 0; k < DH / 16; ++k)
+              umma_bf16_ss(tDPT + h * 64, desc_kmajor(sV, k), desc_kmajor(sDOh, k), idesc_h, k > 0);
+            umma_commit(&s_half[h]);
+          };
+          uint32_t s = ring_n % kStages;
+          mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
+          ++ring_n;
+          tc_fence_after();
+          mma1_half(s, 0);
+          mma1_half(s, 1);
+          for (int q = 0; q < it.n_q; ++q) {
+            const uint32_t sQ = smem_u32(smem + kOffRing + s * kStageBytes), sDO = sQ + kTileBytes;
+            const bool more = q + 1 < it.n_q;
+            uint32_t s_next = s;
+            for (uint32_t h = 0; h < 2; ++h) {
+              mbar_wait(&p_half[h], pair_n & 1);
+              if (q == 0 && h == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);   // the previous item's epilogue has read dV / dK
+              const uint32_t acc = (q > 0 || h > 0) ? 1u : 0u;
+              tc_fence_after();
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
+                const uint32_t k = h * 4 + kk;
+                umma_bf16_ts(tDV, tST + h * 64 + kk * 8, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+              }
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk) {
+                const uint32_t k = h * 4 + kk;
+                umma_bf16_ts(tDK, tDPT + h * 64 + kk * 8, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+              }
+              if (h == 1) umma_commit(&qdo_empty[s]);   // Q_i / dO_i / lse / delta of this pair are no longer read
+              if (more) {
+                if (h == 0) {
+                  s_next = ring_n % kStages;
+                  mbar_wait(&qdo_full[s_next], (ring_n / kStages) & 1);
+                  ++ring_n;
+                  tc_fence_after();
+                }
+                mma1_half(s_next, h);
+              }
+            }
+            const uint32_t buf = pair_n & 1;
+            mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);     // the drain has read this dQ buffer's previous content
+            tc_fence_after();
+            const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
+            const uint32_t sDSb = sDS + buf * (kTile * kTile * 2);
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k)
+              umma_bf16_ss(tDQ, desc_mnmajor(sDSb, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+            umma_commit(&dq_full[buf]);
+            s = s_next;
+            ++pair_n;
+          }
+        } else
         for (int q = 0; q < it.n_q; ++q) {
           const uint32_t s = ring_n % kStages;
           mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
@@ -431,7 +505,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         ++ring_n;
         const float4* st_lse = reinterpret_cast<const float4*>(smem + kOffStat + s * 1024) + hf * 16;
         const float4* st_del = st_lse + 32;
-        mbar_wait(sdp_full, pair_n & 1);
+        mbar_wait(DH == 64 ? &s_half[hf] : sdp_full, pair_n & 1);
+        uint8_t* sDSp = sDS + (DH == 64 ? (pair_n & 1) * (kTile * kTile * 2) : 0);   // dh 64: dS^T buffer of the pair's parity
         ++pair_n;
         tc_fence_after();
         const bool full = doc_row == nullptr && ilo <= i0 && i0 + 64 <= ihi;
@@ -460,9 +535,9 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           tmem_st_x16(tDPT + c * 16, dk);
 #pragma unroll
           for (int g = 0; g < 4; ++g)
-            *reinterpret_cast<uint4*>(sDS + tile_chunk_offset(r, hf * 8 + c * 4 + g)) =
+            *reinterpret_cast<uint4*>(sDSp + tile_chunk_offset(r, hf * 8 + c * 4 + g)) =
                 make_uint4(dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
-          if (c == 0) {    // dV / dK over these 32 query columns may start (they read P^T / dS^T from TMEM only)
+          if (DH == 128 && c == 0) {    // dV / dK over these 32 query columns may start (they read P^T / dS^T from TMEM only)
             tmem_st_wait();
             tc_fence_before();
             mbar_arrive(pds_half);
@@ -471,7 +546,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tmem_st_wait();
         tc_fence_before();
         fence_proxy_async_smem();
-        mbar_arrive(pds_full);
+        mbar_arrive(DH == 64 ? &p_half[hf] : pds_full);
       }
       // epilogue: WG0 stores dV_j, WG1 stores dK_j
       mbar_wait(acc_done, item_n & 1);
