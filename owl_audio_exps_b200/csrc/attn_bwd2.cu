@@ -242,7 +242,11 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
   } else if (warp == 9) {
     // ---------------------------------------------------------------- MMA issuer
-    if (lane == 0) {
+    // The WHOLE warp walks the schedule (waits included) and one elected lane issues each tcgen05 instruction.  Under a
+    // divergent `if (lane == 0)` ptxas wraps every UTCHMMA in an ELECT / BRA.U.ANY loop and moves its operands to uniform
+    // registers one at a time: ~100 clk per MMA, and with 40 MMAs of 32-64 clk per pair this warp, not the tensor pipe or the
+    // softmax, set the pace of the kernel (ncu source view: the issuer warp never waited).
+    {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);   // S^T, dP^T
       constexpr uint32_t idesc_acc = make_idesc_bf16(kTile, DH, false, true);     // dV, dK: A from TMEM, B MN-major
       constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, true, true);       // dQ: A = dS^T tile read MN-major
@@ -251,6 +255,15 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       const uint32_t sK = smem_u32(smem + kOffK), sV = smem_u32(smem + kOffV), sDS = smem_u32(smem + kOffDS);
       const uint32_t tST = tmem_base + kColST, tDPT = tmem_base + kColDPT;
       const uint32_t tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
+      auto e_ss = [](uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+        if (elect_one()) umma_bf16_ss(d, da, db, idesc, accumulate);
+      };
+      auto e_ts = [](uint32_t d, uint32_t ta, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+        if (elect_one()) umma_bf16_ts(d, ta, db, idesc, accumulate);
+      };
+      auto e_commit = [](uint64_t* bar) {
+        if (elect_one()) umma_commit(bar);
+      };
       uint32_t item_n = 0, ring_n = 0, pair_n = 0;
       for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
         const Bwd2Item it = bwd2_item(p, w);
@@ -268,11 +281,11 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             const uint32_t sQh = smem_u32(smem + kOffRing + st * kStageBytes) + h * (64 * 128), sDOh = sQh + kTileBytes;
 #pragma unroll
             for (int k = 0; k < DH / 16; ++k)
-              umma_bf16_ss(tST + h * 64, desc_kmajor(sK, k), desc_kmajor(sQh, k), idesc_h, k > 0);
+              e_ss(tST + h * 64, desc_kmajor(sK, k), desc_kmajor(sQh, k), idesc_h, k > 0);
 #pragma unroll
             for (int k = 0; k < DH / 16; ++k)
-              umma_bf16_ss(tDPT + h * 64, desc_kmajor(sV, k), desc_kmajor(sDOh, k), idesc_h, k > 0);
-            umma_commit(&s_half[h]);
+              e_ss(tDPT + h * 64, desc_kmajor(sV, k), desc_kmajor(sDOh, k), idesc_h, k > 0);
+            e_commit(&s_half[h]);
           };
           uint32_t s = ring_n % kStages;
           mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
@@ -292,14 +305,14 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
                 const uint32_t k = h * 4 + kk;
-                umma_bf16_ts(tDV, tST + h * 64 + kk * 8, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+                e_ts(tDV, tST + h * 64 + kk * 8, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
               }
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk) {
                 const uint32_t k = h * 4 + kk;
-                umma_bf16_ts(tDK, tDPT + h * 64 + kk * 8, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+                e_ts(tDK, tDPT + h * 64 + kk * 8, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
               }
-              if (h == 1) umma_commit(&qdo_empty[s]);   // Q_i / dO_i / lse / delta of this pair are no longer read
+              if (h == 1) e_commit(&qdo_empty[s]);   // Q_i / dO_i / lse / delta of this pair are no longer read
               if (more) {
                 if (h == 0) {
                   s_next = ring_n % kStages;
@@ -317,8 +330,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             const uint32_t sDSb = sDS + buf * (kTile * kTile * 2);
 #pragma unroll
             for (int k = 0; k < kTile / 16; ++k)
-              umma_bf16_ss(tDQ, desc_mnmajor(sDSb, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
-            umma_commit(&dq_full[buf]);
+              e_ss(tDQ, desc_mnmajor(sDSb, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+            e_commit(&dq_full[buf]);
             s = s_next;
             ++pair_n;
           }
@@ -335,10 +348,10 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           tc_fence_after();
           // MMA 1 (in issue order behind MMA 2 of the previous pair, which still reads P^T / dS^T from these columns)
 #pragma unroll
-          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tST, desc_kmajor(sK, k), desc_kmajor(sQ, k), idesc_s, k > 0);
+          for (int k = 0; k < DH / 16; ++k) e_ss(tST, desc_kmajor(sK, k), desc_kmajor(sQ, k), idesc_s, k > 0);
 #pragma unroll
-          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDPT, desc_kmajor(sV, k), desc_kmajor(sDO, k), idesc_s, k > 0);
-          umma_commit(sdp_full);
+          for (int k = 0; k < DH / 16; ++k) e_ss(tDPT, desc_kmajor(sV, k), desc_kmajor(sDO, k), idesc_s, k > 0);
+          e_commit(sdp_full);
           // MMA 2, first part: the k-steps of dV / dK over the query columns the softmax finishes first (chunk 0 of both
           // warpgroups = columns [0,32) and [64,96) = k 0,1,4,5) run while the softmax is still on the other 64 columns
           mbar_wait(pds_half, pair_n & 1);
@@ -349,13 +362,13 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
             const int k = (kk >> 1) * 4 + (kk & 1);
             const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+            e_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
           }
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             const int k = (kk >> 1) * 4 + (kk & 1);
             const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+            e_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
           }
           // second part: everything is in TMEM / shared memory
           mbar_wait(pds_full, pair_n & 1);
@@ -366,8 +379,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
 #pragma unroll
             for (int k = 0; k < kTile / 16; ++k)
-              umma_bf16_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
-            umma_commit(&dq_full[buf]);
+              e_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+            e_commit(&dq_full[buf]);
           } else {
             tc_fence_after();
             // dQ partial first, as four N = 32 pieces into the column gaps [32,64) [96,128) [160,192) [224,256): piece c
@@ -378,28 +391,28 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
               const uint32_t sKc = sK + (c >> 1) * kPanelBytes + (c & 1) * 64;
 #pragma unroll
               for (int k = 0; k < kTile / 16; ++k)
-                umma_bf16_ss(tDQc, desc_mnmajor(sDS, k), make_smem_desc(sKc + k * 2048, kPanelBytes, 1024), idesc_dq32,
+                e_ss(tDQc, desc_mnmajor(sDS, k), make_smem_desc(sKc + k * 2048, kPanelBytes, 1024), idesc_dq32,
                              k > 0 ? 1u : 0u);
             }
-            umma_commit(&dq_full[0]);
+            e_commit(&dq_full[0]);
           }
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             const int k = (kk >> 1) * 4 + (kk & 1) + 2;
             const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, 1u);
+            e_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, 1u);
           }
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             const int k = (kk >> 1) * 4 + (kk & 1) + 2;
             const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, 1u);
+            e_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, 1u);
           }
-          umma_commit(&qdo_empty[s]);
+          e_commit(&qdo_empty[s]);
           ++pair_n;
         }
-        umma_commit(acc_done);
-        umma_commit(kv_empty);
+        e_commit(acc_done);
+        e_commit(kv_empty);
         ++item_n;
       }
     }
