@@ -277,61 +277,70 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           // each warpgroup waits for 2 x 256 clk of MMA per pair instead of the whole pair's 1280.  dQ (all 128 queries,
           // M = 128) follows half B and reads the dS^T buffer of the pair's parity.
           constexpr uint32_t idesc_h = make_idesc_bf16(kTile, 64, false, false);   // S^T / dP^T of one half: N = 64 queries
+          // (plain issue, to be called inside ONE elect_one() region per batch: one ELECT and one set of uniform operands
+          // per batch instead of per instruction - the issuer warp's instruction count is what bounds this kernel)
           auto mma1_half = [&](uint32_t st, uint32_t h) {
             const uint32_t sQh = smem_u32(smem + kOffRing + st * kStageBytes) + h * (64 * 128), sDOh = sQh + kTileBytes;
 #pragma unroll
             for (int k = 0; k < DH / 16; ++k)
-              e_ss(tST + h * 64, desc_kmajor(sK, k), desc_kmajor(sQh, k), idesc_h, k > 0);
+              umma_bf16_ss(tST + h * 64, desc_kmajor(sK, k), desc_kmajor(sQh, k), idesc_h, k > 0);
 #pragma unroll
             for (int k = 0; k < DH / 16; ++k)
-              e_ss(tDPT + h * 64, desc_kmajor(sV, k), desc_kmajor(sDOh, k), idesc_h, k > 0);
-            e_commit(&s_half[h]);
+              umma_bf16_ss(tDPT + h * 64, desc_kmajor(sV, k), desc_kmajor(sDOh, k), idesc_h, k > 0);
+            umma_commit(&s_half[h]);
           };
           uint32_t s = ring_n % kStages;
           mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
           ++ring_n;
           tc_fence_after();
-          mma1_half(s, 0);
-          mma1_half(s, 1);
+          if (elect_one()) {
+            mma1_half(s, 0);
+            mma1_half(s, 1);
+          }
+          __syncwarp();
           for (int q = 0; q < it.n_q; ++q) {
             const uint32_t sQ = smem_u32(smem + kOffRing + s * kStageBytes), sDO = sQ + kTileBytes;
             const bool more = q + 1 < it.n_q;
             uint32_t s_next = s;
+            if (more) {   // {Q, dO} of the next pair (prefetched by the TMA warp while this pair was computed)
+              s_next = ring_n % kStages;
+              mbar_wait(&qdo_full[s_next], (ring_n / kStages) & 1);
+              ++ring_n;
+            }
+            if (q == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);   // the previous item's epilogue has read dV / dK
+#pragma unroll
             for (uint32_t h = 0; h < 2; ++h) {
               mbar_wait(&p_half[h], pair_n & 1);
-              if (q == 0 && h == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);   // the previous item's epilogue has read dV / dK
               const uint32_t acc = (q > 0 || h > 0) ? 1u : 0u;
               tc_fence_after();
+              if (elect_one()) {
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
-                const uint32_t k = h * 4 + kk;
-                e_ts(tDV, tST + h * 64 + kk * 8, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
-              }
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk) {
-                const uint32_t k = h * 4 + kk;
-                e_ts(tDK, tDPT + h * 64 + kk * 8, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
-              }
-              if (h == 1) e_commit(&qdo_empty[s]);   // Q_i / dO_i / lse / delta of this pair are no longer read
-              if (more) {
-                if (h == 0) {
-                  s_next = ring_n % kStages;
-                  mbar_wait(&qdo_full[s_next], (ring_n / kStages) & 1);
-                  ++ring_n;
-                  tc_fence_after();
+                for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
+                  const uint32_t k = h * 4 + kk;
+                  umma_bf16_ts(tDV, tST + h * 64 + kk * 8, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
                 }
-                mma1_half(s_next, h);
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                  const uint32_t k = h * 4 + kk;
+                  umma_bf16_ts(tDK, tDPT + h * 64 + kk * 8, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+                }
+                if (h == 1) umma_commit(&qdo_empty[s]);   // Q_i / dO_i / lse / delta of this pair are no longer read
+                if (more) mma1_half(s_next, h);
               }
+              __syncwarp();
             }
             const uint32_t buf = pair_n & 1;
             mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);     // the drain has read this dQ buffer's previous content
             tc_fence_after();
             const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
             const uint32_t sDSb = sDS + buf * (kTile * kTile * 2);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < kTile / 16; ++k)
-              e_ss(tDQ, desc_mnmajor(sDSb, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
-            e_commit(&dq_full[buf]);
+              for (int k = 0; k < kTile / 16; ++k)
+                umma_bf16_ss(tDQ, desc_mnmajor(sDSb, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+              umma_commit(&dq_full[buf]);
+            }
+            __syncwarp();
             s = s_next;
             ++pair_n;
           }
