@@ -154,8 +154,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
 
+  // Producer and MMA issuer: the WHOLE warp walks the loop (barrier waits included) and one elected lane issues the TMA /
+  // tcgen05 instructions of a k-block as one batch.  Under a divergent `if (lane == 0)` ptxas wraps every UTCHMMA / UTMALDG
+  // in an ELECT / BRA.U.ANY loop and moves its operands to uniform registers one at a time (~100 clk per instruction, seen
+  // in the ncu source view of the attention backward) - as long as the 128 clk a 128x256x16 MMA takes on the tensor pipe.
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int stage = 0;
       uint32_t phase = 0;
       auto load = [&](void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
@@ -171,28 +175,31 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
           uint8_t* sa = smem_a + stage * Cfg::kABytes;
           uint8_t* sb = smem_b + stage * Cfg::kBBytes;
           const int k0 = kb * BK;
-          if (A_MN) {
+          if (elect_one()) {
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes * CTAS);
+            if (A_MN) {
 #pragma unroll
-            for (int pn = 0; pn < BM / 64; ++pn) load(sa + pn * 8192, &tmA, &full_bar[stage], m0 + pn * 64, k0);
-          } else {
-            load(sa, &tmA, &full_bar[stage], k0, m0);
-          }
-          if (B_MN) {
+              for (int pn = 0; pn < BM / 64; ++pn) load(sa + pn * 8192, &tmA, &full_bar[stage], m0 + pn * 64, k0);
+            } else {
+              load(sa, &tmA, &full_bar[stage], k0, m0);
+            }
+            if (B_MN) {
 #pragma unroll
-            for (int pn = 0; pn < BN / CTAS / 64; ++pn) load(sb + pn * 8192, &tmB, &full_bar[stage], n0 + pn * 64, k0);
-          } else {
-            load(sb, &tmB, &full_bar[stage], k0, n0);
+              for (int pn = 0; pn < BN / CTAS / 64; ++pn) load(sb + pn * 8192, &tmB, &full_bar[stage], n0 + pn * 64, k0);
+            } else {
+              load(sb, &tmB, &full_bar[stage], k0, n0);
+            }
           }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(TM, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
@@ -210,21 +217,33 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           tc_fence_after();
           const uint32_t sa = smem_u32(smem_a + stage * Cfg::kABytes);
           const uint32_t sb = smem_u32(smem_b + stage * Cfg::kBBytes);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, 8192, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
-            const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
-            if (CTAS == 2) umma_bf16_ss_2cta(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-            else umma_bf16_ss(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = A_MN ? make_smem_desc(sa + k * 2048, 8192, 1024) : make_smem_desc(sa + k * 32, 16, 1024);
+              const uint64_t db = B_MN ? make_smem_desc(sb + k * 2048, 8192, 1024) : make_smem_desc(sb + k * 32, 16, 1024);
+              if (CTAS == 2) umma_bf16_ss_2cta(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+              else umma_bf16_ss(tacc, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            }
+            // slot reusable once these MMAs have read it (pair: in both CTAs)
+            if (CTAS == 2) umma_commit_2cta(&empty_bar[stage]);
+            else umma_commit(&empty_bar[stage]);
+            // accumulator complete (pair: each CTA's epilogue reads its own 128 rows from its own TMEM)
+            if (kb + 1 == kb1) {
+              if (CTAS == 2) umma_commit_2cta(&tfull_bar[as]);
+              else umma_commit(&tfull_bar[as]);
+            }
           }
-          // slot reusable once these MMAs have read it (pair: in both CTAs)
-          if (CTAS == 2) umma_commit_2cta(&empty_bar[stage]);
-          else umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        // accumulator complete (pair: each CTA's epilogue reads its own 128 rows from its own TMEM)
-        if (CTAS == 2) umma_commit_2cta(&tfull_bar[as]);
-        else umma_commit(&tfull_bar[as]);
+        if (kb1 <= kb0) {   // (no k-block: cannot happen with the planner's splits; the epilogue must still be released)
+          if (elect_one()) {
+            if (CTAS == 2) umma_commit_2cta(&tfull_bar[as]);
+            else umma_commit(&tfull_bar[as]);
+          }
+          __syncwarp();
+        }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
