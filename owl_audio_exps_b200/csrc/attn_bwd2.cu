@@ -181,32 +181,38 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   pdl_launch();
 
   if (warp == 8) {
-    // ---------------------------------------------------------------- TMA producer
-    if (lane == 0) {
+    // ---------------------------------------------------------------- TMA producer (whole warp; one elected lane issues)
+    {
       uint32_t item_n = 0, ring_n = 0;
       for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
         const Bwd2Item it = bwd2_item(p, w);
         if (it.n_q <= 0) continue;
         mbar_wait(kv_empty, (item_n & 1) ^ 1);
         ++item_n;
-        mbar_arrive_expect_tx(kv_full, 2 * kTileBytes);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(kv_full, 2 * kTileBytes);
 #pragma unroll
-        for (int pn = 0; pn < DH / 64; ++pn) {
-          tma_load_4d(smem + kOffK + pn * kPanelBytes, &tmK, kv_full, pn * 64, it.j0, it.h, it.b);
-          tma_load_4d(smem + kOffV + pn * kPanelBytes, &tmV, kv_full, pn * 64, it.j0, it.h, it.b);
+          for (int pn = 0; pn < DH / 64; ++pn) {
+            tma_load_4d(smem + kOffK + pn * kPanelBytes, &tmK, kv_full, pn * 64, it.j0, it.h, it.b);
+            tma_load_4d(smem + kOffV + pn * kPanelBytes, &tmV, kv_full, pn * 64, it.j0, it.h, it.b);
+          }
         }
+        __syncwarp();
         for (int q = 0; q < it.n_q; ++q) {
           const uint32_t s = ring_n % kStages;
           mbar_wait(&qdo_empty[s], ((ring_n / kStages) & 1) ^ 1);
           ++ring_n;
-          mbar_arrive_expect_tx(&qdo_full[s], kStageBytes);
           const int i0 = (it.t0 + q) * kTile;
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&qdo_full[s], kStageBytes);
 #pragma unroll
-          for (int pn = 0; pn < DH / 64; ++pn) {
-            tma_load_4d(smem + kOffRing + s * kStageBytes + pn * kPanelBytes, &tmQ, &qdo_full[s], pn * 64, i0, it.h, it.b);
-            tma_load_4d(smem + kOffRing + s * kStageBytes + kTileBytes + pn * kPanelBytes, &tmDO, &qdo_full[s], pn * 64, i0,
-                        it.h, it.b);
+            for (int pn = 0; pn < DH / 64; ++pn) {
+              tma_load_4d(smem + kOffRing + s * kStageBytes + pn * kPanelBytes, &tmQ, &qdo_full[s], pn * 64, i0, it.h, it.b);
+              tma_load_4d(smem + kOffRing + s * kStageBytes + kTileBytes + pn * kPanelBytes, &tmDO, &qdo_full[s], pn * 64,
+                          i0, it.h, it.b);
+            }
           }
+          __syncwarp();
         }
       }
     }
@@ -242,7 +248,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
   } else if (warp == 9) {
     // ---------------------------------------------------------------- MMA issuer
-    // The WHOLE warp walks the schedule (waits included) and one elected lane issues each tcgen05 instruction.  Under a
+    // The WHOLE warp walks the schedule (waits included) and one elected lane issues each BATCH of tcgen05 instructions.  Under a
     // divergent `if (lane == 0)` ptxas wraps every UTCHMMA in an ELECT / BRA.U.ANY loop and moves its operands to uniform
     // registers one at a time: ~100 clk per MMA, and with 40 MMAs of 32-64 clk per pair this warp, not the tensor pipe or the
     // softmax, set the pace of the kernel (ncu source view: the issuer warp never waited).
@@ -255,15 +261,6 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       const uint32_t sK = smem_u32(smem + kOffK), sV = smem_u32(smem + kOffV), sDS = smem_u32(smem + kOffDS);
       const uint32_t tST = tmem_base + kColST, tDPT = tmem_base + kColDPT;
       const uint32_t tDV = tmem_base + kColDV, tDK = tmem_base + kColDK;
-      auto e_ss = [](uint32_t d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
-        if (elect_one()) umma_bf16_ss(d, da, db, idesc, accumulate);
-      };
-      auto e_ts = [](uint32_t d, uint32_t ta, uint64_t db, uint32_t idesc, uint32_t accumulate) {
-        if (elect_one()) umma_bf16_ts(d, ta, db, idesc, accumulate);
-      };
-      auto e_commit = [](uint64_t* bar) {
-        if (elect_one()) umma_commit(bar);
-      };
       uint32_t item_n = 0, ring_n = 0, pair_n = 0;
       for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
         const Bwd2Item it = bwd2_item(p, w);
@@ -345,53 +342,50 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             ++pair_n;
           }
         } else
-        for (int q = 0; q < it.n_q; ++q) {
+        for (int q = 0; q < it.n_q; ++q) {   // dh 128: one S^T / dP^T buffer, three batches per pair
           const uint32_t s = ring_n % kStages;
           mbar_wait(&qdo_full[s], (ring_n / kStages) & 1);
           ++ring_n;
           const uint32_t sQ = smem_u32(smem + kOffRing + s * kStageBytes), sDO = sQ + kTileBytes;
-          if (DH == 128 && pair_n > 0) {
+          if (pair_n > 0) {
             // the previous pair's dQ partial sits inside the S^T / dP^T columns MMA 1 is about to overwrite
             mbar_wait(&dq_free[0], (pair_n - 1) & 1);
           }
           tc_fence_after();
           // MMA 1 (in issue order behind MMA 2 of the previous pair, which still reads P^T / dS^T from these columns)
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < DH / 16; ++k) e_ss(tST, desc_kmajor(sK, k), desc_kmajor(sQ, k), idesc_s, k > 0);
+            for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tST, desc_kmajor(sK, k), desc_kmajor(sQ, k), idesc_s, k > 0);
 #pragma unroll
-          for (int k = 0; k < DH / 16; ++k) e_ss(tDPT, desc_kmajor(sV, k), desc_kmajor(sDO, k), idesc_s, k > 0);
-          e_commit(sdp_full);
+            for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDPT, desc_kmajor(sV, k), desc_kmajor(sDO, k), idesc_s, k > 0);
+            umma_commit(sdp_full);
+          }
+          __syncwarp();
           // MMA 2, first part: the k-steps of dV / dK over the query columns the softmax finishes first (chunk 0 of both
           // warpgroups = columns [0,32) and [64,96) = k 0,1,4,5) run while the softmax is still on the other 64 columns
           mbar_wait(pds_half, pair_n & 1);
           if (q == 0) mbar_wait(acc_free, (item_n & 1) ^ 1);       // the previous item's epilogue has read dV / dK
           const uint32_t acc = q > 0 ? 1u : 0u;
           tc_fence_after();
+          if (elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
-            const int k = (kk >> 1) * 4 + (kk & 1);
-            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            e_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
-          }
+            for (int kk = 0; kk < 4; ++kk) {  // P^T: query columns 16k.. sit at 32-bit columns (k/4)*64 + (k%4)*8
+              const int k = (kk >> 1) * 4 + (kk & 1);
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+            }
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const int k = (kk >> 1) * 4 + (kk & 1);
-            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            e_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+            for (int kk = 0; kk < 4; ++kk) {
+              const int k = (kk >> 1) * 4 + (kk & 1);
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, (acc | (kk > 0)) ? 1u : 0u);
+            }
           }
+          __syncwarp();
           // second part: everything is in TMEM / shared memory
           mbar_wait(pds_full, pair_n & 1);
-          if (DH == 64) {
-            const uint32_t buf = pair_n & 1;
-            mbar_wait(&dq_free[buf], ((pair_n >> 1) & 1) ^ 1);     // the drain has read this dQ buffer's previous content
-            tc_fence_after();
-            const uint32_t tDQ = tmem_base + kColDQ + buf * DH;
-#pragma unroll
-            for (int k = 0; k < kTile / 16; ++k)
-              e_ss(tDQ, desc_mnmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
-            e_commit(&dq_full[buf]);
-          } else {
-            tc_fence_after();
+          tc_fence_after();
+          if (elect_one()) {
             // dQ partial first, as four N = 32 pieces into the column gaps [32,64) [96,128) [160,192) [224,256): piece c
             // holds head-dim columns [32c, 32c + 32); B = K_j read MN-major at a 64-byte offset inside its 64-column panel
 #pragma unroll
@@ -400,28 +394,32 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
               const uint32_t sKc = sK + (c >> 1) * kPanelBytes + (c & 1) * 64;
 #pragma unroll
               for (int k = 0; k < kTile / 16; ++k)
-                e_ss(tDQc, desc_mnmajor(sDS, k), make_smem_desc(sKc + k * 2048, kPanelBytes, 1024), idesc_dq32,
+                umma_bf16_ss(tDQc, desc_mnmajor(sDS, k), make_smem_desc(sKc + k * 2048, kPanelBytes, 1024), idesc_dq32,
                              k > 0 ? 1u : 0u);
             }
-            e_commit(&dq_full[0]);
-          }
+            umma_commit(&dq_full[0]);
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const int k = (kk >> 1) * 4 + (kk & 1) + 2;
-            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            e_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, 1u);
-          }
+            for (int kk = 0; kk < 4; ++kk) {
+              const int k = (kk >> 1) * 4 + (kk & 1) + 2;
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDV, tST + a, desc_mnmajor(sDO, k), idesc_acc, 1u);
+            }
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            const int k = (kk >> 1) * 4 + (kk & 1) + 2;
-            const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
-            e_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, 1u);
+            for (int kk = 0; kk < 4; ++kk) {
+              const int k = (kk >> 1) * 4 + (kk & 1) + 2;
+              const uint32_t a = static_cast<uint32_t>((k >> 2) * 64 + (k & 3) * 8);
+              umma_bf16_ts(tDK, tDPT + a, desc_mnmajor(sQ, k), idesc_acc, 1u);
+            }
+            umma_commit(&qdo_empty[s]);
           }
-          e_commit(&qdo_empty[s]);
+          __syncwarp();
           ++pair_n;
         }
-        e_commit(acc_done);
-        e_commit(kv_empty);
+        if (elect_one()) {
+          umma_commit(acc_done);
+          umma_commit(kv_empty);
+        }
+        __syncwarp();
         ++item_n;
       }
     }

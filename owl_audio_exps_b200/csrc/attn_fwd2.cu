@@ -150,7 +150,10 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     // WG2: TMA producer (warp 8) and MMA issuer (warp 9); warps 10, 11 only hand their registers over
     // ------------------------------------------------------------------------------------------------------------
     reg_dealloc<80>();
-    if (warp == 8 && lane == 0) {
+    // Both roles: the WHOLE warp walks the schedule (waits included), one elected lane issues each batch of TMA / tcgen05
+    // instructions.  (Under `lane == 0` ptxas wraps every UTCHMMA / UTMALDG in an ELECT / BRA.U.ANY loop, ~100 clk per
+    // instruction: 30 tcgen05 instructions per KV step then take longer than the step's MMAs and exponentials.)
+    if (warp == 8) {
       uint32_t ring_n = 0;       // tiles pushed so far (ring position, persistent over work items)
       uint32_t q_n[2] = {0, 0};  // Q_t loads so far (indexed only inside fully unrolled loops)
       for (int w = blockIdx.x; w < p.total_items; w += gridDim.x) {
@@ -160,11 +163,14 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           if (it.z[t] <= it.a[t]) continue;
           mbar_wait(&q_empty[t], (q_n[t] & 1) ^ 1);
           ++q_n[t];
-          mbar_arrive_expect_tx(&q_full[t], Cfg::kTileBytes);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&q_full[t], Cfg::kTileBytes);
 #pragma unroll
-          for (int pn = 0; pn < DH / 64; ++pn)
-            tma_load_4d(smem + t * Cfg::kTileBytes + pn * kPanelBytes, &tmQ, &q_full[t], pn * 64, it.i0 + t * kTile, it.h,
-                        it.b);
+            for (int pn = 0; pn < DH / 64; ++pn)
+              tma_load_4d(smem + t * Cfg::kTileBytes + pn * kPanelBytes, &tmQ, &q_full[t], pn * 64, it.i0 + t * kTile, it.h,
+                          it.b);
+          }
+          __syncwarp();
         }
         for (int j = it.u0; j < it.u1; ++j) {
 #pragma unroll
@@ -172,15 +178,18 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             const uint32_t s = ring_n % kRing;
             mbar_wait(&ring_empty[s], ((ring_n / kRing) & 1) ^ 1);
             ++ring_n;
-            mbar_arrive_expect_tx(&ring_full[s], Cfg::kTileBytes);
             uint8_t* dst = smem + Cfg::kOffRing + s * Cfg::kTileBytes;
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&ring_full[s], Cfg::kTileBytes);
 #pragma unroll
-            for (int pn = 0; pn < DH / 64; ++pn)
-              tma_load_4d(dst + pn * kPanelBytes, kv == 0 ? &tmK : &tmV, &ring_full[s], pn * 64, j * kTile, it.h, it.b);
+              for (int pn = 0; pn < DH / 64; ++pn)
+                tma_load_4d(dst + pn * kPanelBytes, kv == 0 ? &tmK : &tmV, &ring_full[s], pn * 64, j * kTile, it.h, it.b);
+            }
+            __syncwarp();
           }
         }
       }
-    } else if (warp == 9 && lane == 0) {
+    } else if (warp == 9) {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
       constexpr uint32_t idesc_o = make_idesc_bf16(kTile, DH, false, true);
       uint32_t ring_n = 0;             // tiles consumed so far
@@ -203,22 +212,30 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         auto step = [&](auto tc, int j, uint32_t sV, bool more, uint32_t sK, uint32_t& q_n, uint32_t& p_n) {
           constexpr int t = decltype(tc)::value;
           const int a = it.a[t], z = it.z[t];
-          if (j >= a && j < z) {
+          const bool pv = j >= a && j < z;
+          const bool nxt = more && j + 1 >= a && j + 1 < z;
+          if (pv) {
             mbar_wait(&p_full[t], p_n & 1);
             ++p_n;
             if (j == a) mbar_wait(&o_free[t], q_n & 1);  // the previous item's epilogue has read O_t
-            tc_fence_after();
-            const uint32_t tP = tmem_base + (t == 0 ? Cfg::kColS0 : Cfg::kColS1);
-            const uint32_t tO = tmem_base + (t == 0 ? Cfg::kColO0 : Cfg::kColO1);
-#pragma unroll
-            for (int k = 0; k < kTile / 16; ++k)
-              umma_bf16_ts(tO, tP + k * 8, desc_mnmajor(sV, k), idesc_o, (j > a || k > 0) ? 1u : 0u);
-            umma_commit(&pv_done[t]);
           }
-          if (more && j + 1 >= a && j + 1 < z) {
+          if (pv || nxt) {
             tc_fence_after();
-            issue_s(tc, sK);
-            if (j + 2 == z) umma_commit(&q_empty[t]);  // that was this item's last S_t: Q_t may be overwritten
+            if (elect_one()) {
+              if (pv) {
+                const uint32_t tP = tmem_base + (t == 0 ? Cfg::kColS0 : Cfg::kColS1);
+                const uint32_t tO = tmem_base + (t == 0 ? Cfg::kColO0 : Cfg::kColO1);
+#pragma unroll
+                for (int k = 0; k < kTile / 16; ++k)
+                  umma_bf16_ts(tO, tP + k * 8, desc_mnmajor(sV, k), idesc_o, (j > a || k > 0) ? 1u : 0u);
+                umma_commit(&pv_done[t]);
+              }
+              if (nxt) {
+                issue_s(tc, sK);
+                if (j + 2 == z) umma_commit(&q_empty[t]);  // that was this item's last S_t: Q_t may be overwritten
+              }
+            }
+            __syncwarp();
           }
         };
         using T0 = std::integral_constant<int, 0>;
@@ -231,15 +248,18 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           ++ring_n;
           tc_fence_after();
           const uint32_t sK = smem_u32(smem + Cfg::kOffRing + s * Cfg::kTileBytes);
-          if (it.u0 >= it.a[0] && it.u0 < it.z[0]) {
-            issue_s(T0{}, sK);
-            if (it.u0 + 1 == it.z[0]) umma_commit(&q_empty[0]);
+          if (elect_one()) {
+            if (it.u0 >= it.a[0] && it.u0 < it.z[0]) {
+              issue_s(T0{}, sK);
+              if (it.u0 + 1 == it.z[0]) umma_commit(&q_empty[0]);
+            }
+            if (it.u0 >= it.a[1] && it.u0 < it.z[1]) {
+              issue_s(T1{}, sK);
+              if (it.u0 + 1 == it.z[1]) umma_commit(&q_empty[1]);
+            }
+            umma_commit(&ring_empty[s]);
           }
-          if (it.u0 >= it.a[1] && it.u0 < it.z[1]) {
-            issue_s(T1{}, sK);
-            if (it.u0 + 1 == it.z[1]) umma_commit(&q_empty[1]);
-          }
-          umma_commit(&ring_empty[s]);
+          __syncwarp();
         }
         for (int j = it.u0; j < it.u1; ++j) {
           const uint32_t sv = ring_n % kRing;  // V_j
@@ -256,8 +276,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           }
           step(T0{}, j, sV, more, sK, q_n0, p_n0);
           step(T1{}, j, sV, more, sK, q_n1, p_n1);
-          umma_commit(&ring_empty[sv]);
-          if (more) umma_commit(&ring_empty[sk]);
+          if (elect_one()) {
+            umma_commit(&ring_empty[sv]);
+            if (more) umma_commit(&ring_empty[sk]);
+          }
+          __syncwarp();
         }
       }
     }
