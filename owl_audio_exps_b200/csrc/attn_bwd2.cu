@@ -180,6 +180,12 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   pdl_wait();
   pdl_launch();
 
+  // Registers follow the work (setmaxnreg at the head of each warpgroup's role; 512 x 128 = 65536 in total): the TMA / MMA / stat-loader
+  // warpgroup needs few.  dh 64: the softmax warpgroups get 176 (the second chunk's TMEM loads are in flight while the
+  // first is computed).  dh 128: the drain gets 192 and reads the whole 128-column dQ partial at once, so the S^T / dP^T
+  // columns it sits in go back to the next pair's MMA 1 before the ~32 reduce-adds per thread are issued.
+  if (warp >= 8 && warp < 12) {
+  reg_dealloc<64>();
   if (warp == 8) {
     // ---------------------------------------------------------------- TMA producer (whole warp; one elected lane issues)
     {
@@ -246,8 +252,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (lane == 0) mbar_arrive(&stat_full[s]);
       }
     }
-  } else if (warp == 9) {
-    // ---------------------------------------------------------------- MMA issuer
+  } else {
+    // ---------------------------------------------------------------- MMA issuer (warp 9)
     // The WHOLE warp walks the schedule (waits included) and one elected lane issues each BATCH of tcgen05 instructions.  Under a
     // divergent `if (lane == 0)` ptxas wraps every UTCHMMA in an ELECT / BRA.U.ANY loop and moves its operands to uniform
     // registers one at a time: ~100 clk per MMA, and with 40 MMAs of 32-64 clk per pair this warp, not the tensor pipe or the
@@ -423,8 +429,11 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         ++item_n;
       }
     }
+  }
   } else if (warp >= 12) {
     // ---------------------------------------------------------------- WG3: dQ drain (thread = query row)
+    if (DH == 64) reg_dealloc<96>();
+    else reg_alloc<192>();
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
@@ -470,28 +479,27 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           ++pair_n;
           tc_fence_after();
           float* dst = p.dq_acc + (row_base + static_cast<long long>(it.t0 + q) * kTile + r) * DH;
+          uint32_t v[4][32];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {     // 32 columns at a time (128 registers per thread in this kernel)
-            uint32_t v[32];
-            tmem_ld_x32(tmem_base + 32u + 64u * static_cast<uint32_t>(c) + lane_addr, v);
-            tmem_ld_wait();
-            if (c == 3) {
-              tc_fence_before();
-              mbar_arrive(&dq_free[0]);
-            }
+          for (int c = 0; c < 4; ++c) tmem_ld_x32(tmem_base + 32u + 64u * static_cast<uint32_t>(c) + lane_addr, v[c]);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(&dq_free[0]);         // the columns are free before the reduce-adds are issued
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
 #pragma unroll
             for (int g = 0; g < 8; ++g)
               asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c * 32 + g * 4),
-                           "f"(__uint_as_float(v[4 * g])), "f"(__uint_as_float(v[4 * g + 1])),
-                           "f"(__uint_as_float(v[4 * g + 2])), "f"(__uint_as_float(v[4 * g + 3]))
+                           "f"(__uint_as_float(v[c][4 * g])), "f"(__uint_as_float(v[c][4 * g + 1])),
+                           "f"(__uint_as_float(v[c][4 * g + 2])), "f"(__uint_as_float(v[c][4 * g + 3]))
                            : "memory");
-          }
         }
       }
     }
     if (leader) tma_store_wait_all0();
   } else {
     // ---------------------------------------------------------------- WG0 / WG1: softmax, thread = key row
+    if (DH == 64) reg_alloc<176>();
     const int hf = warp >> 2;                 // query columns [64 hf, 64 hf + 64) of every pair
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;
@@ -530,11 +538,22 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         ++pair_n;
         tc_fence_after();
         const bool full = doc_row == nullptr && ilo <= i0 && i0 + 64 <= ihi;
+        uint32_t rsx[2][32], rpx[2][32];
+        if (DH == 64) {   // both chunks requested at once (176 registers): one TMEM round trip per pair instead of two
+          tmem_ld_x32(tST, rsx[0]);
+          tmem_ld_x32(tDPT, rpx[0]);
+          tmem_ld_x32(tST + 32, rsx[1]);
+          tmem_ld_x32(tDPT + 32, rpx[1]);
+        }
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-          uint32_t rs[32], rp[32], pk[16], dk[16];
-          tmem_ld_x32(tST + c * 32, rs);
-          tmem_ld_x32(tDPT + c * 32, rp);
+          uint32_t(&rs)[32] = rsx[DH == 64 ? c : 0];
+          uint32_t(&rp)[32] = rpx[DH == 64 ? c : 0];
+          uint32_t pk[16], dk[16];
+          if (DH == 128) {
+            tmem_ld_x32(tST + c * 32, rs);
+            tmem_ld_x32(tDPT + c * 32, rp);
+          }
           uint32_t valid = 0xffffffffu;
           if (!full) {
             const int qc = i0 + c * 32;
@@ -547,7 +566,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                 if (__ldg(doc_row + (qc + e + p.m.q_offset) / p.m.T) != dkey) valid &= ~(1u << e);
             }
           }
-          tmem_ld_wait();
+          if (DH == 128 || c == 0) tmem_ld_wait();
           if (full) bwd2_softmax_chunk<true>(rs, rp, pk, dk, st_lse + c * 8, st_del + c * 8, p.scale_log2, p.scale, valid);
           else bwd2_softmax_chunk<false>(rs, rp, pk, dk, st_lse + c * 8, st_del + c * 8, p.scale_log2, p.scale, valid);
           // P^T / dS^T over the columns this thread has already read (first half of its own 64-column region)
