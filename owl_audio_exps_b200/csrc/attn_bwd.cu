@@ -173,27 +173,34 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDQ = tmem_base + 256;
 
   if (warp == 0) {
-    if (lane == 0 && n_kv > 0) {
-      mbar_arrive_expect_tx(qdo_full, 2 * Cfg::kTileBytes);
+    // (whole warp walks the loop, one elected lane issues each batch: no per-instruction ELECT / BRA.U.ANY loop)
+    if (n_kv > 0) {
+      if (elect_one()) {
+        mbar_arrive_expect_tx(qdo_full, 2 * Cfg::kTileBytes);
 #pragma unroll
-      for (int pn = 0; pn < DH / 64; ++pn) {
-        tma_load_4d(smem + pn * kPanelBytes, &tmQ, qdo_full, pn * 64, i0, h, b);
-        tma_load_4d(smem + Cfg::kOffDO + pn * kPanelBytes, &tmDO, qdo_full, pn * 64, i0, h, b);
+        for (int pn = 0; pn < DH / 64; ++pn) {
+          tma_load_4d(smem + pn * kPanelBytes, &tmQ, qdo_full, pn * 64, i0, h, b);
+          tma_load_4d(smem + Cfg::kOffDO + pn * kPanelBytes, &tmDO, qdo_full, pn * 64, i0, h, b);
+        }
       }
+      __syncwarp();
       for (int it = 0; it < n_kv; ++it) {
         const int s = it & 1;
         mbar_wait(&kv_empty[s], ((it >> 1) & 1) ^ 1);
-        mbar_arrive_expect_tx(&kv_full[s], 2 * Cfg::kTileBytes);
         const int j0 = (t0 + it) * kTile;
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&kv_full[s], 2 * Cfg::kTileBytes);
 #pragma unroll
-        for (int pn = 0; pn < DH / 64; ++pn) {
-          tma_load_4d(smem + Cfg::kOffK + s * Cfg::kTileBytes + pn * kPanelBytes, &tmK, &kv_full[s], pn * 64, j0, h, b);
-          tma_load_4d(smem + Cfg::kOffV + s * Cfg::kTileBytes + pn * kPanelBytes, &tmV, &kv_full[s], pn * 64, j0, h, b);
+          for (int pn = 0; pn < DH / 64; ++pn) {
+            tma_load_4d(smem + Cfg::kOffK + s * Cfg::kTileBytes + pn * kPanelBytes, &tmK, &kv_full[s], pn * 64, j0, h, b);
+            tma_load_4d(smem + Cfg::kOffV + s * Cfg::kTileBytes + pn * kPanelBytes, &tmV, &kv_full[s], pn * 64, j0, h, b);
+          }
         }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && n_kv > 0) {
+    if (n_kv > 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
       constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, false, true);
       const uint32_t sQ = smem_u32(smem), sDO = smem_u32(smem + Cfg::kOffDO), sDS = smem_u32(smem + Cfg::kOffDS);
@@ -204,11 +211,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         tc_fence_after();
         const uint32_t sK = smem_u32(smem + Cfg::kOffK + s * Cfg::kTileBytes);
         const uint32_t sV = smem_u32(smem + Cfg::kOffV + s * Cfg::kTileBytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tS, desc_kmajor(sQ, k), desc_kmajor(sK, k), idesc_s, k > 0);
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tS, desc_kmajor(sQ, k), desc_kmajor(sK, k), idesc_s, k > 0);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDP, desc_kmajor(sDO, k), desc_kmajor(sV, k), idesc_s, k > 0);
-        umma_commit(sdp_full);
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDP, desc_kmajor(sDO, k), desc_kmajor(sV, k), idesc_s, k > 0);
+          umma_commit(sdp_full);
+        }
+        __syncwarp();
       };
       mbar_wait(qdo_full, 0);
       issue_sdp(0);
@@ -218,11 +228,14 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_wait(ds_full, it & 1);
         tc_fence_after();
         const uint32_t sK = smem_u32(smem + Cfg::kOffK + s * Cfg::kTileBytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kTile / 16; ++k)
-          umma_bf16_ss(tDQ, desc_kmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, (it > 0 || k > 0) ? 1u : 0u);
-        umma_commit(&kv_empty[s]);
-        umma_commit(dq_done);
+          for (int k = 0; k < kTile / 16; ++k)
+            umma_bf16_ss(tDQ, desc_kmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, (it > 0 || k > 0) ? 1u : 0u);
+          umma_commit(&kv_empty[s]);
+          umma_commit(dq_done);
+        }
+        __syncwarp();
       }
     }
   } else {
@@ -363,27 +376,35 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const uint32_t tDQ = tmem_base + Cfg::kColDQ;  // FUSE_DQ only
 
   if (warp == 0) {
-    if (lane == 0 && n_q > 0) {
-      mbar_arrive_expect_tx(kv_full, 2 * Cfg::kTileBytes);
+    // (whole warp walks the loop, one elected lane issues each batch: no per-instruction ELECT / BRA.U.ANY loop)
+    if (n_q > 0) {
+      if (elect_one()) {
+        mbar_arrive_expect_tx(kv_full, 2 * Cfg::kTileBytes);
 #pragma unroll
-      for (int pn = 0; pn < DH / 64; ++pn) {
-        tma_load_4d(smem + pn * kPanelBytes, &tmK, kv_full, pn * 64, j0, h, b);
-        tma_load_4d(smem + Cfg::kOffV + pn * kPanelBytes, &tmV, kv_full, pn * 64, j0, h, b);
+        for (int pn = 0; pn < DH / 64; ++pn) {
+          tma_load_4d(smem + pn * kPanelBytes, &tmK, kv_full, pn * 64, j0, h, b);
+          tma_load_4d(smem + Cfg::kOffV + pn * kPanelBytes, &tmV, kv_full, pn * 64, j0, h, b);
+        }
       }
+      __syncwarp();
       for (int it = 0; it < n_q; ++it) {
         const int s = it % kStages;
         mbar_wait(&qdo_empty[s], ((it / kStages) & 1) ^ 1);
-        mbar_arrive_expect_tx(&qdo_full[s], 2 * Cfg::kTileBytes);
         const int i0 = (t0 + it) * kTile;
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&qdo_full[s], 2 * Cfg::kTileBytes);
 #pragma unroll
-        for (int pn = 0; pn < DH / 64; ++pn) {
-          tma_load_4d(smem + Cfg::kOffQ + s * Cfg::kTileBytes + pn * kPanelBytes, &tmQ, &qdo_full[s], pn * 64, i0, h, b);
-          tma_load_4d(smem + Cfg::kOffDO + s * Cfg::kTileBytes + pn * kPanelBytes, &tmDO, &qdo_full[s], pn * 64, i0, h, b);
+          for (int pn = 0; pn < DH / 64; ++pn) {
+            tma_load_4d(smem + Cfg::kOffQ + s * Cfg::kTileBytes + pn * kPanelBytes, &tmQ, &qdo_full[s], pn * 64, i0, h, b);
+            tma_load_4d(smem + Cfg::kOffDO + s * Cfg::kTileBytes + pn * kPanelBytes, &tmDO, &qdo_full[s], pn * 64, i0, h,
+                        b);
+          }
         }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && n_q > 0) {
+    if (n_q > 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
       constexpr uint32_t idesc_acc = make_idesc_bf16(kTile, DH, true, true);
       const uint32_t sK = smem_u32(smem), sV = smem_u32(smem + Cfg::kOffV);
@@ -395,11 +416,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tc_fence_after();
         const uint32_t sQ = smem_u32(smem + Cfg::kOffQ + s * Cfg::kTileBytes);
         const uint32_t sDO = smem_u32(smem + Cfg::kOffDO + s * Cfg::kTileBytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tS, desc_kmajor(sQ, k), desc_kmajor(sK, k), idesc_s, k > 0);
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tS, desc_kmajor(sQ, k), desc_kmajor(sK, k), idesc_s, k > 0);
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDP, desc_kmajor(sDO, k), desc_kmajor(sV, k), idesc_s, k > 0);
-        umma_commit(sdp_full);
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tDP, desc_kmajor(sDO, k), desc_kmajor(sV, k), idesc_s, k > 0);
+          umma_commit(sdp_full);
+        }
+        __syncwarp();
       };
       mbar_wait(kv_full, 0);
       issue_sdp(0);
@@ -410,20 +434,23 @@ attn_bwd_dkv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         tc_fence_after();
         const uint32_t sQ = smem_u32(smem + Cfg::kOffQ + s * Cfg::kTileBytes);
         const uint32_t sDO = smem_u32(smem + Cfg::kOffDO + s * Cfg::kTileBytes);
-#pragma unroll
-        for (int k = 0; k < kTile / 16; ++k)
-          umma_bf16_ss(tDV, desc_mnmajor(sP, k), desc_mnmajor(sDO, k), idesc_acc, (it > 0 || k > 0) ? 1u : 0u);
-#pragma unroll
-        for (int k = 0; k < kTile / 16; ++k)
-          umma_bf16_ss(tDK, desc_mnmajor(sDS, k), desc_mnmajor(sQ, k), idesc_acc, (it > 0 || k > 0) ? 1u : 0u);
-        if (FUSE_DQ) {  // dQ[i, :] = sum_j dS[i, j] K[j, :]: dS as the K-major A operand, K as the MN-major B operand
-          constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, false, true);
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < kTile / 16; ++k)
-            umma_bf16_ss(tDQ, desc_kmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+            umma_bf16_ss(tDV, desc_mnmajor(sP, k), desc_mnmajor(sDO, k), idesc_acc, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+          for (int k = 0; k < kTile / 16; ++k)
+            umma_bf16_ss(tDK, desc_mnmajor(sDS, k), desc_mnmajor(sQ, k), idesc_acc, (it > 0 || k > 0) ? 1u : 0u);
+          if (FUSE_DQ) {  // dQ[i, :] = sum_j dS[i, j] K[j, :]: dS as the K-major A operand, K as the MN-major B operand
+            constexpr uint32_t idesc_dq = make_idesc_bf16(kTile, DH, false, true);
+#pragma unroll
+            for (int k = 0; k < kTile / 16; ++k)
+              umma_bf16_ss(tDQ, desc_kmajor(sDS, k), desc_mnmajor(sK, k), idesc_dq, k > 0 ? 1u : 0u);
+          }
+          umma_commit(&qdo_empty[s]);
+          umma_commit(acc_done);
         }
-        umma_commit(&qdo_empty[s]);
-        umma_commit(acc_done);
+        __syncwarp();
         if (kStages == 1 && it + 1 < n_q) issue_sdp(it + 1);
       }
     }

@@ -201,28 +201,37 @@ attn_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   for (int t = tile_lo; t < tile_hi; ++t) n_kv += ring.tile_any(t * kTile) ? 1 : 0;
 
   if (warp == 0) {
-    if (lane == 0 && n_kv > 0) {
+    // (whole warp walks the loop, one elected lane issues each batch: no per-instruction ELECT / BRA.U.ANY loop)
+    if (n_kv > 0) {
       if (!FUSED) {
-        mbar_arrive_expect_tx(q_full, Cfg::kTileBytes);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(q_full, Cfg::kTileBytes);
 #pragma unroll
-        for (int pn = 0; pn < DH / 64; ++pn) tma_load_4d(smem + pn * kPanelBytes, &tmQ, q_full, pn * 64, 0, h, b);
+          for (int pn = 0; pn < DH / 64; ++pn) tma_load_4d(smem + pn * kPanelBytes, &tmQ, q_full, pn * 64, 0, h, b);
+        }
+        __syncwarp();
       }
       int it = has_new ? 1 : 0;    // stage 0 of the first round belongs to the tile of new rows
       for (int t = tile_lo; t < tile_hi; ++t) {
         if (!ring.tile_any(t * kTile)) continue;
         const int s = it & 1;
         mbar_wait(&kv_empty[s], ((it >> 1) & 1) ^ 1);
-        mbar_arrive_expect_tx(&kv_full[s], 2 * Cfg::kTileBytes);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&kv_full[s], 2 * Cfg::kTileBytes);
 #pragma unroll
-        for (int pn = 0; pn < DH / 64; ++pn) {
-          tma_load_4d(smem + Cfg::kOffK + s * Cfg::kTileBytes + pn * kPanelBytes, &tmK, &kv_full[s], pn * 64, t * kTile, h, b);
-          tma_load_4d(smem + Cfg::kOffV + s * Cfg::kTileBytes + pn * kPanelBytes, &tmV, &kv_full[s], pn * 64, t * kTile, h, b);
+          for (int pn = 0; pn < DH / 64; ++pn) {
+            tma_load_4d(smem + Cfg::kOffK + s * Cfg::kTileBytes + pn * kPanelBytes, &tmK, &kv_full[s], pn * 64, t * kTile, h,
+                        b);
+            tma_load_4d(smem + Cfg::kOffV + s * Cfg::kTileBytes + pn * kPanelBytes, &tmV, &kv_full[s], pn * 64, t * kTile, h,
+                        b);
+          }
         }
+        __syncwarp();
         ++it;
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && n_kv > 0) {
+    if (n_kv > 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
       constexpr uint32_t idesc_o = make_idesc_bf16(kTile, DH, false, true);
       const uint32_t sQ = smem_u32(smem), sP = smem_u32(smem + Cfg::kOffP);
@@ -232,9 +241,12 @@ attn_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         if (it > 0) mbar_wait(s_free, (it - 1) & 1);
         tc_fence_after();
         const uint32_t sK = smem_u32(smem + Cfg::kOffK + s * Cfg::kTileBytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tS, desc_kmajor(sQ, k), desc_kmajor(sK, k), idesc_s, k > 0);
-        umma_commit(s_full);
+          for (int k = 0; k < DH / 16; ++k) umma_bf16_ss(tS, desc_kmajor(sQ, k), desc_kmajor(sK, k), idesc_s, k > 0);
+          umma_commit(s_full);
+        }
+        __syncwarp();
       };
       mbar_wait(q_full, 0);
       issue_s(0);
@@ -244,11 +256,14 @@ attn_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         mbar_wait(p_full, it & 1);
         tc_fence_after();
         const uint32_t sV = smem_u32(smem + Cfg::kOffV + s * Cfg::kTileBytes);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kTile / 16; ++k)
-          umma_bf16_ss(tO, desc_kmajor(sP, k), desc_mnmajor(sV, k), idesc_o, (it > 0 || k > 0) ? 1u : 0u);
-        umma_commit(&kv_empty[s]);
-        umma_commit(pv_done);
+          for (int k = 0; k < kTile / 16; ++k)
+            umma_bf16_ss(tO, desc_kmajor(sP, k), desc_mnmajor(sV, k), idesc_o, (it > 0 || k > 0) ? 1u : 0u);
+          umma_commit(&kv_empty[s]);
+          umma_commit(pv_done);
+        }
+        __syncwarp();
       }
     }
   } else {

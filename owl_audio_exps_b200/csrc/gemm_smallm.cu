@@ -230,20 +230,27 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   // CTA on this SM has exited, others are in their reduction round trips), so the producer fills the ring with the first
   // weight tiles BEFORE griddepcontrol.wait and HBM keeps streaming across the kernel boundary.
   int pre = 0;
-  if (warp == 0 && lane == 0 && static_cast<int>(blockIdx.x) < total) {
+  // (producer and issuer: the whole warp walks the loops, one elected lane issues each batch of TMA / tcgen05 instructions -
+  // under `lane == 0` ptxas wraps each of them in an ELECT / BRA.U.ANY loop, ~100 clk per instruction)
+  if (warp == 0 && static_cast<int>(blockIdx.x) < total) {
     const int t = blockIdx.x;
     const int tn = p.cluster ? t / p.splits : t % p.tiles_n, ks = p.cluster ? t % p.splits : t / p.tiles_n;
     const int kb0 = ks * p.kb_per_split, kb1 = min(kb0 + p.kb_per_split, p.kb_total);
-    for (int kb = kb0; kb < kb1 && pre < kStages; ++kb, ++pre) {
-      mbar_arrive_expect_tx(&full_bar[pre], p.ln_x != nullptr ? kBBytes : kStageBytes);
-      tma_load_2d(smem_b + pre * kBBytes, &tmB, &full_bar[pre], kb * kSmBK, tn * BN);
+    const int n_pre = min(kb1 - kb0, kStages);
+    if (elect_one()) {
+      for (int i = 0; i < n_pre; ++i) {
+        mbar_arrive_expect_tx(&full_bar[i], p.ln_x != nullptr ? kBBytes : kStageBytes);
+        tma_load_2d(smem_b + i * kBBytes, &tmB, &full_bar[i], (kb0 + i) * kSmBK, tn * BN);
+      }
     }
+    __syncwarp();
+    pre = n_pre > 0 ? n_pre : 0;
   }
   pdl_wait();     // the activations (and the zeroed workspace) come from the previous kernel
   pdl_launch();
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
@@ -253,19 +260,22 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           const bool tma_a = p.ln_x == nullptr;   // adaLN prologue: the epilogue warps write the A tile instead
           if (pre > 0) {   // this stage's weights are already on their way: add the activations
             --pre;
-            if (tma_a) tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);
+            if (tma_a && elect_one()) tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);
           } else {
             mbar_wait(&empty_bar[stage], phase ^ 1);
-            mbar_arrive_expect_tx(&full_bar[stage], tma_a ? kStageBytes : kBBytes);
-            tma_load_2d(smem_b + stage * kBBytes, &tmB, &full_bar[stage], kb * kSmBK, tn * BN);   // weights: HBM
-            if (tma_a) tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);   // activations: L2
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&full_bar[stage], tma_a ? kStageBytes : kBBytes);
+              tma_load_2d(smem_b + stage * kBBytes, &tmB, &full_bar[stage], kb * kSmBK, tn * BN);   // weights: HBM
+              if (tma_a) tma_load_2d(smem_a + stage * kSmABytes, &tmA, &full_bar[stage], kb * kSmBK, 0);   // activations: L2
+            }
           }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = make_idesc_bf16(128, BN, false, false);
       int stage = 0, as = 0;
       uint32_t phase = 0, aphase = 0;
@@ -279,14 +289,21 @@ gemm_smallm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem_a + stage * kSmABytes), sb = smem_u32(smem_b + stage * kBBytes);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kSmBK / 16; ++k)
-            umma_bf16_ss(tacc, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
-                         (kb > kb0 || k > 0) ? 1u : 0u);
-          umma_commit(&empty_bar[stage]);
+            for (int k = 0; k < kSmBK / 16; ++k)
+              umma_bf16_ss(tacc, make_smem_desc(sa + k * 32, 16, 1024), make_smem_desc(sb + k * 32, 16, 1024), idesc,
+                           (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_commit(&empty_bar[stage]);
+            if (kb + 1 == kb1) umma_commit(&tfull_bar[as]);
+          }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[as]);
+        if (kb1 <= kb0) {
+          if (elect_one()) umma_commit(&tfull_bar[as]);
+          __syncwarp();
+        }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
