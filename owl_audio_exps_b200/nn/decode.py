@@ -135,6 +135,25 @@ def _stack_operands(dit):
     return per_layer, wc, bc
 
 
+# Which kernel multiplies the square-ish Linears (qkv, out, fc1: N >= K) of a decode evaluation.  "smallm": the
+# weight-streaming split-K kernel for all of them.  "tiles": the training GEMM's 64- / 128-wide tiles, no split-K (no
+# fp32 atomics, no arrival counter); fc2 (K = 4 N) always streams through the split-K kernel.  OWL_DECODE_GEMM selects;
+# measured on B200 (tools/decode_eval.py, causvid.yml model, graph replay): tiles 2.52 ms, smallm 2.69 ms per evaluation.
+DECODE_GEMM = _os.environ.get("OWL_DECODE_GEMM", "tiles")
+
+
+def _lin(a, w, M, N, K, *, mode=0, bias=None, out0=None, aux0=None, aux1=None, rows_per_frame=1, next_w=None, scratch=None):
+    if DECODE_GEMM == "tiles" and N >= K:
+        kw = {}
+        if mode == OWL_EPI_BIAS_SILU:     # the training epilogue writes the pre-activation too
+            kw["out1"] = out0
+            out0 = scratch
+        ops.gemm(0, a, w, M, N, K, mode=mode, bias=bias, out0=out0, aux0=aux0, aux1=aux1, rows_per_frame=rows_per_frame, **kw)
+    else:
+        ops.gemm_smallm(a, w, M, N, K, mode=mode, bias=bias, out0=out0, aux0=aux0, aux1=aux1, rows_per_frame=rows_per_frame,
+                        next_w=next_w)
+
+
 @torch.no_grad()
 def dit_decode_forward(dit, x, cond, ring: RingKVCache):
     """DiT.forward (attn.py:175-191) for <= 128 new tokens against a RingKVCache, decode mode (no mask).  x [B, L, d],
@@ -165,6 +184,7 @@ def dit_decode_forward(dit, x, cond, ring: RingKVCache):
     qkv = torch.empty(B, L, 3 * d, device=dev, dtype=bf16)
     o = torch.empty(B, L, d, device=dev, dtype=bf16)
     s = torch.empty(M, 4 * d, device=dev, dtype=bf16)
+    z = torch.empty(M, 4 * d, device=dev, dtype=bf16) if DECODE_GEMM == "tiles" else None
     for i, blk in enumerate(dit.blocks):
         W = per_layer[i]
         mod = mod_all[:, i * 6 * d:(i + 1) * 6 * d]
@@ -177,7 +197,7 @@ def dit_decode_forward(dit, x, cond, ring: RingKVCache):
                             adaln=(a1, b1, T, OF.RMS_EPS))
         else:
             h1, _ = ops.adaln_modulate_fwd(x2, a1, b1, T, OF.RMS_EPS, want_rstd=False)
-            ops.gemm_smallm(h1, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d), next_w=W["wout"])
+            _lin(h1, W["wqkv"], M, 3 * d, d, bias=W["bqkv"], out0=qkv.view(M, 3 * d), next_w=W["wout"])
         vis = attn.local_offset if attn.local else 0
         if FUSED_ATTENTION:
             # QK-norm + RoPE + ring append applied in the attention kernel's own load path (one launch)
@@ -186,14 +206,14 @@ def dit_decode_forward(dit, x, cond, ring: RingKVCache):
             ops.qk_norm_rope_decode(qkv, attn.rope.cos, attn.rope.sin, ring.state, q, ring.k[i], ring.v[i], H, OF.RMS_EPS)
             ops.attn_decode(q, ring.k[i], ring.v[i], ring.state, vis, out=o)
         x1 = torch.empty(M, d, device=dev, dtype=bf16)
-        ops.gemm_smallm(o.view(M, d), W["wout"], M, d, d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["bout"], out0=x1, aux0=x2,
-                        aux1=c1, rows_per_frame=T, next_w=W["w1"])
+        _lin(o.view(M, d), W["wout"], M, d, d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["bout"], out0=x1, aux0=x2, aux1=c1,
+             rows_per_frame=T, next_w=W["w1"])
         if ADALN_PROLOGUE:
             ops.gemm_smallm(x1, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"],
                             adaln=(a2, b2, T, OF.RMS_EPS))
         else:
             h2, _ = ops.adaln_modulate_fwd(x1, a2, b2, T, OF.RMS_EPS, want_rstd=False)
-            ops.gemm_smallm(h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"])
+            _lin(h2, W["w1"], M, 4 * d, d, mode=OWL_EPI_BIAS_SILU, bias=W["b1"], out0=s, next_w=W["w2"], scratch=z)
         x2n = torch.empty(M, d, device=dev, dtype=bf16)
         ops.gemm_smallm(s, W["w2"], M, d, 4 * d, mode=OWL_EPI_GATE_RESIDUAL, bias=W["b2"], out0=x2n, aux0=x1, aux1=c2,
                         rows_per_frame=T, next_w=nxt)
