@@ -139,7 +139,8 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint64_t* pds_half = sdp_full + 8;        // softmax -> MMA: first 32 query columns of both halves are in TMEM (256 arrivals)
   uint64_t* s_half = sdp_full + 9;          // [2] dh 64, MMA -> softmax warpgroup h: S^T / dP^T of ITS 64 query columns
   uint64_t* p_half = sdp_full + 11;         // [2] dh 64, softmax warpgroup h -> MMA (128 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 13);
+  uint64_t* ds_free = sdp_full + 13;        // dh 128, drain -> softmax: the dQ staging (which borrows the dS^T buffer) has been read
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sdp_full + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -157,6 +158,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     mbar_init(sdp_full, 1);
     mbar_init(pds_full, 256);
     mbar_init(pds_half, 256);
+    mbar_init(ds_free, 1);
     for (int h = 0; h < 2; ++h) {
       mbar_init(&s_half[h], 1);
       mbar_init(&p_half[h], 128);
@@ -478,21 +480,44 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           mbar_wait(&dq_full[0], pair_n & 1);
           ++pair_n;
           tc_fence_after();
-          float* dst = p.dq_acc + (row_base + static_cast<long long>(it.t0 + q) * kTile + r) * DH;
           uint32_t v[4][32];
 #pragma unroll
           for (int c = 0; c < 4; ++c) tmem_ld_x32(tmem_base + 32u + 64u * static_cast<uint32_t>(c) + lane_addr, v[c]);
           tmem_ld_wait();
           tc_fence_before();
-          mbar_arrive(&dq_free[0]);         // the columns are free before the reduce-adds are issued
+          mbar_arrive(&dq_free[0]);         // the columns go back to the next pair's MMA 1
+          // No shared memory is left for a 64 KB staging tile, and 32 red.global per thread (16 bytes per lane, 32 rows per
+          // warp instruction) made the dQ accumulation the bound of this kernel (5B shape: 208 ms with, 132 ms without it).
+          // The dS^T buffer is idle from here (dq_full: the dQ MMAs have read it) until the NEXT pair's softmax writes it -
+          // after MMA 1 (1024 clk) and a chunk of exponentials: the partial goes through it in two 32 KB rounds of
+          // full-row TMA reduce-adds, and the softmax waits for ds_free before its first dS^T store.
+          uint8_t* stag2 = smem + kOffDS;
+          const int row0 = static_cast<int>(row_base + static_cast<long long>(it.t0 + q) * kTile);
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
+          for (int half = 0; half < 2; ++half) {
+            if (half == 1) {
+              if (leader) tma_store_wait_read0();   // round 0 has been read
+              named_bar_sync(1, 128);
+            }
 #pragma unroll
-            for (int g = 0; g < 8; ++g)
-              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c * 32 + g * 4),
-                           "f"(__uint_as_float(v[c][4 * g])), "f"(__uint_as_float(v[c][4 * g + 1])),
-                           "f"(__uint_as_float(v[c][4 * g + 2])), "f"(__uint_as_float(v[c][4 * g + 3]))
-                           : "memory");
+            for (int pn = 0; pn < 2; ++pn)
+#pragma unroll
+              for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(stag2 + pn * 16384 + r * 128 + ((c ^ (r & 7)) << 4)) =
+                    make_uint4(v[half * 2 + pn][4 * c], v[half * 2 + pn][4 * c + 1], v[half * 2 + pn][4 * c + 2],
+                               v[half * 2 + pn][4 * c + 3]);
+            fence_proxy_async_smem();
+            named_bar_sync(1, 128);
+            if (leader) {
+              tma_reduce_add_2d(&tmDQ, stag2, half * 64, row0);
+              tma_reduce_add_2d(&tmDQ, stag2 + 16384, half * 64 + 32, row0);
+              tma_store_commit();
+            }
+          }
+          if (leader) {
+            tma_store_wait_read0();
+            mbar_arrive(ds_free);
+          }
         }
       }
     }
@@ -572,6 +597,7 @@ attn_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           // P^T / dS^T over the columns this thread has already read (first half of its own 64-column region)
           tmem_st_x16(tST + c * 16, pk);
           tmem_st_x16(tDPT + c * 16, dk);
+          if (DH == 128 && c == 0 && pair_n > 1) mbar_wait(ds_free, pair_n & 1);   // the previous pair's dQ staging is out
 #pragma unroll
           for (int g = 0; g < 4; ++g)
             *reinterpret_cast<uint4*>(sDSp + tile_chunk_offset(r, hf * 8 + c * 4 + g)) =
