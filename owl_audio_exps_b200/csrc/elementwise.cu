@@ -107,8 +107,25 @@ __global__ void __launch_bounds__(256) cast_multi_kernel(const CastSegs s) {
   const long long stride = static_cast<long long>(s.blk0[i + 1] - s.blk0[i]) * blockDim.x;
   const float4* src = reinterpret_cast<const float4*>(s.src[i]);
   bf16* dst = s.dst[i];
-#pragma unroll 2
-  for (long long j = static_cast<long long>(local) * blockDim.x + threadIdx.x; j < s.n8[i]; j += stride) {
+  long long j = static_cast<long long>(local) * blockDim.x + threadIdx.x;
+  // four independent 32-byte reads in flight per thread (one resident wave of CTAs covers the whole launch: the weights of
+  // a block are 75 MB at audio.yml's width and this kernel sits on the step's critical path 17 times)
+  for (; j + 3 * stride < s.n8[i]; j += 4 * stride) {
+    float4 a[4], b[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      a[u] = __ldg(src + 2 * (j + u * stride));
+      b[u] = __ldg(src + 2 * (j + u * stride) + 1);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint4 o;
+      o.x = pack_bf16(a[u].x, a[u].y); o.y = pack_bf16(a[u].z, a[u].w);
+      o.z = pack_bf16(b[u].x, b[u].y); o.w = pack_bf16(b[u].z, b[u].w);
+      stg16(dst + 8 * (j + u * stride), o);
+    }
+  }
+  for (; j < s.n8[i]; j += stride) {
     const float4 a = __ldg(src + 2 * j);
     const float4 b = __ldg(src + 2 * j + 1);
     uint4 o;
@@ -1139,7 +1156,7 @@ int owl_cast_f32_bf16_multi(const float* const* srcs, void* const* dsts, const i
                             owl_stream_t stream) {
   OWL_REQUIRE(srcs && dsts && ns && count > 0, OWL_ERR_BAD_ARG);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const long long cap_total = static_cast<long long>(sm_count()) * 16;
+  const long long cap_total = static_cast<long long>(sm_count()) * 8;   // 8 x 256 threads = one resident wave per SM
   for (int base = 0; base < count; base += 8) {
     const int c = count - base < 8 ? count - base : 8;
     CastSegs s{};
