@@ -16,11 +16,18 @@ namespace owl {
 static constexpr int kTile = 128;
 static constexpr int kPanelBytes = 128 * 128;  // [128 rows][64 bf16]
 
+// Descriptor of the same tile `bytes` further on: the start address sits in the low 14 bits of the low word (in 16-byte
+// units; shared memory ends far below 2^18 bytes, so the sum cannot carry into the next field).  One add on the low word:
+// the unrolled k-loops of the MMA issuers derive every k-step's descriptor from ONE base per tile instead of re-encoding
+// it (shift / mask / or / or), which is what the issuer warps spend their instructions on.
+__device__ __forceinline__ uint64_t desc_advance(uint64_t d, uint32_t bytes) {
+  return (d & 0xFFFFFFFF00000000ull) | static_cast<uint64_t>(static_cast<uint32_t>(d) + (bytes >> 4));
+}
 __device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile_saddr, int k) {
-  return make_smem_desc(tile_saddr + (k >> 2) * kPanelBytes + (k & 3) * 32, 16, 1024);
+  return desc_advance(make_smem_desc(tile_saddr, 16, 1024), static_cast<uint32_t>((k >> 2) * kPanelBytes + (k & 3) * 32));
 }
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile_saddr, int k) {
-  return make_smem_desc(tile_saddr + k * 2048, kPanelBytes, 1024);
+  return desc_advance(make_smem_desc(tile_saddr, kPanelBytes, 1024), static_cast<uint32_t>(k * 2048));
 }
 
 // byte offset of the 16-byte chunk holding columns [8*chunk16, 8*chunk16+8) of row `row` in a
